@@ -1,0 +1,335 @@
+// RMSNorm and LayerNorm, forward and backward, one CTA per row with the row held
+// in registers (single pass over HBM).  Weight/bias gradients are reduced across
+// rows in two steps: per-CTA partial sums into a caller-provided fp32 scratch
+// [num_partials, D], then a column reduction.
+//
+// Reference semantics: RMSNorm  /root/reference/fsdp_tp/llama2_model.py:115-142
+//   (fp32 upcast, x * rsqrt(mean(x^2) + eps), cast back, * weight);
+// LayerNorm: nn.LayerNorm in /root/reference/scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:141-143
+//   and /root/reference/scripts/04_pipeline_parallel_pp/03_pipeline_training.py:56,59.
+#include "vec.cuh"
+
+namespace b200 {
+
+constexpr int kMaxChunks = 4;  // 8-element chunks cached per thread
+
+// ------------------------------- RMSNorm -----------------------------------
+template <typename T>
+__global__ void rmsnorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w, T* __restrict__ y,
+                                   float* __restrict__ rstd_out, int rows, int D, float eps) {
+  __shared__ float red[33];
+  const int nchunks = D >> 3;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* xr = x + (long long)row * D;
+    float v[kMaxChunks][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        Vec8<T>::load(xr + c * 8, v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
+      }
+    }
+    ss = block_sum(ss, red);
+    const float rstd = rsqrtf(ss / (float)D + eps);
+    if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
+    T* yr = y + (long long)row * D;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        float wv[8], o[8];
+        Vec8<T>::load(w + c * 8, wv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = to_f<T>(from_f<T>(v[i][j] * rstd)) * wv[j];
+        Vec8<T>::store(yr + c * 8, o);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                   const T* __restrict__ w, const float* __restrict__ rstd_in,
+                                   T* __restrict__ dx, float* __restrict__ dw_partial, int rows, int D,
+                                   int add_to_dx) {
+  __shared__ float red[33];
+  const int nchunks = D >> 3;
+  float dwacc[kMaxChunks][8];
+  float wv[kMaxChunks][8];
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
+    if (c < nchunks) Vec8<T>::load(w + c * 8, wv[i]);
+  }
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* xr = x + (long long)row * D;
+    const T* gr = dy + (long long)row * D;
+    const float rstd = rstd_in[row];
+    float xv[kMaxChunks][8], gv[kMaxChunks][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        Vec8<T>::load(xr + c * 8, xv[i]);
+        Vec8<T>::load(gr + c * 8, gv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          dwacc[i][j] += gv[i][j] * xv[i][j] * rstd;
+          gv[i][j] *= wv[i][j];
+          dot += gv[i][j] * xv[i][j];
+        }
+      }
+    }
+    dot = block_sum(dot, red);
+    const float coef = dot * rstd * rstd * rstd / (float)D;
+    T* dxr = dx + (long long)row * D;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = gv[i][j] * rstd - xv[i][j] * coef;
+        if (add_to_dx) {
+          float prev[8];
+          Vec8<T>::load(dxr + c * 8, prev);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += prev[j];
+        }
+        Vec8<T>::store(dxr + c * 8, o);
+      }
+    }
+  }
+  float* part = dw_partial + (long long)blockIdx.x * D;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+    if (c < nchunks) {
+      *reinterpret_cast<float4*>(part + c * 8) = make_float4(dwacc[i][0], dwacc[i][1], dwacc[i][2], dwacc[i][3]);
+      *reinterpret_cast<float4*>(part + c * 8 + 4) = make_float4(dwacc[i][4], dwacc[i][5], dwacc[i][6], dwacc[i][7]);
+    }
+  }
+}
+
+// out[c] (+)= sum_p partial[p][c]
+template <typename T>
+__global__ void colsum_partials_kernel(const float* __restrict__ partial, T* __restrict__ out,
+                                       int nparts, int D, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  float s = 0.f;
+  for (int p = 0; p < nparts; ++p) s += partial[(long long)p * D + c];
+  if (accumulate) s += to_f<T>(out[c]);
+  out[c] = from_f<T>(s);
+}
+
+// ------------------------------- LayerNorm ---------------------------------
+template <typename T>
+__global__ void layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w,
+                                     const T* __restrict__ b, T* __restrict__ y,
+                                     float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                     int rows, int D, float eps) {
+  __shared__ float red[33];
+  const int nchunks = D >> 3;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* xr = x + (long long)row * D;
+    float v[kMaxChunks][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        Vec8<T>::load(xr + c * 8, v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[i][j];
+      }
+    }
+    const float mean = block_sum(s, red) / (float)D;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; ss += d * d; }
+      }
+    }
+    const float rstd = rsqrtf(block_sum(ss, red) / (float)D + eps);
+    if (threadIdx.x == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    T* yr = y + (long long)row * D;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        float wv[8], bv[8], o[8];
+        Vec8<T>::load(w + c * 8, wv);
+        if (b) Vec8<T>::load(b + c * 8, bv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * wv[j] + (b ? bv[j] : 0.f);
+        Vec8<T>::store(yr + c * 8, o);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                     const T* __restrict__ w, const float* __restrict__ mean_in,
+                                     const float* __restrict__ rstd_in, T* __restrict__ dx,
+                                     float* __restrict__ dw_partial, float* __restrict__ db_partial,
+                                     int rows, int D) {
+  __shared__ float red[33];
+  const int nchunks = D >> 3;
+  float dwacc[kMaxChunks][8], dbacc[kMaxChunks][8], wv[kMaxChunks][8];
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dwacc[i][j] = 0.f; dbacc[i][j] = 0.f; }
+    if (c < nchunks) Vec8<T>::load(w + c * 8, wv[i]);
+  }
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* xr = x + (long long)row * D;
+    const T* gr = dy + (long long)row * D;
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float xh[kMaxChunks][8], gv[kMaxChunks][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        Vec8<T>::load(xr + c * 8, xh[i]);
+        Vec8<T>::load(gr + c * 8, gv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xh[i][j] - mean) * rstd;
+          dwacc[i][j] += gv[i][j] * xh[i][j];
+          dbacc[i][j] += gv[i][j];
+          gv[i][j] *= wv[i][j];
+          s1 += gv[i][j];
+          s2 += gv[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = block_sum(s1, red) / (float)D;
+    s2 = block_sum(s2, red) / (float)D;
+    T* dxr = dx + (long long)row * D;
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (gv[i][j] - s1 - xh[i][j] * s2);
+        Vec8<T>::store(dxr + c * 8, o);
+      }
+    }
+  }
+  float* pw = dw_partial + (long long)blockIdx.x * D;
+  float* pb = db_partial + (long long)blockIdx.x * D;
+#pragma unroll
+  for (int i = 0; i < kMaxChunks; ++i) {
+    const int c = threadIdx.x + i * blockDim.x;
+    if (c < nchunks) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { pw[c * 8 + j] = dwacc[i][j]; pb[c * 8 + j] = dbacc[i][j]; }
+    }
+  }
+}
+
+static int norm_threads(int D, int* threads) {
+  const int nchunks = D >> 3;
+  int t = 32;
+  while (t * kMaxChunks < nchunks && t < 256) t <<= 1;  // bwd kernels use ~200 regs: 256 threads max
+  if (t * kMaxChunks < nchunks || (D & 7)) {
+    b200_set_error("norm kernels need D %% 8 == 0 and D <= %d (got %d)", 256 * kMaxChunks * 8, D);
+    return B200_ERR_SHAPE;
+  }
+  if (t < 64) t = 64;
+  *threads = t;
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Number of per-CTA partial rows the backward kernels write into `scratch`
+// ([b200_norm_bwd_partials(rows), D] fp32 for RMSNorm, twice that for LayerNorm).
+B200_API int b200_norm_bwd_partials(int rows) {
+  int n = b200_sm_count() * 2;
+  return rows < n ? (rows < 1 ? 1 : rows) : n;
+}
+
+B200_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int rows, int D,
+                              float eps, int dtype, cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  const int grid = rows < b200_sm_count() * 8 ? rows : b200_sm_count() * 8;
+  B200_DISPATCH_DTYPE(dtype, T, (rmsnorm_fwd_kernel<T><<<grid, threads, 0, stream>>>(
+      (const T*)x, (const T*)w, (T*)y, rstd, rows, D, eps)));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// dx = d/dx, dw (+)= d/dw.  scratch: fp32 [b200_norm_bwd_partials(rows), D].
+B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                              void* dx, void* dw, float* scratch, int rows, int D, int add_to_dx,
+                              int accumulate_dw, int dtype, cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  const int grid = b200_norm_bwd_partials(rows);
+  B200_DISPATCH_DTYPE(dtype, T, {
+    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                        (T*)dx, scratch, rows, D, add_to_dx);
+    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
+                                                                    accumulate_dw);
+  });
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+B200_API int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,
+                                float* rstd, int rows, int D, float eps, int dtype,
+                                cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  const int grid = rows < b200_sm_count() * 8 ? rows : b200_sm_count() * 8;
+  B200_DISPATCH_DTYPE(dtype, T, (layernorm_fwd_kernel<T><<<grid, threads, 0, stream>>>(
+      (const T*)x, (const T*)w, (const T*)b, (T*)y, mean, rstd, rows, D, eps)));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// scratch: fp32 [2 * b200_norm_bwd_partials(rows), D]
+B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, const float* mean,
+                                const float* rstd, void* dx, void* dw, void* db, float* scratch,
+                                int rows, int D, int accumulate, int dtype, cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  const int grid = b200_norm_bwd_partials(rows);
+  float* pw = scratch;
+  float* pb = scratch + (long long)grid * D;
+  B200_DISPATCH_DTYPE(dtype, T, {
+    layernorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w,
+                                                          mean, rstd, (T*)dx, pw, pb, rows, D);
+    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(pw, (T*)dw, grid, D, accumulate);
+    if (db)
+      colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(pb, (T*)db, grid, D, accumulate);
+  });
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
