@@ -1,0 +1,36 @@
+// Shared declarations for the attention kernels (forward, backward, SIMT fallback).
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+// Q/K/V/O are addressed as [B, S, H, hd] with arbitrary (16-byte aligned) batch/seq/head
+// strides and unit stride on hd, so the kernels read straight out of a fused QKV GEMM
+// output and write the layout the output projection consumes: no transposes.
+struct AttnParams {
+  int B, H, Hkv, Sq, Sk, hd;
+  long long q_sb, q_ss, q_sh;      // element strides: batch, seq, head
+  long long k_sb, k_ss, k_sh;
+  long long v_sb, v_ss, v_sh;
+  long long o_sb, o_ss, o_sh;
+  float scale;                     // softmax scale (1/sqrt(hd))
+  int causal;
+  int q_offset, k_offset;          // global positions of row 0 / key 0 (ring attention chunks)
+  void* O;                         // bf16 [B, Sq, H, hd] (strided)
+  float* LSE;                      // fp32 [B, H, Sq]
+};
+
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+// 4-D tensor map over a [B, S, H, hd] bf16 tensor: dims {hd, S, H, B}, box {64, rows, 1, 1},
+// 128-byte swizzle.  One box = `rows` sequence positions x 64 head-dim elements.
+inline int make_attn_tmap(CUtensorMap* out, const void* base, int B, int S, int H, int hd,
+                          long long sb, long long ss, long long sh, int box_rows) {
+  const uint64_t dims[4] = {(uint64_t)hd, (uint64_t)S, (uint64_t)H, (uint64_t)B};
+  const uint64_t strides[3] = {(uint64_t)ss * 2, (uint64_t)sh * 2, (uint64_t)sb * 2};
+  const uint32_t box[4] = {64u, (uint32_t)box_rows, 1u, 1u};
+  return b200_make_tmap(out, base, 2, 4, dims, strides, box, 1);
+}
+
+}  // namespace b200

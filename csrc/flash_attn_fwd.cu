@@ -1,0 +1,337 @@
+// Flash-attention forward on tcgen05: S = Q K^T and O += P V both run on the 5th-gen
+// tensor cores with S/P and O resident in TMEM; K/V tiles stream through a TMA ring.
+//   warp 0   : TMA loader (Q once, K/V double-buffered)
+//   warp 1   : MMA issuer  (QK^T for block j+1 is issued before PV of block j, so the
+//              tensor cores work on the next scores while softmax handles the current ones)
+//   warp 2-5 : softmax, one thread per query row (TMEM lane == row: no shuffles), writes P
+//              as packed bf16 back INTO the S columns (TS-MMA reads A from TMEM), and rescales
+//              O lazily (only when the running max moves by more than 2^8).
+// Returns O (bf16) and LSE (fp32); q_offset/k_offset let ring-attention call it on chunks.
+//
+// Replaces F.scaled_dot_product_attention(q, k, v, is_causal=True)
+//   (/root/reference/fsdp_tp/llama2_model.py:218-223) and the explicit softmax(QK^T)V of
+//   /root/reference/scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122.
+#include "attn_common.cuh"
+
+namespace b200 {
+
+constexpr int kFaThreads = 192;
+constexpr int kFaBlock = 128;  // query rows per CTA == keys per KV block
+
+template <int HD>
+struct FaCfg {
+  static constexpr int kHalves = HD / 64;
+  static constexpr int kTileBytes = kFaBlock * HD * 2;
+  static constexpr int kSmemBytes = 5 * kTileBytes + 1024 + 256;  // Q + 2 K + 2 V
+};
+
+template <int HD>
+__global__ void __launch_bounds__(kFaThreads, 1)
+flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
+                      const __grid_constant__ CUtensorMap tmap_k,
+                      const __grid_constant__ CUtensorMap tmap_v, const AttnParams p) {
+  using Cfg = FaCfg<HD>;
+  constexpr int kTile = Cfg::kTileBytes;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = smem_base;
+  auto sK = [&](int s) { return smem_base + kTile * (1 + s); };
+  auto sV = [&](int s) { return smem_base + kTile * (3 + s); };
+  const uint32_t bar = smem_base + 5 * kTile;
+  const uint32_t q_full = bar;
+  auto k_full = [&](int s) { return bar + 8u * (1 + s); };
+  auto k_empty = [&](int s) { return bar + 8u * (3 + s); };
+  auto v_full = [&](int s) { return bar + 8u * (5 + s); };
+  auto v_empty = [&](int s) { return bar + 8u * (7 + s); };
+  auto s_full = [&](int s) { return bar + 8u * (9 + s); };
+  auto p_ready = [&](int s) { return bar + 8u * (11 + s); };
+  auto pv_done = [&](int s) { return bar + 8u * (13 + s); };
+  const uint32_t tmem_ptr_addr = bar + 8u * 15;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int hk = h / (p.H / p.Hkv);
+  const int q0 = q_blk * kFaBlock;
+
+  // number of KV blocks this query block attends to
+  int kv_limit = p.Sk;
+  if (p.causal) {
+    const int lim = q0 + kFaBlock - 1 + p.q_offset - p.k_offset + 1;
+    kv_limit = lim < kv_limit ? lim : kv_limit;
+  }
+  const int n_blocks = kv_limit > 0 ? (kv_limit + kFaBlock - 1) / kFaBlock : 0;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_q);
+    tma_prefetch_desc(&tmap_k);
+    tma_prefetch_desc(&tmap_v);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1);
+      mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1);
+      mbar_init(s_full(s), 1); mbar_init(p_ready(s), 4); mbar_init(pv_done(s), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc<1>(tmem_ptr_addr, 512);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_addr));
+  const uint32_t tO = tmem_base + 256;
+
+  if (warp == 0) {
+    if (lane == 0 && n_blocks > 0) {
+      // ===================== loader =====================
+      mbar_expect_tx(q_full, kTile);
+#pragma unroll
+      for (int hh = 0; hh < Cfg::kHalves; ++hh)
+        tma_load_4d(sQ + hh * 16384, &tmap_q, q_full, hh * 64, q0, h, b, kEvictFirst);
+      for (int j = 0; j < n_blocks; ++j) {
+        const int st = j & 1;
+        const uint32_t par = ((j >> 1) & 1) ^ 1u;
+        const int kv0 = j * kFaBlock;
+        mbar_wait(k_empty(st), par);
+        mbar_expect_tx(k_full(st), kTile);
+#pragma unroll
+        for (int hh = 0; hh < Cfg::kHalves; ++hh)
+          tma_load_4d(sK(st) + hh * 16384, &tmap_k, k_full(st), hh * 64, kv0, hk, b, kEvictLast);
+        mbar_wait(v_empty(st), par);
+        mbar_expect_tx(v_full(st), kTile);
+#pragma unroll
+        for (int hh = 0; hh < Cfg::kHalves; ++hh)
+          tma_load_4d(sV(st) + hh * 16384, &tmap_v, v_full(st), hh * 64, kv0, hk, b, kEvictLast);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0 && n_blocks > 0) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, false, false);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, HD, false, true);
+      auto issue_qk = [&](int j) {
+        const int st = j & 1;
+        mbar_wait(k_full(st), (j >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
+          umma_f16_ss<1>(tmem_base + st * 128, umma_smem_desc_sw128(sQ + off, 16, 1024),
+                         umma_smem_desc_sw128(sK(st) + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(s_full(st));
+        umma_commit(k_empty(st));
+      };
+      mbar_wait(q_full, 0);
+      issue_qk(0);
+      for (int j = 0; j < n_blocks; ++j) {
+        const int st = j & 1;
+        if (j + 1 < n_blocks) issue_qk(j + 1);
+        mbar_wait(p_ready(st), (j >> 1) & 1);
+        mbar_wait(v_full(st), (j >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < kFaBlock / 16; ++kk) {
+          umma_f16_ts<1>(tO, tmem_base + st * 128 + kk * 8,
+                         umma_smem_desc_sw128(sV(st) + kk * 2048, 16384, 1024), idesc_pv,
+                         (j > 0 || kk > 0) ? 1u : 0u);
+        }
+        umma_commit(v_empty(st));
+        umma_commit(pv_done(st));
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== softmax / correction / epilogue =====================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int q_idx = q0 + row;
+    const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
+    const float sl2 = p.scale * kLog2e;
+    float m_used = -INFINITY;  // max used for scaling (raw score units)
+    float l_run = 0.f;
+    const int q_pos = q_idx + p.q_offset - p.k_offset;  // key j visible iff j <= q_pos (causal)
+
+    for (int j = 0; j < n_blocks; ++j) {
+      const int st = j & 1;
+      const int kv0 = j * kFaBlock;
+      const bool need_mask = (kv0 + kFaBlock > p.Sk) ||
+                             (p.causal && (kv0 + kFaBlock - 1 > q0 + p.q_offset - p.k_offset));
+      mbar_wait(s_full(st), (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tS = tmem_base + lane_off + st * 128;
+      // ---- pass 1: block row max ----
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + c * 32, r);
+        tmem_ld_wait();
+        if (need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int col = kv0 + c * 32 + i;
+            const bool ok = col < p.Sk && (!p.causal || col <= q_pos);
+            mx = fmaxf(mx, ok ? __uint_as_float(r[i]) : -INFINITY);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        }
+      }
+      // ---- lazy rescale decision ----
+      float alpha = 1.f;
+      bool rescale = false;
+      if (mx > m_used && (m_used == -INFINITY || (mx - m_used) * sl2 > 8.f)) {
+        alpha = (m_used == -INFINITY) ? 0.f : exp2f((m_used - mx) * sl2);
+        m_used = mx;
+        rescale = true;
+      }
+      l_run *= alpha;
+      if (j > 0 && __any_sync(0xffffffffu, rescale)) {
+        const int pj = j - 1;
+        mbar_wait(pv_done(pj & 1), (pj >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < HD / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tO + lane_off + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st_32x32(tO + lane_off + c * 32, r);
+        }
+        tmem_st_wait();
+      }
+      // ---- pass 2: P = exp2((S - m) * scale), row sum, packed bf16 back into the S columns ----
+      const float mneg = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
+      float lsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + c * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
+          float p0 = exp2f(fmaf(s0, sl2, mneg)), p1 = exp2f(fmaf(s1, sl2, mneg));
+          if (need_mask) {
+            const int col = kv0 + c * 32 + i;
+            if (!(col < p.Sk && (!p.causal || col <= q_pos))) p0 = 0.f;
+            if (!(col + 1 < p.Sk && (!p.causal || col + 1 <= q_pos))) p1 = 0.f;
+          }
+          lsum += p0 + p1;
+          pk[i >> 1] = pack_bf16(p0, p1);
+        }
+        tmem_st_32x16(tS + c * 16, pk);
+      }
+      l_run += lsum;
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_ready(st));
+    }
+
+    // ---- epilogue: O / l -> bf16 global, LSE ----
+    __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.O) + (long long)b * p.o_sb +
+                          (long long)q_idx * p.o_ss + (long long)h * p.o_sh;
+    if (n_blocks > 0) {
+      const int lj = n_blocks - 1;
+      mbar_wait(pv_done(lj & 1), (lj >> 1) & 1);
+      tc_fence_after();
+      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+#pragma unroll 1
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, r);
+        tmem_ld_wait();
+        if (q_idx < p.Sq) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 o;
+            o.x = pack_bf16(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+            o.y = pack_bf16(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+            o.z = pack_bf16(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+            o.w = pack_bf16(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+            st_v4(orow + c * 32 + g * 8, o);
+          }
+        }
+      }
+    } else if (q_idx < p.Sq) {
+      for (int c = 0; c < HD / 8; ++c) st_v4(orow + c * 8, make_uint4(0, 0, 0, 0));
+    }
+    if (q_idx < p.Sq && p.LSE)
+      p.LSE[((long long)b * p.H + h) * p.Sq + q_idx] =
+          (l_run > 0.f) ? m_used * p.scale + __logf(l_run) : -INFINITY;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+template <int HD>
+static int launch_fa_fwd(const void* Q, const void* K, const void* V, const AttnParams& p,
+                         cudaStream_t stream) {
+  using Cfg = FaCfg<HD>;
+  CUtensorMap tq, tk, tv;
+  if (int rc = make_attn_tmap(&tq, Q, p.B, p.Sq, p.H, HD, p.q_sb, p.q_ss, p.q_sh, kFaBlock)) return rc;
+  if (int rc = make_attn_tmap(&tk, K, p.B, p.Sk, p.Hkv, HD, p.k_sb, p.k_ss, p.k_sh, kFaBlock)) return rc;
+  if (int rc = make_attn_tmap(&tv, V, p.B, p.Sk, p.Hkv, HD, p.v_sb, p.v_ss, p.v_sh, kFaBlock)) return rc;
+  auto kern = flash_attn_fwd_kernel<HD>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(p.Sq, kFaBlock), p.H, p.B);
+  kern<<<grid, kFaThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+static bool al16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
+
+// Strides are in elements.  Supported on the tensor-core path: hd in {64, 128}, bf16,
+// all strides multiples of 8.  Returns B200_ERR_SHAPE otherwise (callers use b200_attn_simt_*).
+B200_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, void* O, float* LSE,
+                                 int B, int H, int Hkv, int Sq, int Sk, int hd,
+                                 long long q_sb, long long q_ss, long long q_sh,
+                                 long long k_sb, long long k_ss, long long k_sh,
+                                 long long v_sb, long long v_ss, long long v_sh,
+                                 long long o_sb, long long o_ss, long long o_sh,
+                                 float scale, int causal, int q_offset, int k_offset,
+                                 cudaStream_t stream) {
+  if (B <= 0 || H <= 0 || Sq <= 0) return B200_OK;
+  AttnParams p = {};
+  p.B = B; p.H = H; p.Hkv = Hkv; p.Sq = Sq; p.Sk = Sk; p.hd = hd;
+  p.q_sb = q_sb; p.q_ss = q_ss; p.q_sh = q_sh;
+  p.k_sb = k_sb; p.k_ss = k_ss; p.k_sh = k_sh;
+  p.v_sb = v_sb; p.v_ss = v_ss; p.v_sh = v_sh;
+  p.o_sb = o_sb; p.o_ss = o_ss; p.o_sh = o_sh;
+  p.scale = scale; p.causal = causal; p.q_offset = q_offset; p.k_offset = k_offset;
+  p.O = O; p.LSE = LSE;
+  const bool ok = (hd == 64 || hd == 128) && al16(Q) && al16(K) && al16(V) && al16(O) &&
+                  !((q_sb | q_ss | q_sh | k_sb | k_ss | k_sh | v_sb | v_ss | v_sh | o_sb | o_ss | o_sh) & 7) &&
+                  Hkv > 0 && H % Hkv == 0 && Sk > 0;
+  if (!ok) {
+    b200_set_error("flash_attn_fwd: unsupported shape/stride (hd=%d H=%d Hkv=%d)", hd, H, Hkv);
+    return B200_ERR_SHAPE;
+  }
+  if (hd == 128) return launch_fa_fwd<128>(Q, K, V, p, stream);
+  return launch_fa_fwd<64>(Q, K, V, p, stream);
+}

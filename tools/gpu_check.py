@@ -148,6 +148,12 @@ GROUPS = {
     "gemm_k3": lambda r: group_gemm(3, r),
     "simt": group_simt,
 }
+try:
+    from tools import gpu_check_more as _more
+
+    GROUPS.update(_more.GROUPS)
+except ImportError:
+    pass
 
 
 def run_group(name: str) -> int:
@@ -181,10 +187,6 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1].startswith("--only="):
         names = sys.argv[1][7:].split(",")
     extra = []
-    try:
-        from tools import gpu_check_more  # noqa: F401  (registers additional groups)
-    except Exception:
-        pass
     summary = {}
     for n in names + extra:
         log = OUT / f"check_{n}.log"

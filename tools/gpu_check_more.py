@@ -1,0 +1,240 @@
+"""Additional bring-up groups: memory-bound ops, optimizers, attention."""
+from __future__ import annotations
+
+import math
+
+
+def _h():
+    from tools.gpu_check import _check, _time
+    return _check, _time
+
+
+def group_norms(results):
+    import torch
+    import torch.nn.functional as F
+    from b200dist.ops import native as N
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(1)
+    for dt, tol in ((torch.bfloat16, 3e-2), (torch.float32, 1e-4)):
+        for rows, D in ((64, 256), (300, 4096), (33, 5120), (17, 64)):
+            x = torch.randn(rows, D, device=dev).to(dt)
+            w = (1 + 0.1 * torch.randn(D, device=dev)).to(dt)
+            b = (0.1 * torch.randn(D, device=dev)).to(dt)
+            dy = torch.randn(rows, D, device=dev).to(dt)
+            xr = x.float().requires_grad_(True); wr = w.float().requires_grad_(True); br = b.float().requires_grad_(True)
+            # RMSNorm (reference expression)
+            yr = (xr * torch.rsqrt(xr.pow(2).mean(-1, keepdim=True) + 1e-5)) * wr
+            yr.backward(dy.float())
+            y, rstd = N.rmsnorm_fwd(x, w, 1e-5)
+            dx, dw = N.rmsnorm_bwd(dy, x, w, rstd)
+            _check(f"rmsnorm fwd {dt} {rows}x{D}", y, yr, tol, tol, results)
+            _check(f"rmsnorm dx {dt} {rows}x{D}", dx, xr.grad, tol, tol, results)
+            _check(f"rmsnorm dw {dt} {rows}x{D}", dw, wr.grad, tol * math.sqrt(rows), tol, results)
+            xr.grad = None; wr.grad = None
+            yl = F.layer_norm(xr, (D,), wr, br, 1e-5)
+            yl.backward(dy.float())
+            y, mean, rs = N.layernorm_fwd(x, w, b, 1e-5)
+            dx, dw, db = N.layernorm_bwd(dy, x, w, mean, rs)
+            _check(f"layernorm fwd {dt} {rows}x{D}", y, yl, tol, tol, results)
+            _check(f"layernorm dx {dt} {rows}x{D}", dx, xr.grad, tol, tol, results)
+            _check(f"layernorm dw {dt} {rows}x{D}", dw, wr.grad, tol * math.sqrt(rows), tol, results)
+            _check(f"layernorm db {dt} {rows}x{D}", db, br.grad, tol * math.sqrt(rows), tol, results)
+    x = torch.randn(8192, 4096, device=dev).bfloat16(); w = torch.ones(4096, device=dev).bfloat16()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ms = _time(lambda: N.rmsnorm_fwd(x, w, 1e-5), flush=flush)
+    print(f"[TIME] rmsnorm_fwd 8192x4096 bf16: {ms*1e3:.1f} us  {2*x.numel()*2/ms/1e6:.0f} GB/s", flush=True)
+    y, rstd = N.rmsnorm_fwd(x, w, 1e-5)
+    ms = _time(lambda: N.rmsnorm_bwd(x, x, w, rstd), flush=flush)
+    print(f"[TIME] rmsnorm_bwd 8192x4096 bf16: {ms*1e3:.1f} us  {3*x.numel()*2/ms/1e6:.0f} GB/s", flush=True)
+
+
+def group_elementwise(results):
+    import torch
+    import torch.nn.functional as F
+    from b200dist.ops import native as N
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(2)
+    # RoPE vs the reference complex formulation
+    B, S, H, hd = 2, 96, 4, 128
+    freqs = 1.0 / (10000.0 ** (torch.arange(0, hd, 2, device=dev)[: hd // 2].float() / hd))
+    t = torch.arange(256, device=dev).float()
+    fc = torch.polar(torch.ones(256, hd // 2, device=dev), torch.outer(t, freqs))
+    fr = torch.view_as_real(fc).contiguous()
+    for dt, tol in ((torch.bfloat16, 2e-2), (torch.float32, 1e-5)):
+        x = torch.randn(B, S, H, hd, device=dev).to(dt)
+        xc = torch.view_as_complex(x.float().reshape(B, S, H, hd // 2, 2))
+        ref = torch.view_as_real(xc * fc[5:5 + S].view(1, S, 1, hd // 2)).flatten(3)
+        _check(f"rope fwd {dt}", N.rope(x, fr, pos_offset=5), ref, tol, tol, results)
+        refb = torch.view_as_real(xc * fc[5:5 + S].conj().view(1, S, 1, hd // 2)).flatten(3)
+        _check(f"rope bwd {dt}", N.rope(x, fr, pos_offset=5, backward=True), refb, tol, tol, results)
+        a = torch.randn(100, 512, device=dev).to(dt); b = torch.randn(100, 512, device=dev).to(dt)
+        g = torch.randn(100, 512, device=dev).to(dt)
+        ar = a.float().requires_grad_(True); br = b.float().requires_grad_(True)
+        yr = F.silu(ar) * br
+        yr.backward(g.float())
+        _check(f"swiglu fwd {dt}", N.swiglu_fwd(a, b), yr, tol, tol, results)
+        da, db = N.swiglu_bwd(g, a, b)
+        _check(f"swiglu da {dt}", da, ar.grad, tol * 2, tol, results)
+        _check(f"swiglu db {dt}", db, br.grad, tol * 2, tol, results)
+        # fused layout: a|b halves of one [M, 2F] buffer
+        ab = torch.cat([a, b], dim=1)
+        _check(f"swiglu fwd strided {dt}", N.swiglu_fwd(ab[:, :512], ab[:, 512:]), yr, tol, tol, results)
+        x1 = torch.randn(1003, device=dev).to(dt); x2 = torch.randn(1003, device=dev).to(dt)
+        xr = x1.float().requires_grad_(True)
+        F.gelu(xr).backward(x2.float())
+        _check(f"gelu {dt}", N.elementwise("gelu", x1), F.gelu(x1.float()), tol, tol, results)
+        _check(f"gelu_bwd {dt}", N.elementwise("gelu_bwd", x1, x2), xr.grad, tol, tol, results)
+        _check(f"relu_bwd {dt}", N.elementwise("relu_bwd", x1, x2), (x1 > 0).float() * x2.float(), tol, tol, results)
+        _check(f"add {dt}", N.elementwise("add", x1, x2), x1.float() + x2.float(), tol, tol, results)
+        _check(f"axpy {dt}", N.elementwise("axpy", x1, x2, alpha=0.5), x1.float() + 0.5 * x2.float(), tol, tol, results)
+    xf = torch.randn(4099, device=dev)
+    _check("cast f32->bf16 scale", N.cast_scale(xf, torch.bfloat16, 0.25), xf * 0.25, 1e-2, 1e-2, results)
+    _check("cast bf16->f32", N.cast_scale(xf.bfloat16(), torch.float32, 2.0), xf.bfloat16().float() * 2, 1e-6, 1e-6, results)
+    # embedding
+    V, D = 1000, 256
+    for dt in (torch.bfloat16, torch.float32):
+        w = torch.randn(V, D, device=dev).to(dt)
+        idx = torch.randint(0, V, (4, 77), device=dev)
+        _check(f"embedding fwd {dt}", N.embedding_fwd(idx, w), w[idx], 0, 0, results)
+        half = N.embedding_fwd(idx, w[500:], vocab_start=500)
+        ref = torch.where((idx >= 500).unsqueeze(-1), w[idx], torch.zeros_like(w[idx]))
+        _check(f"embedding fwd vocab-parallel {dt}", half, ref, 0, 0, results)
+        dy = torch.randn(4, 77, D, device=dev).to(dt)
+        dw = N.embedding_bwd(idx, dy, V)
+        ref = torch.zeros(V, D, device=dev).index_add_(0, idx.reshape(-1), dy.reshape(-1, D).float())
+        _check(f"embedding bwd {dt}", dw, ref, 1e-3, 1e-3, results)
+    # cross entropy
+    for dt, tol in ((torch.float32, 1e-4), (torch.bfloat16, 2e-2)):
+        for rows, V in ((64, 32000), (33, 1000), (16, 10)):
+            lg = (torch.randn(rows, V, device=dev) * 3).to(dt)
+            tg = torch.randint(0, V, (rows,), device=dev)
+            tg[0] = -100
+            lr = lg.float().requires_grad_(True)
+            ref = F.cross_entropy(lr, tg, ignore_index=-100, reduction="none")
+            loss, lse = N.xent_fwd(lg, tg)
+            _check(f"xent fwd {dt} {rows}x{V}", loss, ref, tol, tol, results)
+            ref.sum().backward()
+            gs = torch.ones(1, device=dev)
+            _check(f"xent bwd {dt} {rows}x{V}", N.xent_bwd(lg, tg, lse, gs), lr.grad, tol, tol, results)
+    lg = torch.randn(8192, 32000, device=dev); tg = torch.randint(0, 32000, (8192,), device=dev)
+    ms = _time(lambda: N.xent_fwd(lg, tg))
+    print(f"[TIME] xent_fwd 8192x32000 fp32: {ms:.3f} ms {lg.numel()*4*2/ms/1e6:.0f} GB/s (2 reads)", flush=True)
+    # optimizers vs torch
+    for pdt, gdt in ((torch.float32, torch.float32), (torch.float32, torch.bfloat16)):
+        n = 10007
+        p0 = torch.randn(n, device=dev); g = torch.randn(n, device=dev).to(gdt)
+        pr = p0.clone().requires_grad_(True)
+        opt = torch.optim.AdamW([pr], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+        p = p0.clone(); m = torch.zeros(n, device=dev); v = torch.zeros(n, device=dev)
+        lowp = torch.empty(n, device=dev, dtype=torch.bfloat16)
+        for step in (1, 2, 3):
+            pr.grad = g.float().clone(); opt.step()
+            N.adamw_step(p, g, m, v, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8, wd=0.1, step=step, p_lowp=lowp)
+        _check(f"adamw p={pdt} g={gdt}", p, pr.detach(), 1e-5, 1e-5, results)
+        _check(f"adamw lowp copy g={gdt}", lowp, pr.detach(), 1e-2, 1e-2, results)
+        pr = p0.clone().requires_grad_(True)
+        opt = torch.optim.SGD([pr], lr=0.1, momentum=0.9, weight_decay=1e-5)
+        p = p0.clone(); buf = torch.zeros(n, device=dev)
+        for step in (1, 2, 3):
+            pr.grad = g.float().clone(); opt.step()
+            N.sgd_step(p, g, buf, lr=0.1, momentum=0.9, wd=1e-5, first_step=(step == 1))
+        _check(f"sgd p={pdt} g={gdt}", p, pr.detach(), 1e-5, 1e-5, results)
+    n = 64 << 20
+    p = torch.randn(n, device=dev); g = torch.randn(n, device=dev).bfloat16(); m = torch.zeros(n, device=dev); v = torch.zeros(n, device=dev)
+    lowp = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    ms = _time(lambda: N.adamw_step(p, g, m, v, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, wd=0.1, step=5, p_lowp=lowp))
+    print(f"[TIME] adamw 64Mi params: {ms:.3f} ms {n*(4*3*2+2+2)/ms/1e6:.0f} GB/s", flush=True)
+
+
+def _attn_ref(q, k, v, causal, q_off=0, k_off=0):
+    import torch
+    B, Sq, H, hd = q.shape
+    Hkv = k.shape[2]
+    qf, kf, vf = q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2)
+    if Hkv != H:
+        kf = kf.repeat_interleave(H // Hkv, dim=1); vf = vf.repeat_interleave(H // Hkv, dim=1)
+    s = qf @ kf.transpose(-1, -2) * (hd ** -0.5)
+    if causal:
+        qi = torch.arange(Sq, device=q.device).view(-1, 1) + q_off
+        ki = torch.arange(k.shape[1], device=q.device).view(1, -1) + k_off
+        s = s.masked_fill(ki > qi, float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    p = torch.nan_to_num(p, nan=0.0)
+    return (p @ vf).transpose(1, 2), torch.logsumexp(s, dim=-1)
+
+
+def group_attn_fwd(results):
+    import torch
+    from b200dist.ops import native as N
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(3)
+    cases = [(1, 128, 128, 1, 1, 128, False), (1, 128, 128, 1, 1, 128, True), (2, 256, 256, 4, 4, 128, True),
+             (2, 200, 200, 4, 2, 128, True), (1, 384, 640, 2, 2, 64, False), (2, 320, 320, 4, 4, 64, True),
+             (1, 1024, 1024, 8, 8, 128, True)]
+    for (B, Sq, Sk, H, Hkv, hd, causal) in cases:
+        q = torch.randn(B, Sq, H, hd, device=dev).bfloat16()
+        k = torch.randn(B, Sk, Hkv, hd, device=dev).bfloat16()
+        v = torch.randn(B, Sk, Hkv, hd, device=dev).bfloat16()
+        o, lse = N.flash_attn_fwd(q, k, v, causal=causal)
+        torch.cuda.synchronize()
+        ro, rl = _attn_ref(q, k, v, causal)
+        tag = f"B{B} Sq{Sq} Sk{Sk} H{H}/{Hkv} hd{hd} causal={causal}"
+        _check(f"attn fwd O {tag}", o, ro, 2e-2, 2e-2, results)
+        _check(f"attn fwd LSE {tag}", lse, rl, 2e-2, 1e-2, results)
+    # fused-QKV strided input and chunk offsets (ring-attention interface)
+    B, S, H, hd = 2, 256, 4, 128
+    qkv = torch.randn(B, S, 3 * H * hd, device=dev).bfloat16()
+    q, k, v = [t.view(B, S, H, hd) for t in qkv.split(H * hd, dim=-1)]
+    o, lse = N.flash_attn_fwd(q, k, v, causal=True)
+    ro, rl = _attn_ref(q, k, v, True)
+    _check("attn fwd strided qkv", o, ro, 2e-2, 2e-2, results)
+    o2, lse2 = N.flash_attn_fwd(q[:, 128:], k[:, :128], v[:, :128], causal=True, q_offset=128, k_offset=0)
+    ro2, rl2 = _attn_ref(q[:, 128:], k[:, :128], v[:, :128], True, 128, 0)
+    _check("attn fwd chunk offsets", o2, ro2, 2e-2, 2e-2, results)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for (B, S, H, hd) in ((2, 4096, 32, 128), (1, 8192, 32, 128)):
+        q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q)
+        ms = _time(lambda: N.flash_attn_fwd(q, k, v, causal=True), flush=flush)
+        fl = 4.0 * B * H * S * S * hd / 2
+        qt, kt, vt = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+        ms_ref = _time(lambda: torch.nn.functional.scaled_dot_product_attention(qt, kt, vt, is_causal=True), flush=flush)
+        print(f"[TIME] attn fwd causal B{B} S{S} H{H} hd{hd}: {ms:.3f} ms {fl/ms/1e9:.0f} TFLOP/s | SDPA {ms_ref:.3f} ms {fl/ms_ref/1e9:.0f} TFLOP/s", flush=True)
+
+
+def group_attn_bwd(results):
+    import torch
+    from b200dist.ops import native as N
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(4)
+    cases = [(1, 128, 128, 1, 1, 128, False), (1, 128, 128, 1, 1, 128, True), (2, 256, 256, 4, 4, 128, True),
+             (2, 200, 200, 4, 2, 128, True), (1, 384, 640, 2, 2, 64, False), (2, 320, 320, 4, 4, 64, True)]
+    for (B, Sq, Sk, H, Hkv, hd, causal) in cases:
+        q = torch.randn(B, Sq, H, hd, device=dev).bfloat16()
+        k = torch.randn(B, Sk, Hkv, hd, device=dev).bfloat16()
+        v = torch.randn(B, Sk, Hkv, hd, device=dev).bfloat16()
+        do = torch.randn(B, Sq, H, hd, device=dev).bfloat16()
+        qr, kr, vr = [t.float().requires_grad_(True) for t in (q, k, v)]
+        ro, _ = _attn_ref(qr, kr, vr, causal)
+        ro.backward(do.float())
+        o, lse = N.flash_attn_fwd(q, k, v, causal=causal)
+        dq, dk, dv = N.flash_attn_bwd(q, k, v, o, do, lse, causal=causal)
+        torch.cuda.synchronize()
+        tag = f"B{B} Sq{Sq} Sk{Sk} H{H}/{Hkv} hd{hd} causal={causal}"
+        _check(f"attn bwd dQ {tag}", dq, qr.grad, 5e-2, 3e-2, results)
+        _check(f"attn bwd dK {tag}", dk, kr.grad, 5e-2, 3e-2, results)
+        _check(f"attn bwd dV {tag}", dv, vr.grad, 5e-2, 3e-2, results)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    B, S, H, hd = 2, 4096, 32, 128
+    q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q); do = torch.randn_like(q)
+    o, lse = N.flash_attn_fwd(q, k, v, causal=True)
+    ms = _time(lambda: N.flash_attn_bwd(q, k, v, o, do, lse, causal=True), flush=flush)
+    fl = 2.5 * 4.0 * B * H * S * S * hd / 2
+    print(f"[TIME] attn bwd causal B{B} S{S} H{H} hd{hd}: {ms:.3f} ms {fl/ms/1e9:.0f} TFLOP/s (5-GEMM flops)", flush=True)
+
+
+GROUPS = {"norms": group_norms, "elementwise": group_elementwise, "attn_fwd": group_attn_fwd,
+          "attn_bwd": group_attn_bwd}
