@@ -1,0 +1,70 @@
+"""Training-step engine: the public call a user makes to run one optimizer step.
+
+``Trainer.train_step(inputs, targets)`` does zero_grad → forward → loss → backward → (gradient
+sync by the parallel wrapper) → optimizer step on device tensors; ``train_step_host`` is the
+end-to-end variant that also stages the batch from pinned host memory on a copy stream and
+returns the loss as a Python float (one D2H read), which is what ``bench.py`` reports as ``e2e``.
+
+The hot loop of the reference recipes (e.g. /root/reference/scripts/main.py:334-339,
+scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:171-180) has exactly this shape.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import torch
+
+from . import ops
+
+
+def lm_loss(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+    return ops.cross_entropy(logits, targets)
+
+
+class Trainer:
+    def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer,
+                 loss_fn: Callable[[torch.Tensor, torch.Tensor], torch.Tensor] = lm_loss,
+                 device: Optional[torch.device] = None):
+        self.model, self.optimizer, self.loss_fn = model, optimizer, loss_fn
+        self.device = device or next(model.parameters()).device
+        self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._staged = None
+        self.steps_done = 0
+
+    # ---------------------------------------------------------------- device-resident step
+    def train_step(self, inputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        self.optimizer.zero_grad(set_to_none=True)
+        out = self.model(inputs)
+        loss = self.loss_fn(out, targets)
+        loss.backward()
+        finish = getattr(self.model, "finish_backward", None)
+        if callable(finish):
+            finish()  # parallel wrappers: wait for gradient collectives issued from hooks
+        self.optimizer.step()
+        self.steps_done += 1
+        return loss.detach()
+
+    # ---------------------------------------------------------------- host -> device -> host step
+    def stage(self, inputs_host: torch.Tensor, targets_host: torch.Tensor):
+        """Start the H2D copy of the next batch on the copy stream (inputs must be pinned)."""
+        if self._copy_stream is None:
+            self._staged = (inputs_host, targets_host, None)
+            return
+        with torch.cuda.stream(self._copy_stream):
+            x = inputs_host.to(self.device, non_blocking=True)
+            y = targets_host.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        self._staged = (x, y, ev)
+
+    def train_step_host(self, inputs_host: torch.Tensor, targets_host: torch.Tensor) -> float:
+        if self._staged is None:
+            self.stage(inputs_host, targets_host)
+        x, y, ev = self._staged
+        self._staged = None
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            x.record_stream(torch.cuda.current_stream(self.device))
+            y.record_stream(torch.cuda.current_stream(self.device))
+        loss = self.train_step(x, y)
+        return float(loss.item())  # D2H read of the step result

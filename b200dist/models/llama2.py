@@ -1,0 +1,248 @@
+"""Llama-2 decoder, state-dict compatible with the reference model
+(/root/reference/fsdp_tp/llama2_model.py, byte-identical copy under scripts/06_hybrid_parallelism/).
+
+Same ``ModelArgs`` fields and defaults (:12-27), same parameter names
+(``tok_embeddings.weight``, ``layers.{i}.attention.{wq,wk,wv,wo}.weight``,
+``layers.{i}.feed_forward.{w1,w2,w3}.weight``, ``layers.{i}.{attention_norm,ffn_norm}.weight``,
+``norm.weight``, ``output.weight``) and the persistent complex64 ``freqs_cis`` buffer (:375-383), same
+initialisation (:185-188,269-272,316-319,414-426), same forward contract
+(``forward(tokens) -> fp32 logits``, :439-448).
+
+What differs is the execution: every op is a hand-written sm_100a kernel from ``b200dist.ops``
+(tcgen05 GEMMs with the residual add fused into the wo / w2 epilogues, flash attention reading
+the [B,S,H,hd] projections in place, fused RMSNorm / RoPE / SwiGLU), and activations stay in
+the [B,S,H,hd] layout end to end — there is no transpose(1,2) and no repeat_kv copy (GQA is
+handled by kernel indexing, reference :103-112,215-216).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+from torch import nn
+
+from .. import ops
+
+
+@dataclass
+class ModelArgs:
+    dim: int = 4096
+    n_layers: int = 32
+    n_heads: int = 32
+    n_kv_heads: Optional[int] = None
+    vocab_size: int = -1
+    multiple_of: int = 256
+    ffn_dim_multiplier: Optional[float] = None
+    norm_eps: float = 1e-5
+    max_batch_size: int = 32
+    max_seq_len: int = 32768
+    depth_init: bool = True
+
+
+PRESETS = {
+    # reference toy config: 01_fsdp_tp_hybrid.py:102
+    "llama2-toy": dict(dim=256, n_layers=2, n_heads=16, vocab_size=32000),
+    "llama2-tiny": dict(dim=512, n_layers=4, n_heads=8, vocab_size=32000, max_seq_len=4096),
+    "llama2-1b": dict(dim=2048, n_layers=16, n_heads=16, vocab_size=32000, max_seq_len=8192),
+    "llama2-7b": dict(dim=4096, n_layers=32, n_heads=32, vocab_size=32000, max_seq_len=8192),
+    "llama2-13b": dict(dim=5120, n_layers=40, n_heads=40, vocab_size=32000, max_seq_len=8192),
+}
+
+
+def model_args_for(name: str, **overrides) -> ModelArgs:
+    cfg = dict(PRESETS[name])
+    cfg.update(overrides)
+    return ModelArgs(**cfg)
+
+
+def ffn_hidden_dim(dim: int, multiple_of: int, ffn_dim_multiplier: Optional[float]) -> int:
+    """int(2 * 4 * dim / 3) rounded up to ``multiple_of`` (reference :256-260): 11008 / 13824."""
+    hidden = int(2 * (4 * dim) / 3)
+    if ffn_dim_multiplier is not None:
+        hidden = int(ffn_dim_multiplier * hidden)
+    return multiple_of * ((hidden + multiple_of - 1) // multiple_of)
+
+
+class RMSNorm(nn.Module):
+    def __init__(self, dim: int, eps: float = 1e-6):
+        super().__init__()
+        self.eps = eps
+        self.weight = nn.Parameter(torch.ones(dim))
+
+    def forward(self, x):
+        return ops.rms_norm(x, self.weight, self.eps)
+
+    def reset_parameters(self):
+        nn.init.ones_(self.weight)
+
+
+class Linear(nn.Module):
+    """Bias-free (or biased) projection on the tcgen05 GEMM; parameter names match nn.Linear."""
+
+    def __init__(self, in_features: int, out_features: int, bias: bool = False):
+        super().__init__()
+        self.in_features, self.out_features = in_features, out_features
+        self.weight = nn.Parameter(torch.empty(out_features, in_features))
+        self.bias = nn.Parameter(torch.zeros(out_features)) if bias else None
+        nn.init.kaiming_uniform_(self.weight, a=5 ** 0.5)
+
+    def forward(self, x, residual=None):
+        return ops.linear(x, self.weight, self.bias, residual)
+
+    def extra_repr(self):
+        return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}"
+
+
+class Attention(nn.Module):
+    def __init__(self, args: ModelArgs):
+        super().__init__()
+        self.n_heads = args.n_heads
+        self.n_kv_heads = args.n_heads if args.n_kv_heads is None else args.n_kv_heads
+        self.head_dim = args.dim // args.n_heads
+        self.wq = Linear(args.dim, args.n_heads * self.head_dim)
+        self.wk = Linear(args.dim, self.n_kv_heads * self.head_dim)
+        self.wv = Linear(args.dim, self.n_kv_heads * self.head_dim)
+        self.wo = Linear(args.n_heads * self.head_dim, args.dim)
+
+    def init_weights(self, init_std: float):
+        for lin in (self.wq, self.wk, self.wv):
+            nn.init.trunc_normal_(lin.weight, mean=0.0, std=0.02)
+        nn.init.trunc_normal_(self.wo.weight, mean=0.0, std=init_std)
+
+    def forward(self, x, freqs_cis, residual=None, pos_offset: int = 0):
+        bsz, seqlen, _ = x.shape
+        hd = self.head_dim
+        # -1 head counts so the same code runs on head-sharded (tensor-parallel) projections
+        xq = self.wq(x).view(bsz, seqlen, -1, hd)
+        xk = self.wk(x).view(bsz, seqlen, -1, hd)
+        xv = self.wv(x).view(bsz, seqlen, -1, hd)
+        xq = ops.rope(xq, freqs_cis, pos_offset)
+        xk = ops.rope(xk, freqs_cis, pos_offset)
+        out = ops.attention(xq, xk, xv, causal=True)
+        return self.wo(out.reshape(bsz, seqlen, -1), residual=residual)
+
+
+class FeedForward(nn.Module):
+    def __init__(self, dim: int, hidden_dim: int, multiple_of: int, ffn_dim_multiplier: Optional[float]):
+        super().__init__()
+        hidden_dim = ffn_hidden_dim(dim, multiple_of, ffn_dim_multiplier) if hidden_dim == 4 * dim else hidden_dim
+        self.w1 = Linear(dim, hidden_dim)
+        self.w2 = Linear(hidden_dim, dim)
+        self.w3 = Linear(dim, hidden_dim)
+
+    def forward(self, x, residual=None):
+        return self.w2(ops.swiglu(self.w1(x), self.w3(x)), residual=residual)
+
+    def init_weights(self, init_std: float):
+        nn.init.trunc_normal_(self.w1.weight, mean=0.0, std=0.02)
+        for lin in (self.w2, self.w3):
+            nn.init.trunc_normal_(lin.weight, mean=0.0, std=init_std)
+
+
+class TransformerBlock(nn.Module):
+    def __init__(self, layer_id: int, args: ModelArgs):
+        super().__init__()
+        self.n_heads, self.dim = args.n_heads, args.dim
+        self.attention = Attention(args)
+        self.feed_forward = FeedForward(args.dim, 4 * args.dim, args.multiple_of, args.ffn_dim_multiplier)
+        self.layer_id, self.num_layers = layer_id, args.n_layers
+        self.attention_norm = RMSNorm(args.dim, eps=args.norm_eps)
+        self.ffn_norm = RMSNorm(args.dim, eps=args.norm_eps)
+        if args.depth_init:
+            self.weight_init_std = 0.02 / (2 * (layer_id + 1)) ** 0.5
+        else:
+            self.weight_init_std = 0.02 / (2 * args.n_layers) ** 0.5
+
+    def forward(self, x, freqs_cis, pos_offset: int = 0):
+        # residual adds are fused into the wo / w2 GEMM epilogues
+        h = self.attention(self.attention_norm(x), freqs_cis, residual=x, pos_offset=pos_offset)
+        return self.feed_forward(self.ffn_norm(h), residual=h)
+
+    def init_weights(self):
+        for norm in (self.attention_norm, self.ffn_norm):
+            norm.reset_parameters()
+        self.attention.init_weights(self.weight_init_std)
+        self.feed_forward.init_weights(self.weight_init_std)
+
+
+class Transformer(nn.Module):
+    def __init__(self, model_args: ModelArgs, init: bool = True):
+        super().__init__()
+        self.model_args = model_args
+        self.vocab_size, self.n_layers, self.model_dim = model_args.vocab_size, model_args.n_layers, model_args.dim
+        self.tok_embeddings = nn.Embedding(model_args.vocab_size, model_args.dim)
+        self.register_buffer("freqs_cis", self._precompute_freqs(), persistent=True)
+        self.layers = nn.ModuleList(TransformerBlock(i, model_args) for i in range(model_args.n_layers))
+        self.norm = RMSNorm(model_args.dim, eps=model_args.norm_eps)
+        self.output = Linear(model_args.dim, model_args.vocab_size)
+        if init:
+            self.init_weights()
+
+    def _precompute_freqs(self) -> torch.Tensor:
+        a = self.model_args
+        return ops.precompute_freqs_cis(a.dim // a.n_heads, a.max_seq_len * 2)
+
+    def _apply(self, fn, *args, **kwargs):
+        # .to(bfloat16) must not squash the complex64 RoPE table (Module.to casts complex buffers too)
+        fc = self._buffers.pop("freqs_cis", None)
+        try:
+            super()._apply(fn, *args, **kwargs)
+        finally:
+            if fc is not None:
+                probe = fn(torch.empty(0, device=fc.device))  # learn the target device only
+                if probe.device != fc.device:
+                    fc = self._precompute_freqs().to(probe.device) if fc.device.type == "meta" else fc.to(probe.device)
+                self._buffers["freqs_cis"] = fc
+        return self
+
+    def init_weights(self):
+        if self.freqs_cis.device.type != "meta":
+            self.freqs_cis = self._precompute_freqs().to(self.freqs_cis.device)
+        nn.init.normal_(self.tok_embeddings.weight)
+        for layer in self.layers:
+            layer.init_weights()
+        self.norm.reset_parameters()
+        std = self.model_args.dim ** -0.5
+        nn.init.trunc_normal_(self.output.weight, mean=0.0, std=std, a=-3 * std, b=3 * std)
+
+    def embed(self, tokens):
+        return ops.embedding(tokens, self.tok_embeddings.weight)
+
+    def forward(self, tokens: torch.Tensor, pos_offset: int = 0):
+        h = self.embed(tokens)
+        if self.freqs_cis.device != h.device:
+            self.freqs_cis = self.freqs_cis.to(h.device)
+        for layer in self.layers:
+            h = layer(h, self.freqs_cis, pos_offset)
+        h = self.norm(h)
+        return self.output(h).float()
+
+    @classmethod
+    def from_model_args(cls, model_args: ModelArgs) -> "Transformer":
+        return cls(model_args)
+
+    @classmethod
+    def from_name(cls, name: str, device=None, dtype=None, **overrides) -> "Transformer":
+        """Build a preset directly on ``device`` in ``dtype`` (avoids a CPU init of 7B weights)."""
+        args = model_args_for(name, **overrides)
+        prev = torch.get_default_dtype()
+        try:
+            if dtype is not None:
+                torch.set_default_dtype(dtype)
+            if device is not None:
+                with torch.device(device):
+                    return cls(args)
+            return cls(args)
+        finally:
+            torch.set_default_dtype(prev)
+
+    def num_params(self) -> int:
+        return sum(p.numel() for p in self.parameters())
+
+    def flops_per_token(self, seq_len: int) -> float:
+        """Training FLOPs per token: 6*N_matmul + causal attention (fwd 2x2xSxD/2 per layer, x3.5 with bwd)."""
+        a = self.model_args
+        n_mm = sum(p.numel() for n, p in self.named_parameters() if p.dim() == 2 and "tok_embeddings" not in n)
+        attn = a.n_layers * (4 * seq_len * a.dim / 2) * 3.5
+        return 6.0 * n_mm + attn

@@ -84,9 +84,13 @@ def dtype_code(dt: torch.dtype) -> int:
     raise NativeError(f"b200dist kernels support bf16 and fp32 tensors, got {dt}")
 
 
+# entry points that launch more than one kernel
+_KERNELS_PER_CALL = {"rmsnorm_bwd": 2, "layernorm_bwd": 3, "flash_attn_bwd": 3}
+
+
 def call(name: str, *args) -> None:
     """Invoke ``b200_<name>`` and raise on a non-zero return code."""
     global launch_count
     fn = getattr(load(), "b200_" + name)
-    launch_count += 1
+    launch_count += _KERNELS_PER_CALL.get(name, 1)
     check(fn(*args), name)

@@ -1,0 +1,98 @@
+"""Fused optimizers with torch.optim semantics on hand-written kernels.
+
+``FusedAdamW`` == torch.optim.AdamW (reference: 01_fsdp_tp_hybrid.py:162, multinode_ddp_unet.py),
+``FusedSGD``  == torch.optim.SGD(momentum, weight_decay) (reference: scripts/main.py:309-311).
+bf16 parameters get an fp32 master copy in the optimizer state; the kernel writes the master
+weight and the bf16 compute copy in the same pass.  CPU parameters use the PyTorch math.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import native as N
+
+
+class FusedAdamW(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, grad_scale=1.0,
+                 foreach=None, fused=None):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+        self.grad_scale = grad_scale
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        for group in self.param_groups:
+            b1, b2 = group["betas"]
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                if not st:
+                    st["step"] = 0
+                    st["exp_avg"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+                    st["exp_avg_sq"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+                    if p.dtype == torch.bfloat16:
+                        st["master"] = p.detach().float()
+                st["step"] += 1
+                g = p.grad
+                if p.is_cuda and p.is_contiguous() and g.is_contiguous() and g.dtype in (torch.float32, torch.bfloat16):
+                    master = st.get("master")
+                    N.adamw_step(master if master is not None else p.data, g, st["exp_avg"], st["exp_avg_sq"],
+                                 lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"], wd=group["weight_decay"],
+                                 step=st["step"], grad_scale=self.grad_scale,
+                                 p_lowp=p.data if master is not None else None)
+                else:
+                    gf = g.float() * self.grad_scale
+                    master = st.get("master", None)
+                    w = master if master is not None else p.data.float()
+                    st["exp_avg"].mul_(b1).add_(gf, alpha=1 - b1)
+                    st["exp_avg_sq"].mul_(b2).addcmul_(gf, gf, value=1 - b2)
+                    bc1, bc2 = 1 - b1 ** st["step"], 1 - b2 ** st["step"]
+                    w.mul_(1 - group["lr"] * group["weight_decay"])
+                    denom = (st["exp_avg_sq"].sqrt() / (bc2 ** 0.5)).add_(group["eps"])
+                    w.addcdiv_(st["exp_avg"], denom, value=-group["lr"] / bc1)
+                    p.data.copy_(w)
+        return loss
+
+
+class FusedSGD(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-2, momentum=0.0, weight_decay=0.0, grad_scale=1.0):
+        super().__init__(params, dict(lr=lr, momentum=momentum, weight_decay=weight_decay))
+        self.grad_scale = grad_scale
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        for group in self.param_groups:
+            mu, wd, lr = group["momentum"], group["weight_decay"], group["lr"]
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                first = not st
+                if first:
+                    st["step"] = 0
+                    if mu != 0:
+                        st["momentum_buffer"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+                    if p.dtype == torch.bfloat16:
+                        st["master"] = p.detach().float()
+                st["step"] += 1
+                g = p.grad
+                buf = st.get("momentum_buffer")
+                master = st.get("master")
+                if p.is_cuda and p.is_contiguous() and g.is_contiguous() and g.dtype in (torch.float32, torch.bfloat16):
+                    N.sgd_step(master if master is not None else p.data, g, buf, lr=lr, momentum=mu, wd=wd,
+                               first_step=first, grad_scale=self.grad_scale,
+                               p_lowp=p.data if master is not None else None)
+                else:
+                    w = master if master is not None else p.data.float()
+                    d = g.float() * self.grad_scale + wd * w
+                    if buf is not None:
+                        if first:
+                            buf.copy_(d)
+                        else:
+                            buf.mul_(mu).add_(d)
+                        d = buf
+                    w.add_(d, alpha=-lr)
+                    p.data.copy_(w)
+        return loss
