@@ -1,0 +1,228 @@
+"""Collectives on the peer-memory data plane, with a torch.distributed fallback for CPU tensors.
+
+``Communicator`` gives all_reduce / all_gather / reduce_scatter / broadcast / all_to_all /
+barrier plus the fused FSDP step (reduce-scatter + sharded AdamW).  CUDA tensors on a group of
+<= 8 ranks of one box run OUR kernels over NVLink peer pointers (csrc/comm_kernels.cu); CPU
+tensors (gloo unit tests) go through torch.distributed, which is the control plane only.
+
+Reference counterparts: every c10d call site listed in SURVEY.md §2.4-D and the collectives DDP /
+FSDP / DTensor issue implicitly (§2.2).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib as L
+from .peer_mem import PeerBuffer
+
+I, LL, F, U = C.c_int, C.c_longlong, C.c_float, C.c_uint
+
+_DEFAULT_STAGING = int(os.environ.get("B200DIST_STAGING_MB", "64")) << 20
+N_CHANNELS = 8
+
+
+class Communicator:
+    def __init__(self, group=None, staging_bytes: int = _DEFAULT_STAGING, device: Optional[torch.device] = None,
+                 force_fallback: bool = False):
+        self.group = group
+        self.initialized = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if self.initialized else 0
+        self.world = dist.get_world_size(group) if self.initialized else 1
+        use_cuda = torch.cuda.is_available() and not force_fallback
+        self.native = bool(use_cuda and self.world <= 8 and L.available())
+        self.device = device or (torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu"))
+        self.max_ctas = 0
+        self.oneshot_threshold = 256 << 10
+        self._seq = [0] * N_CHANNELS
+        if self.native:
+            self.flags = PeerBuffer(64 << 10, group, self.device)
+            self.staging = [None] * N_CHANNELS
+            self.staging_bytes = staging_bytes
+            self.counter = torch.zeros(256, dtype=torch.int32, device=self.device)
+            self.gate = torch.zeros(64, dtype=torch.int32, device=self.device)
+            torch.cuda.synchronize(self.device)
+            if self.initialized and self.world > 1:
+                dist.barrier(group=group, device_ids=[self.device.index]) if dist.get_backend(group) == "nccl" \
+                    else dist.barrier(group=group)
+
+    # ------------------------------------------------------------------ helpers
+    def _stage(self, channel: int, nbytes: int) -> PeerBuffer:
+        buf = self.staging[channel]
+        if buf is None or buf.nbytes < nbytes:
+            # collective allocation: every rank reaches this with the same sizes in the same order
+            size = max(self.staging_bytes, nbytes)
+            self.staging[channel] = buf = PeerBuffer(size, self.group, self.device)
+        return buf
+
+    def _ctx(self, data: PeerBuffer, channel: int):
+        self._seq[channel] += 1
+        return (data.ptr_array, self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
+                U(self._seq[channel] & 0xFFFFFFFF))
+
+    @staticmethod
+    def _s():
+        return L.stream_ptr()
+
+    def symmetric_buffer(self, nbytes: int) -> PeerBuffer:
+        """Collective: allocate a persistent symmetric buffer (e.g. FSDP parameter shards)."""
+        return PeerBuffer(nbytes, self.group, self.device)
+
+    # ------------------------------------------------------------------ barrier
+    def barrier(self, channel: int = 0):
+        if self.world == 1:
+            return
+        if not self.native:
+            dist.barrier(group=self.group)
+            return
+        L.call("comm_barrier", *self._ctx(self.flags, channel), self._s())
+
+    # ------------------------------------------------------------------ all-reduce
+    def all_reduce(self, t: torch.Tensor, scale: float = 1.0, out: Optional[torch.Tensor] = None,
+                   channel: int = 0, algo: int = 0) -> torch.Tensor:
+        """out = scale * sum over ranks of t (in place when ``out`` is None).  ``out`` may have a
+        different dtype (bf16 <-> fp32): the scale and cast are fused into the reduction."""
+        out = t if out is None else out
+        if self.world == 1:
+            if out is not t or scale != 1.0:
+                out.copy_(t.to(out.dtype) * scale if scale != 1.0 else t)
+            return out
+        if not self.native or not t.is_cuda:
+            tmp = t.clone() if out is not t else t
+            dist.all_reduce(tmp, group=self.group)
+            if scale != 1.0:
+                tmp.mul_(scale)
+            if out is not tmp:
+                out.copy_(tmp)
+            return out
+        assert t.is_contiguous() and out.is_contiguous()
+        n = t.numel()
+        item = t.element_size()
+        pad_to = 8 * self.world
+        n_pad = (n + pad_to - 1) // pad_to * pad_to
+        buf = self._stage(channel, n_pad * item)
+        st = buf.tensor(t.dtype, 0, n_pad)
+        st[:n].copy_(t.reshape(-1))
+        if n_pad != n:
+            st[n:].zero_()
+        if algo == 0:
+            algo = 1 if n * item <= self.oneshot_threshold else 2
+        direct = (n_pad == n)
+        dst = out.reshape(-1) if direct else torch.empty(n_pad, dtype=out.dtype, device=out.device)
+        L.call("comm_allreduce", *self._ctx(buf, channel), L.ptr(dst), LL(0), LL(n_pad), F(scale),
+               I(L.dtype_code(t.dtype)), I(L.dtype_code(out.dtype)), I(algo), L.ptr(self.gate), I(self.max_ctas), self._s())
+        if not direct:
+            out.reshape(-1).copy_(dst[:n])
+        return out
+
+    # ------------------------------------------------------------------ all-gather
+    def all_gather(self, out: torch.Tensor, inp: torch.Tensor, channel: int = 1) -> torch.Tensor:
+        """out[r * n : (r+1) * n] = rank r's inp (flat)."""
+        if self.world == 1:
+            out.reshape(-1)[: inp.numel()].copy_(inp.reshape(-1))
+            return out
+        if not self.native or not inp.is_cuda:
+            dist.all_gather_into_tensor(out.reshape(-1), inp.reshape(-1).contiguous(), group=self.group)
+            return out
+        nbytes = inp.numel() * inp.element_size()
+        assert nbytes % 16 == 0, "all_gather shards must be multiples of 16 bytes"
+        buf = self._stage(channel, nbytes)
+        buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
+        return self.all_gather_from(out, buf, 0, nbytes, channel)
+
+    def all_gather_from(self, out: torch.Tensor, src: PeerBuffer, offset_bytes: int, nbytes: int,
+                        channel: int = 1) -> torch.Tensor:
+        """Zero-copy variant: every rank's shard already lives in the symmetric buffer ``src``."""
+        assert out.is_contiguous() and out.numel() * out.element_size() >= nbytes * self.world
+        L.call("comm_allgather", *self._ctx(src, channel), L.ptr(out), LL(offset_bytes), LL(nbytes), I(self.max_ctas),
+               self._s())
+        return out
+
+    # ------------------------------------------------------------------ reduce-scatter
+    def reduce_scatter(self, out: torch.Tensor, inp: torch.Tensor, scale: float = 1.0, channel: int = 2) -> torch.Tensor:
+        """out = scale * sum_r (rank r's inp)[rank * n : (rank+1) * n]."""
+        n = out.numel()
+        if self.world == 1:
+            out.reshape(-1).copy_(inp.reshape(-1)[:n].to(out.dtype) * scale if scale != 1.0 else inp.reshape(-1)[:n])
+            return out
+        if not self.native or not inp.is_cuda:
+            tmp = torch.empty(n, dtype=inp.dtype, device=inp.device)
+            dist.reduce_scatter_tensor(tmp, inp.reshape(-1).contiguous(), group=self.group)
+            out.reshape(-1).copy_(tmp * scale if scale != 1.0 else tmp)
+            return out
+        assert inp.numel() == n * self.world and n % 8 == 0
+        buf = self._stage(channel, inp.numel() * inp.element_size())
+        buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
+        return self.reduce_scatter_from(out, buf, 0, inp.dtype, scale, channel)
+
+    def reduce_scatter_from(self, out: torch.Tensor, src: PeerBuffer, offset_elems: int, in_dtype: torch.dtype,
+                            scale: float = 1.0, channel: int = 2) -> torch.Tensor:
+        L.call("comm_reducescatter", *self._ctx(src, channel), L.ptr(out), LL(offset_elems), LL(out.numel()), F(scale),
+               I(L.dtype_code(in_dtype)), I(L.dtype_code(out.dtype)), I(self.max_ctas), self._s())
+        return out
+
+    def rs_adamw_from(self, src: PeerBuffer, offset_elems: int, in_dtype: torch.dtype, n: int, grad_scale: float,
+                      master, lowp, m, v, *, lr, beta1, beta2, eps, wd, step, channel: int = 2):
+        """Fused gradient reduce-scatter + sharded AdamW update (FSDP)."""
+        bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
+        L.call("comm_rs_adamw", *self._ctx(src, channel), LL(offset_elems), LL(n), F(grad_scale),
+               I(L.dtype_code(in_dtype)), L.ptr(master), L.ptr(lowp), L.ptr(m), L.ptr(v), F(lr), F(beta1), F(beta2),
+               F(eps), F(wd), F(bc1), F(bc2), I(self.max_ctas), self._s())
+
+    # ------------------------------------------------------------------ broadcast / all-to-all
+    def broadcast(self, t: torch.Tensor, src: int = 0, channel: int = 3) -> torch.Tensor:
+        if self.world == 1:
+            return t
+        if not self.native or not t.is_cuda:
+            dist.broadcast(t, src=dist.get_global_rank(self.group, src) if self.group is not None else src, group=self.group)
+            return t
+        assert t.is_contiguous()
+        nbytes = t.numel() * t.element_size()
+        pad = (nbytes + 15) // 16 * 16
+        buf = self._stage(channel, pad)
+        if self.rank == src:
+            buf.tensor(torch.uint8, 0, nbytes).copy_(t.reshape(-1).view(torch.uint8))
+        if pad == nbytes:
+            L.call("comm_broadcast", *self._ctx(buf, channel), L.ptr(t), LL(0), LL(pad), I(src), I(self.max_ctas), self._s())
+        else:
+            tmp = torch.empty(pad, dtype=torch.uint8, device=t.device)
+            L.call("comm_broadcast", *self._ctx(buf, channel), L.ptr(tmp), LL(0), LL(pad), I(src), I(self.max_ctas), self._s())
+            t.reshape(-1).view(torch.uint8).copy_(tmp[:nbytes])
+        return t
+
+    def all_to_all(self, out: torch.Tensor, inp: torch.Tensor, channel: int = 4) -> torch.Tensor:
+        """out chunk r = rank r's inp chunk [this rank]; equal-size chunks along the flat dimension."""
+        if self.world == 1:
+            out.copy_(inp)
+            return out
+        if not self.native or not inp.is_cuda:
+            dist.all_to_all_single(out.reshape(-1), inp.reshape(-1).contiguous(), group=self.group)
+            return out
+        nbytes = inp.numel() * inp.element_size()
+        per = nbytes // self.world
+        assert per % 16 == 0 and out.is_contiguous()
+        buf = self._stage(channel, nbytes)
+        buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
+        L.call("comm_alltoall", *self._ctx(buf, channel), L.ptr(out), LL(0), LL(per), I(self.max_ctas), self._s())
+        return out
+
+
+_default: Optional[Communicator] = None
+_by_group = {}
+
+
+def get_communicator(group=None) -> Communicator:
+    """One communicator per process group (created collectively on first use)."""
+    global _default
+    key = id(group) if group is not None else None
+    if key is None:
+        if _default is None:
+            _default = Communicator(None)
+        return _default
+    if key not in _by_group:
+        _by_group[key] = Communicator(group)
+    return _by_group[key]

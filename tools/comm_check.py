@@ -1,0 +1,136 @@
+"""Multi-GPU correctness + bandwidth check of the peer-memory collectives against NCCL.
+
+    torchrun --nproc-per-node 2 --master-addr 127.0.0.1 tools/comm_check.py
+"""
+from __future__ import annotations
+
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+from b200dist.comm import Communicator  # noqa: E402
+
+
+def ev_time(fn, iters=10, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([s.elapsed_time(e) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm = Communicator(None, staging_bytes=1 << 30)
+    dev = torch.device("cuda", local)
+    fails = 0
+
+    def check(name, got, ref, tol=0.0):
+        nonlocal fails
+        err = (got.float() - ref.float()).abs().max().item()
+        ok = err <= tol
+        fails += (not ok)
+        if rank == 0 or not ok:
+            print(f"[{'PASS' if ok else 'FAIL'}] rank{rank} {name}: max_err={err:.4g}", flush=True)
+
+    torch.manual_seed(100 + rank)
+    comm.barrier()
+    torch.cuda.synchronize()
+    for dt in (torch.float32, torch.bfloat16):
+        for n in (8 * world, 1024, 100003, 1 << 20, 5 * (1 << 20) + 8 * world):
+            x = torch.randint(-8, 8, (n,), device=dev).to(dt)   # integer payload: sums are exact
+            ref = x.clone(); dist.all_reduce(ref)
+            for algo in (1, 2):
+                y = x.clone()
+                comm.all_reduce(y, algo=algo)
+                check(f"all_reduce {dt} n={n} algo={algo}", y, ref)
+            y32 = torch.empty(n, device=dev, dtype=torch.float32)
+            comm.all_reduce(x, scale=0.5, out=y32)
+            check(f"all_reduce scale+cast {dt} n={n}", y32, ref.float() * 0.5)
+        n = 1 << 18
+        x = torch.randint(-8, 8, (n,), device=dev).to(dt)
+        out = torch.empty(n * world, device=dev, dtype=dt); ref = torch.empty_like(out)
+        dist.all_gather_into_tensor(ref, x)
+        comm.all_gather(out, x)
+        check(f"all_gather {dt}", out, ref)
+        xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+        o = torch.empty(n, device=dev, dtype=dt); r = torch.empty(n, device=dev, dtype=dt)
+        dist.reduce_scatter_tensor(r, xin)
+        comm.reduce_scatter(o, xin)
+        check(f"reduce_scatter {dt}", o, r)
+        b = torch.randint(-8, 8, (12345,), device=dev).to(dt); rb = b.clone()
+        dist.broadcast(rb, src=world - 1)
+        comm.broadcast(b, src=world - 1)
+        check(f"broadcast {dt}", b, rb)
+        a2 = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+        oa = torch.empty_like(a2); ra = torch.empty_like(a2)
+        dist.all_to_all_single(ra, a2)
+        comm.all_to_all(oa, a2)
+        check(f"all_to_all {dt}", oa, ra)
+    # fused reduce-scatter + AdamW vs (NCCL reduce-scatter, torch AdamW)
+    n = 1 << 16
+    g = torch.randn(n * world, device=dev).bfloat16()
+    p0 = torch.randn(n, device=dev)
+    gr = torch.empty(n, device=dev, dtype=torch.float32)
+    dist.reduce_scatter_tensor(gr, g.float())
+    pr = p0.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([pr], lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    pr.grad = gr / world
+    opt.step()
+    buf = comm.symmetric_buffer(g.numel() * 2)
+    buf.tensor(torch.bfloat16).copy_(g)
+    master = p0.clone(); m = torch.zeros(n, device=dev); v = torch.zeros(n, device=dev)
+    lowp = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    comm.rs_adamw_from(buf, 0, torch.bfloat16, n, 1.0 / world, master, lowp, m, v, lr=1e-2, beta1=0.9, beta2=0.95,
+                       eps=1e-8, wd=0.1, step=1)
+    check("rs_adamw master", master, pr.detach(), 2e-3)
+    check("rs_adamw lowp", lowp, pr.detach(), 3e-2)
+    torch.cuda.synchronize()
+    # bandwidth
+    for mb in (1, 16, 256):
+        n = mb * (1 << 20) // 2
+        x = torch.randn(n, device=dev).bfloat16()
+        t_own = ev_time(lambda: comm.all_reduce(x, algo=2))
+        t_nccl = ev_time(lambda: dist.all_reduce(x))
+        bus = lambda t: 2 * (world - 1) / world * n * 2 / t / 1e6
+        if rank == 0:
+            print(f"[TIME] all_reduce {mb} MiB bf16 x{world}: own {t_own*1e3:.1f} us busbw {bus(t_own):.0f} GB/s | "
+                  f"NCCL {t_nccl*1e3:.1f} us busbw {bus(t_nccl):.0f} GB/s", flush=True)
+        out = torch.empty(n * world, device=dev, dtype=torch.bfloat16)
+        t_own = ev_time(lambda: comm.all_gather(out, x))
+        t_nccl = ev_time(lambda: dist.all_gather_into_tensor(out, x))
+        busg = lambda t: (world - 1) * n * 2 / t / 1e6
+        if rank == 0:
+            print(f"[TIME] all_gather {mb} MiB/rank: own {t_own*1e3:.1f} us busbw {busg(t_own):.0f} GB/s | NCCL {t_nccl*1e3:.1f} us "
+                  f"busbw {busg(t_nccl):.0f} GB/s", flush=True)
+    x = torch.zeros(8, device=dev)
+    t_own = ev_time(lambda: comm.barrier(), iters=50)
+    t_small = ev_time(lambda: comm.all_reduce(x), iters=50)
+    t_nccl = ev_time(lambda: dist.all_reduce(x), iters=50)
+    if rank == 0:
+        print(f"[TIME] barrier {t_own*1e3:.1f} us | 32 B all_reduce own {t_small*1e3:.1f} us NCCL {t_nccl*1e3:.1f} us", flush=True)
+    tot = torch.tensor([fails], device=dev)
+    dist.all_reduce(tot)
+    if rank == 0:
+        print(f"== comm_check world={world}: total failures {int(tot.item())}", flush=True)
+    dist.destroy_process_group()
+    sys.exit(1 if int(tot.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()
