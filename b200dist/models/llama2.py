@@ -77,6 +77,13 @@ class RMSNorm(nn.Module):
         nn.init.ones_(self.weight)
 
 
+class Embedding(nn.Embedding):
+    """nn.Embedding parameters, gather/scatter-add on the native kernels."""
+
+    def forward(self, idx):
+        return ops.embedding(idx, self.weight)
+
+
 class Linear(nn.Module):
     """Bias-free (or biased) projection on the tcgen05 GEMM; parameter names match nn.Linear."""
 
@@ -171,7 +178,7 @@ class Transformer(nn.Module):
         super().__init__()
         self.model_args = model_args
         self.vocab_size, self.n_layers, self.model_dim = model_args.vocab_size, model_args.n_layers, model_args.dim
-        self.tok_embeddings = nn.Embedding(model_args.vocab_size, model_args.dim)
+        self.tok_embeddings = Embedding(model_args.vocab_size, model_args.dim)
         self.register_buffer("freqs_cis", self._precompute_freqs(), persistent=True)
         self.layers = nn.ModuleList(TransformerBlock(i, model_args) for i in range(model_args.n_layers))
         self.norm = RMSNorm(model_args.dim, eps=model_args.norm_eps)
@@ -207,7 +214,7 @@ class Transformer(nn.Module):
         nn.init.trunc_normal_(self.output.weight, mean=0.0, std=std, a=-3 * std, b=3 * std)
 
     def embed(self, tokens):
-        return ops.embedding(tokens, self.tok_embeddings.weight)
+        return self.tok_embeddings(tokens)
 
     def forward(self, tokens: torch.Tensor, pos_offset: int = 0):
         h = self.embed(tokens)

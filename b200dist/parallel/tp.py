@@ -1,0 +1,369 @@
+"""Tensor parallelism + Megatron sequence parallelism as a plan over module names.
+
+Same vocabulary as the reference's DTensor plans
+(/root/reference/scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:110-152;
+scripts/03_tensor_parallel_tp/02_basic_tensor_parallel.py:64-71; tensor_parallel_vit.py:352-361):
+``parallelize_module(module, tp_mesh, {"attention.wq": ColwiseParallel(), ...})`` with
+``ColwiseParallel`` / ``RowwiseParallel`` / ``SequenceParallel`` / ``PrepareModuleInput`` and
+``Shard(dim)`` / ``Replicate()`` layouts.  Semantics:
+
+* Colwise: weight rows (out features) sharded; input Replicate or Shard(1) (sequence shard, gathered
+  first); output Shard(-1) or gathered to Replicate.
+* Rowwise: weight columns (in features) sharded; partial outputs are all-reduced (Replicate) or
+  reduce-scattered along the sequence (Shard(1)); on ``nn.Embedding`` it shards the vocabulary.
+* SequenceParallel: the module (a norm) runs on the local sequence shard; its weight gradient is
+  all-reduced over the TP group.
+* PrepareModuleInput: gathers sequence-sharded inputs once for all projections below it; their
+  input gradients stay partial and are summed by the gather's backward reduce-scatter.
+
+There are no DTensors: parameters are plain local shards (same names, so state-dict keys are
+unchanged), activations are plain tensors, and the layout changes are explicit autograd functions
+over the peer-memory collectives of ``b200dist.comm`` (gloo on CPU).  The fused
+all-gather→GEMM and GEMM→reduce-scatter kernels plug in underneath these functions.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Optional, Sequence, Tuple, Union
+
+import torch
+import torch.distributed as dist
+from torch import nn
+from torch.autograd import Function
+
+from .. import ops
+from .mesh import DeviceMesh
+
+
+# ----------------------------------------------------------------------------- layouts
+@dataclass(frozen=True)
+class Shard:
+    dim: int
+
+
+@dataclass(frozen=True)
+class Replicate:
+    pass
+
+
+Layout = Union[Shard, Replicate]
+
+
+def _is_seq_shard(l: Optional[Layout]) -> bool:
+    return isinstance(l, Shard) and l.dim == 1
+
+
+# ----------------------------------------------------------------------------- collectives as autograd fns
+def _ag_seq_raw(comm, x):
+    """[B, S/T, ...] -> [B, S, ...] (concatenate the ranks' sequence shards)."""
+    T = comm.world
+    x = x.contiguous()
+    out = torch.empty((T,) + tuple(x.shape), dtype=x.dtype, device=x.device)
+    comm.all_gather(out, x, channel=5)
+    if x.shape[0] == 1:
+        return out.view(1, T * x.shape[1], *x.shape[2:])
+    return out.transpose(0, 1).reshape(x.shape[0], T * x.shape[1], *x.shape[2:])
+
+
+def _rs_seq_raw(comm, x):
+    """[B, S, ...] partial sums -> [B, S/T, ...] reduced sequence shard."""
+    T = comm.world
+    B, S = x.shape[0], x.shape[1]
+    assert S % T == 0, f"sequence length {S} not divisible by TP degree {T}"
+    if B == 1:
+        src = x.contiguous()
+    else:
+        src = x.view(B, T, S // T, *x.shape[2:]).transpose(0, 1).contiguous()
+    out = torch.empty((B, S // T) + tuple(x.shape[2:]), dtype=x.dtype, device=x.device)
+    comm.reduce_scatter(out, src, channel=6)
+    return out
+
+
+def _ag_last_raw(comm, x):
+    T = comm.world
+    x = x.contiguous()
+    out = torch.empty((T,) + tuple(x.shape), dtype=x.dtype, device=x.device)
+    comm.all_gather(out, x, channel=5)
+    return out.movedim(0, -2).reshape(*x.shape[:-1], T * x.shape[-1])
+
+
+class _AllGatherSeq(Function):
+    @staticmethod
+    def forward(ctx, x, comm):
+        ctx.comm = comm
+        return _ag_seq_raw(comm, x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _rs_seq_raw(ctx.comm, g), None
+
+
+class _ReduceScatterSeq(Function):
+    @staticmethod
+    def forward(ctx, x, comm):
+        ctx.comm = comm
+        return _rs_seq_raw(comm, x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _ag_seq_raw(ctx.comm, g), None
+
+
+class _AllReduce(Function):  # Megatron "g": all-reduce forward, identity backward
+    @staticmethod
+    def forward(ctx, x, comm):
+        y = x.contiguous().clone()
+        comm.all_reduce(y, channel=6)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None
+
+
+class _CopyToTP(Function):  # Megatron "f": identity forward, all-reduce backward
+    @staticmethod
+    def forward(ctx, x, comm):
+        ctx.comm = comm
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.contiguous().clone()
+        ctx.comm.all_reduce(g, channel=6)
+        return g, None
+
+
+class _AllGatherLast(Function):
+    @staticmethod
+    def forward(ctx, x, comm):
+        ctx.comm = comm
+        ctx.n = x.shape[-1]
+        return _ag_last_raw(comm, x)
+
+    @staticmethod
+    def backward(ctx, g):
+        r = ctx.comm.rank
+        return g[..., r * ctx.n:(r + 1) * ctx.n].contiguous(), None
+
+
+def all_gather_seq(x, comm):
+    return x if comm.world == 1 else _AllGatherSeq.apply(x, comm)
+
+
+def reduce_scatter_seq(x, comm):
+    return x if comm.world == 1 else _ReduceScatterSeq.apply(x, comm)
+
+
+def all_reduce(x, comm):
+    return x if comm.world == 1 else _AllReduce.apply(x, comm)
+
+
+def copy_to_tp(x, comm):
+    return x if comm.world == 1 else _CopyToTP.apply(x, comm)
+
+
+def all_gather_last(x, comm):
+    return x if comm.world == 1 else _AllGatherLast.apply(x, comm)
+
+
+# ----------------------------------------------------------------------------- styles
+class ParallelStyle:
+    def apply(self, module: nn.Module, mesh: DeviceMesh, name: str) -> None:  # pragma: no cover
+        raise NotImplementedError
+
+
+def _shard_param(p: nn.Parameter, dim: int, rank: int, world: int) -> nn.Parameter:
+    assert p.shape[dim] % world == 0, f"dim {dim} of size {p.shape[dim]} not divisible by TP degree {world}"
+    return nn.Parameter(p.data.chunk(world, dim=dim)[rank].contiguous().clone(), requires_grad=p.requires_grad)
+
+
+class ColwiseParallel(ParallelStyle):
+    def __init__(self, *, input_layouts: Optional[Layout] = None, output_layouts: Optional[Layout] = None,
+                 use_local_output: bool = True):
+        self.input_layouts = input_layouts or Replicate()
+        self.output_layouts = output_layouts or Shard(-1)
+        self.use_local_output = use_local_output  # kept for API parity; outputs are always local tensors
+
+    def apply(self, module, mesh, name):
+        comm, T, r = mesh.communicator(), mesh.size(), mesh.get_local_rank()
+        assert hasattr(module, "weight") and module.weight.dim() == 2, f"{name}: ColwiseParallel needs a Linear"
+        module.weight = _shard_param(module.weight, 0, r, T)
+        if getattr(module, "bias", None) is not None:
+            module.bias = _shard_param(module.bias, 0, r, T)
+        if hasattr(module, "out_features"):
+            module.out_features //= T
+        seq_in = _is_seq_shard(self.input_layouts)
+        gather_out = isinstance(self.output_layouts, Replicate)
+        module._tp_info = {"style": "colwise", "dim": 0, "world": T, "rank": r}
+
+        def forward(x, residual=None):
+            if seq_in:
+                x = all_gather_seq(x, comm)
+            elif not getattr(module, "_tp_input_from_gather", False):
+                x = copy_to_tp(x, comm)
+            y = ops.linear(x, module.weight, getattr(module, "bias", None))
+            if gather_out:
+                y = all_gather_last(y, comm)
+            return y + residual if residual is not None else y
+
+        module.forward = forward
+
+
+class RowwiseParallel(ParallelStyle):
+    def __init__(self, *, input_layouts: Optional[Layout] = None, output_layouts: Optional[Layout] = None,
+                 use_local_output: bool = True):
+        self.input_layouts = input_layouts or Shard(-1)
+        self.output_layouts = output_layouts or Replicate()
+
+    def apply(self, module, mesh, name):
+        comm, T, r = mesh.communicator(), mesh.size(), mesh.get_local_rank()
+        seq_out = _is_seq_shard(self.output_layouts)
+        if isinstance(module, nn.Embedding):
+            V = module.weight.shape[0]
+            module.weight = _shard_param(module.weight, 0, r, T)
+            module.num_embeddings = V // T
+            vstart = r * (V // T)
+            module._tp_info = {"style": "rowwise-embedding", "dim": 0, "world": T, "rank": r}
+
+            def emb_forward(idx):
+                y = ops.embedding(idx, module.weight, vocab_start=vstart)
+                return reduce_scatter_seq(y, comm) if seq_out else all_reduce(y, comm)
+
+            module.forward = emb_forward
+            return
+        assert hasattr(module, "weight") and module.weight.dim() == 2, f"{name}: RowwiseParallel needs a Linear"
+        module.weight = _shard_param(module.weight, 1, r, T)
+        if hasattr(module, "in_features"):
+            module.in_features //= T
+        module._tp_info = {"style": "rowwise", "dim": 1, "world": T, "rank": r}
+
+        def forward(x, residual=None):
+            y = ops.linear(x, module.weight, None)  # partial sums; bias is added once, after the reduction
+            y = reduce_scatter_seq(y, comm) if seq_out else all_reduce(y, comm)
+            b = getattr(module, "bias", None)
+            if b is not None:
+                y = y + b
+            return y + residual if residual is not None else y
+
+        module.forward = forward
+
+
+class SequenceParallel(ParallelStyle):
+    """Norm layers under Megatron-SP: compute on the local sequence shard, all-reduce weight grads."""
+
+    def apply(self, module, mesh, name):
+        comm = mesh.communicator()
+        module._tp_info = {"style": "sequence", "world": mesh.size(), "rank": mesh.get_local_rank()}
+        if comm.world == 1:
+            return
+        for p in module.parameters(recurse=False):
+            def hook(g, _comm=comm):
+                g = g.contiguous().clone()
+                _comm.all_reduce(g, channel=6)
+                return g
+            p.register_hook(hook)
+
+
+class PrepareModuleInput(ParallelStyle):
+    def __init__(self, *, input_layouts: Sequence[Optional[Layout]], desired_input_layouts: Sequence[Optional[Layout]],
+                 use_local_output: bool = True):
+        self.input_layouts = tuple(input_layouts)
+        self.desired_input_layouts = tuple(desired_input_layouts)
+
+    def apply(self, module, mesh, name):
+        comm = mesh.communicator()
+        gather_idx = [i for i, (a, b) in enumerate(zip(self.input_layouts, self.desired_input_layouts))
+                      if _is_seq_shard(a) and isinstance(b, Replicate)]
+        if not gather_idx:
+            return
+        # projections below read an already-gathered input: their input grads stay partial and the
+        # gather's backward reduce-scatter performs the cross-rank sum (one collective, not three)
+        for sub in module.modules():
+            sub._tp_input_from_gather = True
+
+        def pre_hook(mod, args):
+            args = list(args)
+            for i in gather_idx:
+                if i < len(args) and torch.is_tensor(args[i]):
+                    args[i] = all_gather_seq(args[i], comm)
+            return tuple(args)
+
+        module.register_forward_pre_hook(pre_hook)
+
+
+def parallelize_module(module: nn.Module, device_mesh: DeviceMesh, parallelize_plan: Dict[str, ParallelStyle]) -> nn.Module:
+    """Apply ``parallelize_plan`` (``{relative module name: style}``) over the 1-D TP mesh ``device_mesh``."""
+    assert device_mesh.ndim == 1, "pass the 1-D tensor-parallel sub-mesh (mesh['tp'])"
+    mods = dict(module.named_modules())
+    # PrepareModuleInput first so it can mark the projections beneath it
+    ordered = sorted(parallelize_plan.items(), key=lambda kv: 0 if isinstance(kv[1], PrepareModuleInput) else 1)
+    for name, style in ordered:
+        target = module if name == "" else mods.get(name)
+        if target is None:
+            raise KeyError(f"parallelize_module: no submodule named '{name}'")
+        style.apply(target, device_mesh, name)
+    module._tp_mesh = device_mesh
+    return module
+
+
+# ----------------------------------------------------------------------------- ready-made plans
+def llama_tp_plan(model, tp_mesh: DeviceMesh, sequence_parallel: bool = True, gather_logits: bool = True):
+    """The reference's hybrid plan (01_fsdp_tp_hybrid.py:110-152) applied to ``b200dist.models.llama2.Transformer``."""
+    if sequence_parallel:
+        root = {
+            "tok_embeddings": RowwiseParallel(input_layouts=Replicate(), output_layouts=Shard(1)),
+            "norm": SequenceParallel(),
+            "output": ColwiseParallel(input_layouts=Shard(1), output_layouts=Replicate() if gather_logits else Shard(-1)),
+        }
+        block = {
+            "attention_norm": SequenceParallel(),
+            "attention": PrepareModuleInput(input_layouts=(Shard(1), Replicate()),
+                                            desired_input_layouts=(Replicate(), Replicate())),
+            "attention.wq": ColwiseParallel(use_local_output=False),
+            "attention.wk": ColwiseParallel(use_local_output=False),
+            "attention.wv": ColwiseParallel(use_local_output=False),
+            "attention.wo": RowwiseParallel(output_layouts=Shard(1)),
+            "ffn_norm": SequenceParallel(),
+            "feed_forward": PrepareModuleInput(input_layouts=(Shard(1),), desired_input_layouts=(Replicate(),)),
+            "feed_forward.w1": ColwiseParallel(),
+            "feed_forward.w2": RowwiseParallel(output_layouts=Shard(1)),
+            "feed_forward.w3": ColwiseParallel(),
+        }
+    else:
+        root = {
+            "tok_embeddings": RowwiseParallel(input_layouts=Replicate()),
+            "output": ColwiseParallel(output_layouts=Replicate() if gather_logits else Shard(-1)),
+        }
+        block = {
+            "attention.wq": ColwiseParallel(), "attention.wk": ColwiseParallel(), "attention.wv": ColwiseParallel(),
+            "attention.wo": RowwiseParallel(),
+            "feed_forward.w1": ColwiseParallel(), "feed_forward.w3": ColwiseParallel(),
+            "feed_forward.w2": RowwiseParallel(),
+        }
+    parallelize_module(model, tp_mesh, root)
+    for layer in model.layers:
+        parallelize_module(layer, tp_mesh, block)
+    model._tp_sequence_parallel = sequence_parallel
+    return model
+
+
+def gather_tp_state_dict(module: nn.Module, tp_mesh: DeviceMesh) -> Dict[str, torch.Tensor]:
+    """Collective over the TP group: reassemble full parameters (reference names and shapes)."""
+    comm = tp_mesh.communicator()
+    info = {}
+    for mname, mod in module.named_modules():
+        ti = getattr(mod, "_tp_info", None)
+        if ti and "dim" in ti:
+            for pname, _ in mod.named_parameters(recurse=False):
+                if pname == "weight" or (pname == "bias" and ti["style"] == "colwise"):
+                    info[f"{mname}.{pname}" if mname else pname] = ti["dim"] if pname == "weight" else 0
+    sd = {}
+    for k, v in module.state_dict().items():
+        if k in info and comm.world > 1:
+            parts = torch.empty((comm.world,) + tuple(v.shape), dtype=v.dtype, device=v.device)
+            comm.all_gather(parts, v.contiguous(), channel=5)
+            sd[k] = torch.cat(list(parts.unbind(0)), dim=info[k])
+        else:
+            sd[k] = v
+    return sd

@@ -145,6 +145,44 @@ template <typename T> struct Acc8 {
   }
 };
 
+// Sum `world` peers' 8-element chunks at element offset `off` for kU consecutive grid-strided chunks:
+// all kU * world 128-bit (bf16) / 2x128-bit (fp32) loads are issued before the first add, so one
+// thread keeps kU * world NVLink requests in flight (latency ~2 us needs ~1 MB in flight per GPU).
+template <typename T, int kU>
+__device__ __forceinline__ void peer_sum(const CommCtx& c, long long off, const long long (&idx)[kU],
+                                         const bool (&ok)[kU], float (&acc)[kU][8]) {
+  constexpr int kV = sizeof(T) == 2 ? 1 : 2;
+  uint4 raw[kU][kMaxRanks][kV];
+#pragma unroll
+  for (int u = 0; u < kU; ++u)
+#pragma unroll
+    for (int t = 0; t < kMaxRanks; ++t)
+      if (t < c.world && ok[u]) {
+        const T* p = reinterpret_cast<const T*>(c.data[(t + c.rank) % c.world]) + off + idx[u] * 8;
+#pragma unroll
+        for (int v = 0; v < kV; ++v) raw[u][t][v] = ld_peer_v4(reinterpret_cast<const uint4*>(p) + v);
+      }
+#pragma unroll
+  for (int u = 0; u < kU; ++u) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
+#pragma unroll
+    for (int t = 0; t < kMaxRanks; ++t)
+      if (t < c.world && ok[u]) {
+        if constexpr (sizeof(T) == 2) {
+          const uint4 r = raw[u][t][0];
+          acc[u][0] += bf16lo(r.x); acc[u][1] += bf16hi(r.x); acc[u][2] += bf16lo(r.y); acc[u][3] += bf16hi(r.y);
+          acc[u][4] += bf16lo(r.z); acc[u][5] += bf16hi(r.z); acc[u][6] += bf16lo(r.w); acc[u][7] += bf16hi(r.w);
+        } else {
+          const uint4 a = raw[u][t][0], b = raw[u][t][1];
+          acc[u][0] += __uint_as_float(a.x); acc[u][1] += __uint_as_float(a.y); acc[u][2] += __uint_as_float(a.z);
+          acc[u][3] += __uint_as_float(a.w); acc[u][4] += __uint_as_float(b.x); acc[u][5] += __uint_as_float(b.y);
+          acc[u][6] += __uint_as_float(b.z); acc[u][7] += __uint_as_float(b.w);
+        }
+      }
+  }
+}
+
 // ------------------------------ barrier -------------------------------------
 __global__ void comm_barrier_kernel(CommCtx c) {
   comm_arrive_and_wait(c);
@@ -189,20 +227,22 @@ __global__ void comm_reducescatter_kernel(CommCtx c, TOut* __restrict__ out, lon
                                           long long n, float scale) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
-       i += (long long)gridDim.x * blockDim.x) {
-    Acc8<TIn> acc;
-    acc.zero();
+  constexpr int kU = 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
+    long long idx[kU];
+    bool ok[kU];
+    float acc[kU][8];
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t) {
-      if (t < c.world) {
-        const int src = (t + c.rank) % c.world;
-        acc.add(reinterpret_cast<const TIn*>(c.data[src]) + in_off + (long long)c.rank * n + i * 8);
+    for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < n8; }
+    peer_sum<TIn, kU>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+#pragma unroll
+    for (int u = 0; u < kU; ++u)
+      if (ok[u]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
+        Vec8<TOut>::store(out + idx[u] * 8, acc[u]);
       }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc.v[j] *= scale;
-    Vec8<TOut>::store(out + i * 8, acc.v);
   }
   comm_depart(c);
 }
@@ -217,32 +257,35 @@ __global__ void comm_rs_adamw_kernel(CommCtx c, long long in_off, long long n, f
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
   const float step_size = lr / bc1, decay = 1.f - lr * wd;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
-       i += (long long)gridDim.x * blockDim.x) {
-    Acc8<TIn> acc;
-    acc.zero();
+  constexpr int kU = 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n8; i0 += stride * kU) {
+    long long idx[kU];
+    bool ok[kU];
+    float acc[kU][8];
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t) {
-      if (t < c.world) {
-        const int src = (t + c.rank) % c.world;
-        acc.add(reinterpret_cast<const TIn*>(c.data[src]) + in_off + (long long)c.rank * n + i * 8);
+    for (int u = 0; u < kU; ++u) { idx[u] = i0 + u * stride; ok[u] = idx[u] < n8; }
+    peer_sum<TIn, kU>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      if (!ok[u]) continue;
+      const long long i = idx[u];
+      float pv[8], mv[8], vv[8];
+      Vec8<float>::load(master + i * 8, pv);
+      Vec8<float>::load(m + i * 8, mv);
+      Vec8<float>::load(v + i * 8, vv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float g = acc[u][j] * grad_scale;
+        mv[j] = beta1 * mv[j] + (1.f - beta1) * g;
+        vv[j] = beta2 * vv[j] + (1.f - beta2) * g * g;
+        pv[j] = pv[j] * decay - step_size * (mv[j] / (sqrtf(vv[j]) / bc2_sqrt + eps));
       }
+      Vec8<float>::store(master + i * 8, pv);
+      Vec8<float>::store(m + i * 8, mv);
+      Vec8<float>::store(v + i * 8, vv);
+      if (lowp) Vec8<__nv_bfloat16>::store(lowp + i * 8, pv);
     }
-    float pv[8], mv[8], vv[8];
-    Vec8<float>::load(master + i * 8, pv);
-    Vec8<float>::load(m + i * 8, mv);
-    Vec8<float>::load(v + i * 8, vv);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float g = acc.v[j] * grad_scale;
-      mv[j] = beta1 * mv[j] + (1.f - beta1) * g;
-      vv[j] = beta2 * vv[j] + (1.f - beta2) * g * g;
-      pv[j] = pv[j] * decay - step_size * (mv[j] / (sqrtf(vv[j]) / bc2_sqrt + eps));
-    }
-    Vec8<float>::store(master + i * 8, pv);
-    Vec8<float>::store(m + i * 8, mv);
-    Vec8<float>::store(v + i * 8, vv);
-    if (lowp) Vec8<__nv_bfloat16>::store(lowp + i * 8, pv);
   }
   comm_depart(c);
 }
@@ -254,16 +297,22 @@ __global__ void comm_allreduce_oneshot_kernel(CommCtx c, TOut* __restrict__ out,
                                               long long n, float scale) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
-       i += (long long)gridDim.x * blockDim.x) {
-    Acc8<TIn> acc;
-    acc.zero();
+  constexpr int kU = 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
+    long long idx[kU];
+    bool ok[kU];
+    float acc[kU][8];
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t)
-      if (t < c.world) acc.add(reinterpret_cast<const TIn*>(c.data[(t + c.rank) % c.world]) + in_off + i * 8);
+    for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < n8; }
+    peer_sum<TIn, kU>(c, in_off, idx, ok, acc);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc.v[j] *= scale;
-    Vec8<TOut>::store(out + i * 8, acc.v);
+    for (int u = 0; u < kU; ++u)
+      if (ok[u]) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
+        Vec8<TOut>::store(out + idx[u] * 8, acc[u]);
+      }
   }
   comm_depart(c);
 }
@@ -278,17 +327,24 @@ __global__ void comm_allreduce_twoshot_kernel(CommCtx c, TOut* __restrict__ out,
   const long long slice = n / c.world;
   const long long s8 = slice >> 3;
   T* mine = reinterpret_cast<T*>(c.data[c.rank]) + in_off + (long long)c.rank * slice;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < s8;
-       i += (long long)gridDim.x * blockDim.x) {
-    Acc8<T> acc;
-    acc.zero();
+  {
+    constexpr int kU = 2;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < s8; i += stride * kU) {
+      long long idx[kU];
+      bool ok[kU];
+      float acc[kU][8];
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t)
-      if (t < c.world)
-        acc.add(reinterpret_cast<const T*>(c.data[(t + c.rank) % c.world]) + in_off + (long long)c.rank * slice + i * 8);
+      for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < s8; }
+      peer_sum<T, kU>(c, in_off + (long long)c.rank * slice, idx, ok, acc);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc.v[j] *= scale;
-    Vec8<T>::store(mine + i * 8, acc.v);
+      for (int u = 0; u < kU; ++u)
+        if (ok[u]) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
+          Vec8<T>::store(mine + idx[u] * 8, acc[u]);
+        }
+    }
   }
   comm_grid_barrier(c, local_gate);
   const long long total8 = s8 * c.world;
