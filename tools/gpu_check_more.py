@@ -238,3 +238,142 @@ def group_attn_bwd(results):
 
 GROUPS = {"norms": group_norms, "elementwise": group_elementwise, "attn_fwd": group_attn_fwd,
           "attn_bwd": group_attn_bwd}
+
+
+def group_conv(results):
+    import torch
+    import torch.nn.functional as F
+    from b200dist.ops import conv as C
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(5)
+
+    def cmp(name, fn_mine, fn_ref, inputs, tol=5e-2, rtol=3e-2):
+        mine_in = [t.detach().clone().requires_grad_(t.is_floating_point()) for t in inputs]
+        ref_in = [t.detach().float().clone().requires_grad_(t.is_floating_point()) for t in inputs]
+        ym, yr = fn_mine(*mine_in), fn_ref(*ref_in)
+        _check(f"{name} fwd", ym, yr, tol, rtol, results)
+        g = torch.randn_like(yr)
+        ym.backward(g.to(ym.dtype)); yr.backward(g)
+        for i, (a, b) in enumerate(zip(mine_in, ref_in)):
+            if b.grad is not None:
+                scale = max(1.0, float(b.grad.abs().max()))
+                _check(f"{name} grad{i}", a.grad, b.grad, tol * scale, rtol, results)
+
+    bf = torch.bfloat16
+    for (N, Cin, H, W, K, k, s, p) in [(2, 64, 14, 14, 128, 1, 1, 0), (2, 64, 15, 13, 64, 3, 1, 1), (2, 32, 16, 16, 64, 3, 2, 1),
+                                        (2, 3, 32, 32, 64, 7, 2, 3), (2, 64, 14, 14, 128, 1, 2, 0), (1, 64, 9, 12, 65, 1, 1, 0)]:
+        x = torch.randn(N, Cin, H, W, device=dev).to(bf)
+        w = (torch.randn(K, Cin, k, k, device=dev) * (Cin * k * k) ** -0.5).to(bf)
+        b = torch.randn(K, device=dev).to(bf)
+        cmp(f"conv2d {Cin}->{K} k{k} s{s} {H}x{W}", lambda x, w, b: C.conv2d(x, w, b, s, p),
+            lambda x, w, b: F.conv2d(x, w, b, s, p), [x, w, b])
+    x = torch.randn(4, 64, 12, 10, device=dev).to(bf)
+    g = (1 + 0.1 * torch.randn(64, device=dev)); b = 0.1 * torch.randn(64, device=dev)
+    res = torch.randn(4, 64, 12, 10, device=dev).to(bf)
+    rm, rv = torch.zeros(64, device=dev), torch.ones(64, device=dev)
+    rm2, rv2 = rm.clone(), rv.clone()
+    cmp("batchnorm+res+relu", lambda x, g, b, r: C.batch_norm(x, g, b, rm, rv, True, 0.1, 1e-5, residual=r, relu=True),
+        lambda x, g, b, r: F.relu(F.batch_norm(x, rm2, rv2, g, b, True, 0.1, 1e-5) + r), [x, g, b, res])
+    _check("bn running_mean", rm, rm2, 1e-2, 1e-2, results)
+    _check("bn running_var", rv, rv2, 1e-2, 1e-2, results)
+    cmp("batchnorm plain", lambda x, g, b: C.batch_norm(x, g, b, None, None, True), lambda x, g, b: F.batch_norm(x, None, None, g, b, True),
+        [x, g, b])
+    cmp("maxpool 3/2/1", lambda x: C.max_pool2d(x, 3, 2, 1), lambda x: F.max_pool2d(x, 3, 2, 1), [x])
+    cmp("maxpool 2", lambda x: C.max_pool2d(x, 2), lambda x: F.max_pool2d(x, 2), [x[:, :, :, :9]])
+    cmp("global avgpool", lambda x: C.global_avg_pool(x), lambda x: x.mean((2, 3)), [x])
+    wt = (torch.randn(64, 32, 2, 2, device=dev) * 0.1).to(bf); bt = torch.randn(32, device=dev).to(bf)
+    cmp("convT 2x2", lambda x, w, b: C.conv_transpose2x2(x, w, b), lambda x, w, b: F.conv_transpose2d(x, w, b, stride=2), [x, wt, bt])
+    cmp("bilinear 12x10->25x21", lambda x: C.bilinear_resize(x, (25, 21)),
+        lambda x: F.interpolate(x, size=(25, 21), mode="bilinear", align_corners=False), [x])
+    tgt = torch.randn_like(x)
+    w_l = C.lat_weights(12, dev).view(1, 1, -1, 1)
+    cmp("lat mse", lambda p: C.latitude_weighted_mse(p, tgt), lambda p: (w_l * (p - tgt.float()) ** 2).mean(), [x], tol=1e-2)
+    cmp("lat mse channels_last", lambda p: C.latitude_weighted_mse(p.contiguous(memory_format=torch.channels_last), tgt),
+        lambda p: (w_l * (p - tgt.float()) ** 2).mean(), [x], tol=1e-2)
+
+
+def group_models(results):
+    """Whole-model parity: loss curves of our models vs the reference / torchvision implementations."""
+    import sys
+    import torch
+    import torchvision
+    from b200dist import ops
+    from b200dist.models import build_resnet
+    from b200dist.models.llama2 import ModelArgs, Transformer
+    from b200dist.ops import FusedAdamW, FusedSGD
+    _check, _time = _h()
+    dev = "cuda"
+    ref_dir = "/root/repo/baseline/_ref/reference_src/fsdp_tp"
+    sys.path.insert(0, ref_dir)
+    import llama2_model as ref
+    a = dict(dim=256, n_layers=2, n_heads=4, vocab_size=1024, max_seq_len=256)
+    torch.manual_seed(0)
+    r = ref.Transformer.from_model_args(ref.ModelArgs(**a)).to(dev)
+    m = Transformer(ModelArgs(**a)).to(dev)
+    m.load_state_dict(r.state_dict())
+    m = m.to(torch.bfloat16)
+    ro = torch.optim.AdamW(r.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    mo = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    g = torch.Generator(device="cpu").manual_seed(1)
+    lr_, lm_ = [], []
+    for step in range(8):
+        tok = torch.randint(0, 1024, (4, 129), generator=g).to(dev)
+        x, y = tok[:, :-1], tok[:, 1:]
+        ro.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = r(x)
+        l = torch.nn.functional.cross_entropy(out.float().view(-1, 1024), y.reshape(-1)); l.backward(); ro.step()
+        mo.zero_grad()
+        l2 = ops.cross_entropy(m(x), y); l2.backward(); mo.step()
+        lr_.append(float(l)); lm_.append(float(l2))
+    print("ref  losses", [round(v, 4) for v in lr_], flush=True)
+    print("ours losses", [round(v, 4) for v in lm_], flush=True)
+    _check("llama loss curve vs reference (bf16)", torch.tensor(lm_), torch.tensor(lr_), 0.08, 0.01, results)
+    assert lm_[-1] < lm_[0]
+    # ResNet-18 vs torchvision, SGD
+    torch.manual_seed(0)
+    tv = torchvision.models.resnet18(num_classes=100).to(dev)
+    mine = build_resnet("resnet18", num_classes=100).to(dev)
+    mine.load_state_dict(tv.state_dict())
+    mine = mine.to(torch.bfloat16)
+    to = torch.optim.SGD(tv.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5)
+    mo = FusedSGD(mine.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5)
+    x = torch.rand(16, 3, 64, 64, device=dev); y = torch.randint(0, 100, (16,), device=dev)
+    lt, lm = [], []
+    for step in range(6):
+        to.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            o = tv(x)
+        l = torch.nn.functional.cross_entropy(o.float(), y); l.backward(); to.step()
+        mo.zero_grad()
+        l2 = ops.cross_entropy(mine(x.bfloat16()), y); l2.backward(); mo.step()
+        lt.append(float(l)); lm.append(float(l2))
+    print("tv   losses", [round(v, 4) for v in lt], flush=True)
+    print("ours losses", [round(v, 4) for v in lm], flush=True)
+    _check("resnet18 loss curve vs torchvision (bf16)", torch.tensor(lm), torch.tensor(lt), 0.35, 0.05, results)
+    assert lm[-1] < lm[0]
+    # ResNet-50 throughput, single GPU (no DDP): ours vs torchvision+autocast
+    for arch, B in (("resnet50", 128),):
+        mine = build_resnet(arch).to(dev).to(torch.bfloat16)
+        mo = FusedSGD(mine.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-5)
+        x = torch.rand(B, 3, 224, 224, device=dev).bfloat16(); y = torch.zeros(B, dtype=torch.long, device=dev)
+
+        def step_mine():
+            mo.zero_grad(); ops.cross_entropy(mine(x), y).backward(); mo.step()
+        ms = _time(step_mine, iters=5, warmup=2)
+        tv = getattr(torchvision.models, arch)().to(dev).to(memory_format=torch.channels_last)
+        to = torch.optim.SGD(tv.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-5)
+        xf = x.float().contiguous(memory_format=torch.channels_last)
+
+        def step_tv():
+            to.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                o = tv(xf)
+            torch.nn.functional.cross_entropy(o.float(), y).backward(); to.step()
+        ms_tv = _time(step_tv, iters=5, warmup=2)
+        print(f"[TIME] {arch} B{B} train step: ours {ms:.1f} ms ({B/ms*1e3:.0f} img/s) | torchvision+cuDNN bf16 autocast {ms_tv:.1f} ms "
+              f"({B/ms_tv*1e3:.0f} img/s)", flush=True)
+
+
+GROUPS.update({"conv": group_conv, "models": group_models})
