@@ -191,7 +191,7 @@ __global__ void comm_barrier_kernel(CommCtx c) {
 
 // ------------------------------ all-gather (pull) ----------------------------
 // out[t * n .. (t+1) * n) = peer t's data[in_off .. in_off + n)   (elements of 16 bytes)
-__global__ void comm_allgather_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
+__global__ void __launch_bounds__(512, 1) comm_allgather_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
                                       long long n16) {
   comm_arrive_and_wait(c);
   const long long total = n16 * c.world;
@@ -223,11 +223,11 @@ __global__ void comm_allgather_kernel(CommCtx c, uint4* __restrict__ out, long l
 // ------------------------------ reduce-scatter (pull) ------------------------
 // out[i] = scale * sum_t peer t's data[in_off + rank * n + i],  i in [0, n)  (n in elements, % 8 == 0)
 template <typename TIn, typename TOut>
-__global__ void comm_reducescatter_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
+__global__ void __launch_bounds__(512, 1) comm_reducescatter_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
                                           long long n, float scale) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
-  constexpr int kU = 2;
+  constexpr int kU = sizeof(TIn) == 2 ? 2 : 1;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
     long long idx[kU];
@@ -250,14 +250,14 @@ __global__ void comm_reducescatter_kernel(CommCtx c, TOut* __restrict__ out, lon
 // reduce-scatter fused with the sharded AdamW step (FSDP gradient path):
 // the summed gradient never touches HBM; master weight, moments and the bf16 shard are updated in place.
 template <typename TIn>
-__global__ void comm_rs_adamw_kernel(CommCtx c, long long in_off, long long n, float grad_scale,
+__global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long long in_off, long long n, float grad_scale,
                                      float* __restrict__ master, __nv_bfloat16* __restrict__ lowp,
                                      float* __restrict__ m, float* __restrict__ v, float lr, float beta1,
                                      float beta2, float eps, float wd, float bc1, float bc2_sqrt) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
   const float step_size = lr / bc1, decay = 1.f - lr * wd;
-  constexpr int kU = 2;
+  constexpr int kU = sizeof(TIn) == 2 ? 2 : 1;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n8; i0 += stride * kU) {
     long long idx[kU];
@@ -293,11 +293,11 @@ __global__ void comm_rs_adamw_kernel(CommCtx c, long long in_off, long long n, f
 // ------------------------------ all-reduce -----------------------------------
 // one-shot: every rank sums all peers' buffers (small messages: one NVLink round trip)
 template <typename TIn, typename TOut>
-__global__ void comm_allreduce_oneshot_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
+__global__ void __launch_bounds__(512, 1) comm_allreduce_oneshot_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
                                               long long n, float scale) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
-  constexpr int kU = 2;
+  constexpr int kU = sizeof(TIn) == 2 ? 2 : 1;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
     long long idx[kU];
@@ -321,14 +321,14 @@ __global__ void comm_allreduce_oneshot_kernel(CommCtx c, TOut* __restrict__ out,
 // slices from their owners into `out`.  Per-GPU NVLink traffic ~ 2 * (W-1)/W * bytes.
 // n must be a multiple of 8 * world.  The symmetric buffer is overwritten with the result slices.
 template <typename T, typename TOut>
-__global__ void comm_allreduce_twoshot_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
+__global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
                                               long long n, float scale, uint32_t* local_gate) {
   comm_arrive_and_wait(c);
   const long long slice = n / c.world;
   const long long s8 = slice >> 3;
   T* mine = reinterpret_cast<T*>(c.data[c.rank]) + in_off + (long long)c.rank * slice;
   {
-    constexpr int kU = 2;
+    constexpr int kU = sizeof(T) == 2 ? 2 : 1;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < s8; i += stride * kU) {
       long long idx[kU];
@@ -374,7 +374,7 @@ __global__ void comm_allreduce_twoshot_kernel(CommCtx c, TOut* __restrict__ out,
 }
 
 // ------------------------------ broadcast / all-to-all -----------------------
-__global__ void comm_broadcast_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
+__global__ void __launch_bounds__(512, 1) comm_broadcast_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
                                       long long n16, int root) {
   comm_arrive_and_wait(c);
   const uint4* src = reinterpret_cast<const uint4*>(c.data[root]) + in_off16;
@@ -385,7 +385,7 @@ __global__ void comm_broadcast_kernel(CommCtx c, uint4* __restrict__ out, long l
 }
 
 // out[t * n ..] = peer t's data[in_off + rank * n ..]   (16-byte elements)
-__global__ void comm_alltoall_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
+__global__ void __launch_bounds__(512, 1) comm_alltoall_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
                                      long long n16) {
   comm_arrive_and_wait(c);
   const long long total = n16 * c.world;

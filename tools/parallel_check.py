@@ -1,0 +1,119 @@
+"""Multi-GPU strategy parity on real GPUs: FSDP (fused rs+AdamW), DDP, TP+SP vs a single-GPU run of the
+same model and data.  torchrun --nproc-per-node 2 tools/parallel_check.py"""
+from __future__ import annotations
+
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+
+def toy(seed=3, **kw):
+    from b200dist.models.llama2 import ModelArgs, Transformer
+
+    torch.manual_seed(seed)
+    cfg = dict(dim=256, n_layers=2, n_heads=4, vocab_size=512, max_seq_len=256)
+    cfg.update(kw)
+    return Transformer(ModelArgs(**cfg))
+
+
+def batches(n, B=4, S=128, V=512):
+    g = torch.Generator().manual_seed(9)
+    return [torch.randint(0, V, (B, S + 1), generator=g) for _ in range(n)]
+
+
+def main():
+    from b200dist import ops
+    from b200dist.ops import FusedAdamW, FusedSGD
+    from b200dist.parallel import DDP, FSDP, init_device_mesh
+    from b200dist.parallel.tp import llama_tp_plan
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    steps = 4
+    data = batches(steps, B=2 * world)
+
+    def single(opt_kind):
+        m = toy().to(dev).to(torch.bfloat16)
+        opt = (FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1) if opt_kind == "adamw"
+               else FusedSGD(m.parameters(), lr=0.05, momentum=0.9))
+        losses = []
+        for t in data:
+            t = t.to(dev)
+            opt.zero_grad()
+            l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
+            losses.append(float(l))
+        return m, losses
+
+    ok = True
+
+    def report(name, got, ref, tol):
+        nonlocal ok
+        err = max(abs(a - b) for a, b in zip(got, ref))
+        good = err <= tol
+        ok &= good
+        if rank == 0:
+            print(f"[{'PASS' if good else 'FAIL'}] {name}: max loss diff {err:.4g}  got={['%.4f' % v for v in got]} "
+                  f"ref={['%.4f' % v for v in ref]}", flush=True)
+
+    ref_m, ref_losses = single("adamw")
+    # ---------------- FSDP (fused reduce-scatter + AdamW in peer memory) ----------------
+    for reshard in (True, False):
+        m = toy().to(dev).to(torch.bfloat16)
+        f = FSDP(m, reshard_after_forward=reshard)
+        opt = f.build_optimizer("adamw", lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+        losses = []
+        for t in data:
+            t = t.chunk(world)[rank].to(dev)
+            opt.zero_grad()
+            l = ops.cross_entropy(f(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
+            lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+        report(f"FSDP reshard={reshard} loss curve", losses, ref_losses, 0.03)
+        sd = f.full_state_dict(rank0_only=False, offload_to_cpu=False)
+        w, wr = sd["layers.1.feed_forward.w2.weight"].float(), ref_m.layers[1].feed_forward.w2.weight.float()
+        err = float((w - wr).abs().max())
+        good = err < 2e-2
+        ok &= good
+        if rank == 0:
+            print(f"[{'PASS' if good else 'FAIL'}] FSDP reshard={reshard} final weights: max diff {err:.4g}", flush=True)
+    # ---------------- DDP (bucketed all-reduce over peer memory) ----------------
+    ref_m2, ref_losses2 = single("sgd")
+    m = toy().to(dev).to(torch.bfloat16)
+    d = DDP(m, bucket_cap_mb=1.0, first_bucket_mb=0.25)
+    opt = FusedSGD(d.parameters(), lr=0.05, momentum=0.9)
+    losses = []
+    for t in data:
+        t = t.chunk(world)[rank].to(dev)
+        opt.zero_grad()
+        l = ops.cross_entropy(d(t[:, :-1]), t[:, 1:]); l.backward(); d.finish_backward(); opt.step()
+        lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+    report(f"DDP ({len(d.buckets)} buckets) loss curve", losses, ref_losses2, 0.03)
+    # ---------------- TP + SP ----------------
+    mesh = init_device_mesh("cuda", (world,), ("tp",))
+    for sp in (True, False):
+        m = toy().to(dev).to(torch.bfloat16)
+        llama_tp_plan(m, mesh["tp"], sequence_parallel=sp)
+        opt = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+        losses = []
+        for t in data:
+            t = t.to(dev)
+            opt.zero_grad()
+            l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
+            losses.append(float(l))
+        report(f"TP{world} sp={sp} loss curve", losses, ref_losses, 0.03)
+    t = torch.tensor([0 if ok else 1], device=dev)
+    dist.all_reduce(t)
+    if rank == 0:
+        print("ALL OK" if int(t) == 0 else "SOME FAILED", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t) == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()
