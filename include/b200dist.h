@@ -1,0 +1,168 @@
+/* b200dist native library — C ABI of b200dist/_native/libb200dist.so (sm_100a only).
+ *
+ * Every entry point returns 0 on success or one of the B200_ERR_* codes; b200_last_error() returns the
+ * message of the last failure on the calling thread.  All pointers are DEVICE pointers unless stated
+ * otherwise, `stream` is the CUDA stream the work is enqueued on, dtype codes are 0 = bf16, 1 = fp32.
+ * Entry points never synchronise the device and (unless their comment says so) never allocate: scratch
+ * is passed in by the caller.  Citations are paths under the reference repository
+ * (negin513/distributed-pytorch-hpc) naming the library call each kernel replaces.
+ */
+#ifndef B200DIST_H_
+#define B200DIST_H_
+
+#include <cuda_runtime_api.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+#define B200DIST_API extern "C"
+#else
+#define B200DIST_API
+#endif
+
+enum { B200_OK = 0, B200_ERR_CUDA = 1, B200_ERR_SHAPE = 2, B200_ERR_UNSUPPORTED = 3, B200_ERR_LIMIT = 4 };
+
+/* ---- Runtime ----
+ * no counterpart in the reference (it has no native code) */
+B200DIST_API int b200_version(void);
+B200DIST_API const char* b200_last_error(void);
+B200DIST_API int b200_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin);
+
+/* ---- GEMM (tcgen05 / TMEM / TMA) ----
+ * replaces cuBLAS behind nn.Linear / torch.matmul: fsdp_tp/llama2_model.py:207,228,267,447 and their autograd */
+B200DIST_API int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K,
+                            long long lda, long long ldb, long long ldd, int a_mn_major,
+                            int b_mn_major, int out_fp32, const void* bias, const void* residual,
+                            long long ldr, float alpha, int act, int accumulate, int config,
+                            int max_ctas, cudaStream_t stream);
+
+/* ---- Attention (tcgen05 flash attention) ----
+ * replaces F.scaled_dot_product_attention: fsdp_tp/llama2_model.py:218-223; explicit softmax attention: scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122 */
+B200DIST_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, void* O, float* LSE,
+                                 int B, int H, int Hkv, int Sq, int Sk, int hd,
+                                 long long q_sb, long long q_ss, long long q_sh,
+                                 long long k_sb, long long k_ss, long long k_sh,
+                                 long long v_sb, long long v_ss, long long v_sh,
+                                 long long o_sb, long long o_ss, long long o_sh,
+                                 float scale, int causal, int q_offset, int k_offset,
+                                 cudaStream_t stream);
+B200DIST_API int b200_flash_attn_bwd(const void* Q, const void* K, const void* V, const void* O,
+                                 const void* dO, const float* LSE, float* delta, void* dQ, void* dK,
+                                 void* dV, int B, int H, int Hkv, int Sq, int Sk, int hd,
+                                 const long long* strides /* 24: q,k,v,o,do,dq,dk,dv x (b,s,h) */,
+                                 float scale, int causal, int q_offset, int k_offset,
+                                 cudaStream_t stream);
+
+/* ---- Normalisation ----
+ * RMSNorm fsdp_tp/llama2_model.py:115-142; nn.LayerNorm tensor_parallel_vit.py:141-143 */
+B200DIST_API int b200_norm_bwd_partials(int rows);
+B200DIST_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int rows, int D,
+                              float eps, int dtype, cudaStream_t stream);
+B200DIST_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                              void* dx, void* dw, float* scratch, int rows, int D, int add_to_dx,
+                              int accumulate_dw, int dtype, cudaStream_t stream);
+B200DIST_API int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,
+                                float* rstd, int rows, int D, float eps, int dtype,
+                                cudaStream_t stream);
+B200DIST_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, const float* mean,
+                                const float* rstd, void* dx, void* dw, void* db, float* scratch,
+                                int rows, int D, int accumulate, int dtype, cudaStream_t stream);
+
+/* ---- Elementwise / embedding / loss ----
+ * RoPE llama2_model.py:73-100; SwiGLU :266-267; nn.Embedding :374,440; CrossEntropyLoss scripts/main.py:308 */
+B200DIST_API int b200_rope(const void* x, void* y, const float* freqs, long long rows, int S, int H,
+                       int hd, int pos_offset, int backward, int dtype, cudaStream_t stream);
+B200DIST_API int b200_swiglu_fwd(const void* a, const void* b, void* y, long long rows, int F,
+                             long long lda, long long ldb, long long ldy, int dtype,
+                             cudaStream_t stream);
+B200DIST_API int b200_swiglu_bwd(const void* dy, const void* a, const void* b, void* da, void* db,
+                             long long rows, int F, long long ldy, long long lda, long long ldb,
+                             long long ldda, long long lddb, int dtype, cudaStream_t stream);
+B200DIST_API int b200_elementwise(const void* x, const void* y2, void* out, long long n, int op,
+                              float alpha, int dtype, cudaStream_t stream);
+B200DIST_API int b200_cast_scale(const void* src, int src_dtype, void* dst, int dst_dtype, long long n,
+                             float alpha, cudaStream_t stream);
+B200DIST_API int b200_embedding_fwd(const long long* idx, const void* w, void* out, long long ntok, int D,
+                                long long vocab_start, long long vocab_local, int dtype,
+                                cudaStream_t stream);
+B200DIST_API int b200_embedding_bwd(const long long* idx, const void* dy, float* dw, long long ntok, int D,
+                                long long vocab_start, long long vocab_local, int dtype,
+                                cudaStream_t stream);
+B200DIST_API int b200_xent_fwd(const void* logits, const long long* target, float* loss, float* lse,
+                           int rows, int V, long long ld, long long ignore_index, int dtype,
+                           cudaStream_t stream);
+B200DIST_API int b200_xent_bwd(const void* logits, const long long* target, const float* lse,
+                           const float* gscale, void* dlogits, int rows, int V, long long ld,
+                           long long ldd, long long ignore_index, int dtype, cudaStream_t stream);
+B200DIST_API int b200_sum_scale(const float* x, float* out, int n, float scale, cudaStream_t stream);
+
+/* ---- Optimizers ----
+ * torch.optim.AdamW 01_fsdp_tp_hybrid.py:162; torch.optim.SGD scripts/main.py:309-311 */
+B200DIST_API int b200_adamw(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* m,
+                        float* v, long long n, float lr, float beta1, float beta2, float eps,
+                        float wd, float bc1, float bc2, float grad_scale, cudaStream_t stream);
+B200DIST_API int b200_sgd(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* buf,
+                      long long n, float lr, float momentum, float wd, float grad_scale,
+                      int first_step, cudaStream_t stream);
+B200DIST_API int b200_sumsq(const void* x, float* out, long long n, int dtype, cudaStream_t stream);
+
+/* ---- Convolution-network ops (NHWC) ----
+ * cuDNN conv/BN/pool via torchvision scripts/main.py:249; UNet blocks multinode_ddp_unet.py:171-229 */
+B200DIST_API int b200_im2col(const void* x, void* col, int N, int H, int W, int C, int Cp, int KH, int KW, int stride, int pad, int Ho, int Wo, int dtype, cudaStream_t stream);
+B200DIST_API int b200_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int Cp, int KH, int KW, int stride, int pad, int Ho, int Wo, int dtype, cudaStream_t stream);
+B200DIST_API int b200_col_reduce(const void* a, const void* xin, const void* y, const float* mean, const float* rstd,
+                             float* sums, long long rows, int C, int mode, int relu_mask, int dtype,
+                             cudaStream_t stream);
+B200DIST_API int b200_bn_finalize(const float* sums, float* mean, float* rstd, float* running_mean, float* running_var,
+                              long long rows, int C, float eps, float momentum, cudaStream_t stream);
+B200DIST_API int b200_bn_apply(const void* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                           const void* residual, void* y, long long rows, int C, int relu, int dtype,
+                           cudaStream_t stream);
+B200DIST_API int b200_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
+                               const float* gamma, const float* sums, void* dx, void* dres, long long rows, int C,
+                               int relu_mask, int dtype, cudaStream_t stream);
+B200DIST_API int b200_maxpool(const void* a, const void* x, void* idx, void* out, int N, int H, int W, int C, int K,
+                          int stride, int pad, int Ho, int Wo, int backward, int dtype, cudaStream_t stream);
+B200DIST_API int b200_avgpool(const void* in, void* out, int N, int HW, int C, int backward, int dtype, cudaStream_t stream);
+B200DIST_API int b200_pixel_shuffle2(const void* src, void* dst, int N, int H, int W, int K, int dir, int dtype,
+                                 cudaStream_t stream);
+B200DIST_API int b200_bilinear(const void* src, void* dst, int N, int Hi, int Wi, int Ho, int Wo, int C, int backward,
+                           int dtype, cudaStream_t stream);
+B200DIST_API int b200_lat_mse(const void* pred, const void* target, const float* wlat, float* loss_sum, void* grad,
+                          const float* gscale, long long total, int H, long long h_div, int backward, int dtype,
+                          cudaStream_t stream);
+
+/* ---- Peer memory (CUDA IPC symmetric buffers) ----
+ * plays the role of NCCL's buffer registration, SURVEY.md 5.8 */
+B200DIST_API int b200_peer_alloc(size_t bytes, void** out);
+B200DIST_API int b200_peer_free(void* p);
+B200DIST_API int b200_peer_export(void* p, unsigned char* handle64);
+B200DIST_API int b200_peer_import(const unsigned char* handle64, void** out);
+B200DIST_API int b200_peer_close(void* p);
+
+/* ---- Collectives over NVLink peer memory ----
+ * replace c10d/NCCL: tests/torch_comm_bench.py:49,79; DDP / FSDP / DTensor implicit collectives */
+B200DIST_API int b200_comm_barrier(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, cudaStream_t stream);
+B200DIST_API int b200_comm_allreduce(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off, long long n, float scale,
+                                 int in_dtype, int out_dtype, int algo, void* local_gate, int max_ctas,
+                                 cudaStream_t stream);
+B200DIST_API int b200_comm_allgather(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes,
+                                 int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_reducescatter(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off, long long n, float scale,
+                                     int in_dtype, int out_dtype, int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_rs_adamw(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, long long in_off, long long n, float grad_scale, int in_dtype,
+                                float* master, void* lowp, float* m, float* v, float lr, float beta1,
+                                float beta2, float eps, float wd, float bc1, float bc2, int max_ctas,
+                                cudaStream_t stream);
+B200DIST_API int b200_comm_broadcast(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes, int root,
+                                 int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_alltoall(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes_per_peer,
+                                int max_ctas, cudaStream_t stream);
+
+#endif  /* B200DIST_H_ */
