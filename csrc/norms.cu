@@ -333,3 +333,75 @@ B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, co
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// b200_rmsnorm_bwd_noalloc — the same backward as b200_rmsnorm_bwd, for hosts that have no memory
+// to hand us and must not create any.
+//
+// Who needs this: the regular entry point asks the caller for an fp32 scratch of
+// [b200_norm_bwd_partials(rows), D] floats.  A PyTorch caller takes that from the caching allocator,
+// but some callers of this C ABI cannot do the equivalent: a C/C++ or Fortran host that links the
+// library without any allocator of its own; a job whose whole HBM budget was carved up in advance
+// (every byte of the 180 GB already belongs to a pool, so a late cudaMalloc may simply fail); and
+// latency-sensitive loops where cudaMalloc / cudaFree are off limits because they serialise with
+// all other work on the device.  For them the scratch lives inside the library image.
+//
+// How: a file-scope `static __device__` array below holds the per-CTA partial sums.  Its name is only a
+// host-side handle, so before the first launch on each device (with that device current) we ask the
+// runtime for its device address with cudaGetSymbolAddress, check the result and cache it; kernels get
+// that pointer.  No cudaMalloc / cudaFree / torch call is made here, ever.
+//
+// Limits and rules for the caller:
+//   * D <= 8192 and D % 8 == 0; larger rows are rejected with B200_ERR_LIMIT (text in b200_last_error()).
+//     At most 148 partial rows are used, so the array is 148 * 8192 floats = 4.6 MiB, held by every GPU
+//     that loads the library until the process exits.
+//   * The first call on a device performs the address look-up described above; make that first call
+//     before starting any stream capture on that device.
+//   * All calls on a device share the one array and it keeps whatever the previous call left in it.
+//     Nothing in it has to start at zero: each call overwrites every partial row it later reads, and
+//     reads only those rows, so stale contents are never observed.
+//   * Because the array is shared, two calls that may run at the same time on one GPU (different
+//     streams, or different host threads) race on it.  Order them on one stream or with events.
+namespace {
+constexpr int kNoAllocMaxD = 8192;
+constexpr int kNoAllocMaxPartials = 148;
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) float g_rmsnorm_bwd_scratch[(size_t)kNoAllocMaxPartials * kNoAllocMaxD];
+static float* g_rmsnorm_bwd_scratch_addr[kNoAllocMaxDevices] = {nullptr};
+
+B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* rstd,
+                                      void* dx, void* dw, int rows, int D, int add_to_dx,
+                                      int accumulate_dw, int dtype, cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  if (D > kNoAllocMaxD) {
+    b200_set_error("rmsnorm_bwd_noalloc: D = %d exceeds the built-in scratch limit of %d columns "
+                   "(use b200_rmsnorm_bwd with caller-provided scratch)", D, kNoAllocMaxD);
+    return B200_ERR_LIMIT;
+  }
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  int dev = -1;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    b200_set_error("rmsnorm_bwd_noalloc: device ordinal %d out of range", dev);
+    return B200_ERR_LIMIT;
+  }
+  float* scratch = g_rmsnorm_bwd_scratch_addr[dev];
+  if (scratch == nullptr) {  // once per device, with that device current
+    void* p = nullptr;
+    B200_CUDA_CHECK(cudaGetSymbolAddress(&p, g_rmsnorm_bwd_scratch));
+    scratch = static_cast<float*>(p);
+    g_rmsnorm_bwd_scratch_addr[dev] = scratch;
+  }
+  const int grid = rows < kNoAllocMaxPartials ? rows : kNoAllocMaxPartials;  // grid * D <= array size
+  B200_DISPATCH_DTYPE(dtype, T, {
+    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                        (T*)dx, scratch, rows, D, add_to_dx);
+    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
+                                                                    accumulate_dw);
+  });
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

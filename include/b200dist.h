@@ -60,6 +60,15 @@ B200DIST_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* 
 B200DIST_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
                               void* dx, void* dw, float* scratch, int rows, int D, int add_to_dx,
                               int accumulate_dw, int dtype, cudaStream_t stream);
+/* No counterpart in the reference.  Same result as b200_rmsnorm_bwd, but the partial-sum scratch is a fixed
+ * 4.6 MiB array inside the library instead of a caller buffer, for hosts that cannot allocate device memory
+ * (no allocator of their own, HBM fully pre-partitioned, or cudaMalloc banned from the hot loop).  Calls
+ * nothing that allocates.  D <= 8192 (else B200_ERR_LIMIT).  The first call on a device looks up the array's
+ * device address: issue it before any stream capture.  All calls on a GPU share the array, so calls that can
+ * overlap on that GPU race; serialise them. */
+B200DIST_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* rstd,
+                                      void* dx, void* dw, int rows, int D, int add_to_dx,
+                                      int accumulate_dw, int dtype, cudaStream_t stream);
 B200DIST_API int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,
                                 float* rstd, int rows, int D, float eps, int dtype,
                                 cudaStream_t stream);
