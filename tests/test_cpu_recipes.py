@@ -1,0 +1,96 @@
+"""Recipes end to end on CPU: BASELINE config 1 (ResNet-18 DDP, gloo, world 2, synthetic 224x224) and script smoke runs."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import torch
+
+from tests.dist_utils import free_port, run_distributed
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _resnet_ddp_worker(rank, world):
+    from b200dist import ops
+    from b200dist.models import build_resnet
+    from b200dist.parallel import DDP
+
+    torch.manual_seed(0)
+    model = build_resnet("resnet18", num_classes=10)
+    ddp = DDP(model)
+    opt = torch.optim.SGD(ddp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-5)
+    g = torch.Generator().manual_seed(100 + rank)   # each rank trains on different synthetic images
+    x, y = torch.rand(4, 3, 224, 224, generator=g), torch.randint(0, 10, (4,), generator=g)
+    losses = []
+    for _ in range(3):
+        opt.zero_grad()
+        loss = ops.cross_entropy(ddp(x), y)
+        loss.backward()
+        ddp.finish_backward()
+        opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0], losses
+    import torch.distributed as dist
+
+    flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+    other = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(other, flat)
+    assert torch.equal(other[0], other[1]), "replicas diverged"           # bit-identical after N steps
+    rm = model.bn1.running_mean.clone()
+    others = [torch.empty_like(rm) for _ in range(world)]
+    dist.all_gather(others, rm)
+    # BN buffers follow rank 0 (broadcast_buffers=True): equal at the start of the last forward, local update after
+    assert torch.isfinite(rm).all()
+
+
+def test_config1_resnet18_ddp_gloo_world2():
+    run_distributed(_resnet_ddp_worker, 2, timeout=600)
+
+
+def _run(cmd, nproc=1, timeout=600):
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), B200DIST_DISABLE_MPI4PY="1",
+               OMP_NUM_THREADS="1")
+    if nproc > 1:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr",
+               "127.0.0.1", "--master-port", env["MASTER_PORT"]] + cmd
+    else:
+        cmd = [sys.executable] + cmd
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=str(ROOT), env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + "\n" + r.stderr[-3000:]
+    return r.stdout + r.stderr
+
+
+def test_main_py_gloo_ddp(tmp_path):
+    out = _run(["scripts/main.py", "--use_syn", "--arch", "resnet18", "--backend", "gloo", "--num_epochs", "2", "--steps_syn", "2",
+                "--batch_size", "2", "--image_size", "64", "--num_classes", "10", "--logfile", str(tmp_path / "log.txt"),
+                "--model_dir", str(tmp_path)], nproc=2)
+    assert "images/s" in out and (tmp_path / "log.txt").read_text().count("Average epoch time") == 1
+
+
+def test_recipe_scripts_run_on_cpu(tmp_path):
+    out = _run(["scripts/03_tensor_parallel_tp/01_device_mesh_basics.py"], nproc=2)
+    assert "✓" in out
+    out = _run(["scripts/03_tensor_parallel_tp/02_basic_tensor_parallel.py"], nproc=2)
+    assert "iter 4" in out
+    out = _run(["scripts/04_pipeline_parallel_pp/01_manual_model_split.py"], nproc=2)
+    assert "pipeline output" in out
+    out = _run(["scripts/04_pipeline_parallel_pp/03_pipeline_training.py", "--num-steps", "4", "--batch-size", "4", "--seq-len", "16",
+                "--dim", "32", "--layers-per-stage", "1", "--vocab", "100", "--pp", "2"], nproc=2)
+    assert "tokens/s" in out
+    out = _run(["scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py", "--iters", "3", "--seq-len", "32", "--tp_size", "2"], nproc=2)
+    assert "tokens/s" in out
+    out = _run(["scripts/01_data_parallel_ddp/multinode_ddp_basic.py", "--total_epochs", "2", "--backend", "gloo", "--save_every", "1",
+                "--snapshot", str(tmp_path / "snap.pt")], nproc=2)
+    assert (tmp_path / "snap.pt").exists()
+    out = _run(["scripts/07_domain_parallel/01_halo_conv.py"], nproc=2)
+    assert "with halo exchange" in out
+
+
+def test_comm_bench_csv_columns(tmp_path):
+    out = _run(["bench/comm_bench.py", "--backend", "gloo", "--tensor_sizes", "1024", "--warmup_runs", "1", "--benchmark_runs", "2",
+                "--output_file", str(tmp_path / "r.log"), "--impl", "both"], nproc=2)
+    text = (tmp_path / "r.log").read_text()
+    assert "backend,operation,tensor_elements,tensor_bytes,tensor_mb,warmup_iterations" in text
+    ops = {l.split(",")[1] for l in text.splitlines() if l and not l.startswith("#")}
+    assert {"broadcast", "all_reduce", "all_gather", "reduce_scatter"} <= ops
