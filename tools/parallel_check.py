@@ -107,6 +107,39 @@ def main():
             l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
             losses.append(float(l))
         report(f"TP{world} sp={sp} loss curve", losses, ref_losses, 0.03)
+    # ---------------- long context: Ulysses / ring attention; domain parallel: halo conv ----------------
+    from b200dist.comm import get_communicator
+    from b200dist.ops import conv as cops
+    from b200dist.parallel import halo_conv2d, ring_attention, ulysses_attention
+
+    comm = get_communicator(None)
+    g = torch.Generator().manual_seed(0)
+    S, H, hd = 512 * world, 8, 128
+    q, k, v, do = [torch.randn(2, S, H, hd, generator=g).to(dev).to(torch.bfloat16) for _ in range(4)]
+    qr, kr, vr = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    ref = ops.attention(qr, kr, vr, causal=True)
+    ref.backward(do)
+    sl = slice(rank * S // world, (rank + 1) * S // world)
+    for name, fn in (("ring", ring_attention), ("ulysses", ulysses_attention)):
+        ql, kl, vl = [t[:, sl].contiguous().requires_grad_(True) for t in (q, k, v)]
+        out = fn(ql, kl, vl, comm, causal=True)
+        out.backward(do[:, sl].contiguous())
+        errs = [float((out.float() - ref[:, sl].float()).abs().max())] + \
+               [float((a.grad.float() - b.grad[:, sl].float()).abs().max()) for a, b in ((ql, qr), (kl, kr), (vl, vr))]
+        good = max(errs) < 6e-2
+        ok &= good
+        if rank == 0:
+            print(f"[{'PASS' if good else 'FAIL'}] {name} attention vs single GPU: max err out/dq/dk/dv = {['%.3g' % e for e in errs]}", flush=True)
+    x = torch.randn(2, 64, 16 * world, 40, generator=g).to(dev).to(torch.bfloat16)
+    w = (torch.randn(64, 64, 3, 3, generator=g) * 0.05).to(dev).to(torch.bfloat16)
+    full = cops.conv2d(x, w, None, 1, 1)
+    rows = slice(rank * 16, (rank + 1) * 16)
+    halo = halo_conv2d(x[:, :, rows].contiguous(), w, None, comm, padding=1)
+    err = float((halo.float() - full[:, :, rows].float()).abs().max())
+    good = err < 3e-2
+    ok &= good
+    if rank == 0:
+        print(f"[{'PASS' if good else 'FAIL'}] halo conv vs full conv: max err {err:.3g}", flush=True)
     t = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(t)
     if rank == 0:
