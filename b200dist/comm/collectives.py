@@ -23,7 +23,7 @@ from .peer_mem import PeerBuffer
 I, LL, F, U = C.c_int, C.c_longlong, C.c_float, C.c_uint
 
 _DEFAULT_STAGING = int(os.environ.get("B200DIST_STAGING_MB", "64")) << 20
-N_CHANNELS = 8
+N_CHANNELS = 16
 
 
 class Communicator:

@@ -348,6 +348,39 @@ def llama_tp_plan(model, tp_mesh: DeviceMesh, sequence_parallel: bool = True, ga
     return model
 
 
+def enable_fused_tp(model, tp_mesh: DeviceMesh):
+    """Switch the Llama blocks' attention / feed-forward to the fused all-gather->GEMM and GEMM->reduce-scatter
+    kernels (``tp_fused``) whenever the input qualifies (CUDA bf16, batch 1, local sequence % 256 == 0); other inputs
+    keep the unfused collective + GEMM path.  Requires ``llama_tp_plan(..., sequence_parallel=True)`` first."""
+    from . import tp_fused
+    from .. import ops as _ops
+
+    comm = tp_mesh.communicator()
+
+    for blk in model.layers:
+        att, ffn = blk.attention, blk.feed_forward
+
+        def block_forward(x, freqs_cis, pos_offset: int = 0, _blk=blk, _att=att, _ffn=ffn):
+            if not tp_fused.fusable(x, comm):
+                return _blk._unfused_forward(x, freqs_cis, pos_offset)
+            hd = _att.head_dim
+            xn = _blk.attention_norm(x)                                            # local sequence shard
+            q, k, v = tp_fused.ag_linear(comm, xn, [_att.wq.weight, _att.wk.weight, _att.wv.weight])
+            S = q.shape[1]
+            q = _ops.rope(q.view(1, S, -1, hd), freqs_cis, pos_offset)
+            k = _ops.rope(k.view(1, S, -1, hd), freqs_cis, pos_offset)
+            o = _ops.attention(q, k, v.view(1, S, -1, hd), causal=True)
+            h = tp_fused.linear_rs(comm, o.reshape(1, S, -1), _att.wo.weight, residual=x)
+            hn = _blk.ffn_norm(h)
+            a, b = tp_fused.ag_linear(comm, hn, [_ffn.w1.weight, _ffn.w3.weight])
+            return tp_fused.linear_rs(comm, _ops.swiglu(a, b), _ffn.w2.weight, residual=h)
+
+        blk._unfused_forward = blk.forward
+        blk.forward = block_forward
+    model._tp_fused = True
+    return model
+
+
 def gather_tp_state_dict(module: nn.Module, tp_mesh: DeviceMesh) -> Dict[str, torch.Tensor]:
     """Collective over the TP group: reassemble full parameters (reference names and shapes)."""
     comm = tp_mesh.communicator()

@@ -1,0 +1,167 @@
+"""Fused compute+collective tensor-parallel linears (the north-star TP/SP kernels).
+
+``ag_linear``  : sequence-sharded input -> ONE kernel that all-gathers the peers' chunks over NVLink (communication
+                 CTAs inside the GEMM grid, TMA bulk copies, per-sub-chunk ready flags) while the tcgen05 tiles start
+                 on the local chunk; further projections of the same input (wk, wv / w3) reuse the gathered buffer.
+``linear_rs``  : GEMM whose epilogue stores every output row into the owner rank's staging slab over NVLink, then a
+                 slab reduction (+ residual) at the owner: GEMM -> reduce-scatter without a separate collective pass.
+Backward is the dual: ag_linear's input gradient is a GEMM->reduce-scatter (with the other projections' partials fused
+in as the epilogue residual), linear_rs's is an all-gather->GEMM.
+
+These replace the DTensor redistribute + cuBLAS pairs of the reference's hybrid plan
+(/root/reference/scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:126-152; SURVEY.md §3.3 "hot comm #1-#4").
+Used when tensors are CUDA bf16, batch == 1 and (S / T) % 256 == 0; otherwise ``tp.py`` falls back to the unfused
+collective + GEMM path (same math).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+from torch.autograd import Function
+
+from ..ops import _lib as L
+from ..ops import native as N
+
+I, LL, U = C.c_int, C.c_longlong, C.c_uint
+ROWS_PER_FLAG = 256
+
+
+class FusedWorkspace:
+    """Per-communicator symmetric buffers for the fused kernels (grown on demand, collectively)."""
+
+    def __init__(self, comm):
+        self.comm = comm
+        self.gather = {}     # (M, K) -> (PeerBuffer, flags tensor)
+        self.stage = {}      # (M, N) -> PeerBuffer
+        self.epoch = 0
+
+    def gather_buf(self, M, K):
+        key = (M, K)
+        if key not in self.gather:
+            buf = self.comm.symmetric_buffer(M * K * 2)
+            flags = torch.zeros(M // ROWS_PER_FLAG + 8, dtype=torch.int32, device=self.comm.device)
+            self.gather[key] = (buf, flags)
+        return self.gather[key]
+
+    def stage_buf(self, M, Nn):
+        key = (M, Nn)
+        if key not in self.stage:
+            self.stage[key] = self.comm.symmetric_buffer(M * Nn * 2)
+        return self.stage[key]
+
+
+_ws = {}
+
+
+def workspace(comm) -> FusedWorkspace:
+    if id(comm) not in _ws:
+        _ws[id(comm)] = FusedWorkspace(comm)
+    return _ws[id(comm)]
+
+
+def fusable(x: torch.Tensor, comm) -> bool:
+    return (comm.native and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 3 and x.shape[0] == 1
+            and x.shape[1] % 256 == 0 and comm.world > 1)
+
+
+def _ag_gemm(comm, x_shard2d, w, b_mn=False, bias=None, n_comm=4):
+    """x_shard2d [m, K] -> (y [m*T, N], gathered X view [m*T, K])."""
+    ws = workspace(comm)
+    T, r = comm.world, comm.rank
+    m, K = x_shard2d.shape
+    M = m * T
+    Nn = w.shape[1] if b_mn else w.shape[0]
+    buf, flags = ws.gather_buf(M, K)
+    xg = buf.tensor(torch.bfloat16, 0, M * K).view(M, K)
+    xg[r * m:(r + 1) * m].copy_(x_shard2d)
+    y = torch.empty((M, Nn), dtype=torch.bfloat16, device=x_shard2d.device)
+    ws.epoch += 1
+    ch = 8 + 0  # dedicated flag channel for the fused all-gather
+    comm._seq[ch] += 1
+    L.call("ag_gemm_bf16", buf.ptr_array, L.ptr(w), L.ptr(y), I(M), I(Nn), I(K), LL(w.stride(0)), LL(Nn), I(int(b_mn)),
+           L.ptr(bias), L.ptr(None), LL(0), I(0), L.ptr(flags), I(ROWS_PER_FLAG), U(ws.epoch), I(n_comm),
+           comm.flags.ptr_array, L.ptr(comm.counter), I(ch), U(comm._seq[ch]), I(T), I(r), L.stream_ptr())
+    return y, xg
+
+
+def _gemm_rs(comm, a, w, b_mn=False, residual=None, partial_residual=None):
+    """reduce_scatter_rows(a @ w^T [+ partial_residual]) [+ residual]: a [M, K], result [M/T, N]."""
+    ws = workspace(comm)
+    T, r = comm.world, comm.rank
+    M, K = a.shape
+    Nn = w.shape[1] if b_mn else w.shape[0]
+    stage = ws.stage_buf(M, Nn)
+    L.call("gemm_rs_bf16", L.ptr(a), L.ptr(w), stage.ptr_array, I(M), I(Nn), I(K), LL(a.stride(0)), LL(w.stride(0)),
+           I(int(b_mn)), L.ptr(partial_residual), LL(partial_residual.stride(0) if partial_residual is not None else 0),
+           I(T), I(r), L.stream_ptr())
+    out = torch.empty((M // T, Nn), dtype=torch.bfloat16, device=a.device)
+    L.call("comm_slab_reduce", *comm._ctx(stage, 9), L.ptr(out), L.ptr(residual), LL(out.numel()), I(comm.max_ctas),
+           L.stream_ptr())
+    return out
+
+
+class _AGLinear(Function):
+    """ys[i] = all_gather_seq(x) @ ws[i]^T for several column-parallel weights sharing one gathered input."""
+
+    @staticmethod
+    def forward(ctx, comm, x, *weights):
+        S_loc, K = x.shape[1], x.shape[2]
+        y0, xg = _ag_gemm(comm, x.view(S_loc, K), weights[0])
+        xg_saved = xg.clone()   # the workspace is reused by the next fused call
+        ys = [y0] + [N.gemm(xg_saved, w) for w in weights[1:]]
+        ctx.comm = comm
+        ctx.save_for_backward(xg_saved, *weights)
+        S = S_loc * comm.world
+        return tuple(y.view(1, S, -1) for y in ys)
+
+    @staticmethod
+    def backward(ctx, *dys):
+        comm = ctx.comm
+        xg, *weights = ctx.saved_tensors
+        dys = [d.reshape(-1, d.shape[-1]) for d in dys]
+        dys = [d if d.is_contiguous() else d.contiguous() for d in dys]
+        # dX_partial = sum_i dY_i @ W_i: all but the last accumulate locally, the last GEMM adds that partial in its
+        # epilogue and scatters rows to their owners (GEMM -> reduce-scatter)
+        part = None
+        for d, w in zip(dys[:-1], weights[:-1]):
+            if part is None:
+                part = N.gemm(d, w, b_mn=True)
+            else:
+                N.gemm(d, w, b_mn=True, out=part, residual=part)
+        dx = _gemm_rs(comm, dys[-1], weights[-1], b_mn=True, partial_residual=part)
+        dws = [N.gemm(d, xg, a_mn=True, b_mn=True, out_dtype=w.dtype) for d, w in zip(dys, weights)]
+        return (None, dx.view(1, dx.shape[0], dx.shape[1]), *dws)
+
+
+class _LinearRS(Function):
+    """reduce_scatter_seq(x @ w^T) + residual (row-parallel weight, sequence-sharded output)."""
+
+    @staticmethod
+    def forward(ctx, comm, x, w, residual):
+        x2 = x.reshape(-1, x.shape[-1])
+        res2 = residual.reshape(-1, residual.shape[-1]) if residual is not None else None
+        out = _gemm_rs(comm, x2 if x2.is_contiguous() else x2.contiguous(), w, residual=res2)
+        ctx.comm = comm
+        ctx.save_for_backward(x2, w)
+        ctx.has_res = residual is not None
+        return out.view(1, out.shape[0], out.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        comm = ctx.comm
+        x2, w = ctx.saved_tensors
+        d2 = dy.reshape(-1, dy.shape[-1])
+        d2 = d2 if d2.is_contiguous() else d2.contiguous()
+        dx, dyg = _ag_gemm(comm, d2, w, b_mn=True)          # all-gather(dY) -> GEMM with W [N, K_local] as [K=N, N=K_local]
+        dw = N.gemm(dyg, x2, a_mn=True, b_mn=True, out_dtype=w.dtype)
+        return None, dx.view(1, dx.shape[0], dx.shape[1]), dw, (dy if ctx.has_res else None)
+
+
+def ag_linear(comm, x, weights: List[torch.Tensor]):
+    return _AGLinear.apply(comm, x, *weights)
+
+
+def linear_rs(comm, x, w, residual: Optional[torch.Tensor] = None):
+    return _LinearRS.apply(comm, x, w, residual)

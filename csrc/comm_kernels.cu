@@ -373,6 +373,33 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx 
   comm_depart(c);
 }
 
+// ------------------------------ slab reduce (GEMM -> reduce-scatter, step 2) -------------------
+// out[i] = sum_t local_stage[t * n + i] (+ residual[i]);  the slabs were written by the peers' GEMM epilogues.
+__global__ void __launch_bounds__(512, 1) comm_slab_reduce_kernel(CommCtx c, __nv_bfloat16* __restrict__ out,
+                                                                  const __nv_bfloat16* __restrict__ residual,
+                                                                  long long n) {
+  comm_arrive_and_wait(c);   // every rank's GEMM (and its peer stores) retired before it arrived here
+  const long long n8 = n >> 3;
+  const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(c.data[c.rank]);
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (residual) Vec8<__nv_bfloat16>::load(residual + i * 8, acc);
+#pragma unroll
+    for (int t = 0; t < kMaxRanks; ++t)
+      if (t < c.world) {
+        float v[8];
+        Vec8<__nv_bfloat16>::load(base + (long long)t * n + i * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      }
+    Vec8<__nv_bfloat16>::store(out + i * 8, acc);
+  }
+  comm_depart(c);            // peers may refill our slabs only after we have read them
+}
+
 // ------------------------------ broadcast / all-to-all -----------------------
 __global__ void __launch_bounds__(512, 1) comm_broadcast_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
                                       long long n16, int root) {
@@ -549,6 +576,17 @@ B200_API int b200_comm_allreduce(COMM_ARGS, void* out, long long in_off, long lo
     else { b200_set_error("allreduce: bad dtype"); return B200_ERR_UNSUPPORTED; }
 #undef AR2
   }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// n = elements of this rank's chunk (chunk_rows * N, multiple of 8); staging = data_ptrs[rank], [world, n] bf16
+B200_API int b200_comm_slab_reduce(COMM_ARGS, void* out, const void* residual, long long n, int max_ctas,
+                                   cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if (n & 7) { b200_set_error("slab_reduce: elements must be a multiple of 8"); return B200_ERR_SHAPE; }
+  comm_slab_reduce_kernel<<<comm_grid(n >> 3, 512, max_ctas), 512, 0, stream>>>(
+      COMM_CTX, (__nv_bfloat16*)out, (const __nv_bfloat16*)residual, n);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -30,6 +30,35 @@ struct GemmParams {
   int num_m_blocks, num_n_blocks, num_k_blocks, num_tiles;
 };
 
+// Extra state of the fused compute+collective variants (FUSED = true instantiations only).
+//   all-gather -> GEMM : the A operand lives in a symmetric [M, K] buffer; rows of chunk r are produced by rank r.
+//     The first `n_comm` clusters of the grid are COMMUNICATION CTAs: they pull the peers' chunks into the local
+//     buffer with TMA bulk copies (peer global -> smem ring -> local global, megabytes in flight from one thread) and
+//     publish a ready flag per sub-chunk; the GEMM CTAs' TMA producer waits on the flag of the rows it is about to
+//     load, starting with the local chunk, so math overlaps the transfer tile by tile.
+//   GEMM -> reduce-scatter : the epilogue stores every output row straight into the OWNER rank's staging slab
+//     (peer st over NVLink); tiles are visited owner-rotated so all links are busy; a small reduce kernel sums the
+//     slabs at the owner afterwards.
+struct FusedParams {
+  // ---- all-gather prologue ----
+  uint32_t* a_flags;            // local, one uint32 per sub-chunk of `rows_per_flag` rows; ready when == epoch
+  int rows_per_flag;
+  uint32_t epoch;
+  int n_comm;                   // clusters at the front of the grid that only move data
+  const void* a_src[8];         // rank p's symmetric A buffer as mapped here (same layout as the local one)
+  void* a_dst;                  // local symmetric A buffer [M, K], contiguous rows
+  long long chunk_rows;         // M / world
+  long long row_bytes;          // K * 2
+  uint32_t* sig[8];             // peers' signal pads (arrive / depart rows, see comm_kernels.cu)
+  uint32_t* counter;            // local counter for the depart handshake
+  int channel; uint32_t seq;
+  int world, rank;
+  // ---- scatter epilogue ----
+  void* d_ptrs[8];              // rank p's staging buffer [world, d_chunk_rows, N]
+  long long d_chunk_rows;       // rows owned by each rank (0 = scatter disabled)
+  int m_rot;                    // m-block rotation so that tiles start at a given chunk
+};
+
 constexpr int kBlockM = 128;   // rows per CTA (UMMA M = 128 * CTA_GROUP)
 constexpr int kBlockK = 64;    // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
@@ -56,6 +85,46 @@ __device__ __forceinline__ float apply_act(float v, int act) {
   return v;
 }
 
+__device__ __forceinline__ void st_release_gpu_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void bulk_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_dst), "l"(gsrc), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void spin_flag(const uint32_t* p, uint32_t want, bool sys) {
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while ((int32_t)((sys ? ld_acquire_sys_u32(p) : ld_acquire_gpu_u32(p)) - want) < 0) {
+    if ((++spins & 0xfffu) == 0) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 5 * B200_WATCHDOG_NS) {
+        printf("b200dist watchdog: fused-gemm flag stuck (block %d want %u have %u)\n", blockIdx.x, want, *p);
+        __trap();
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
   const int per_group = kGroupM * num_n;
   const int group = tile / per_group;
@@ -66,10 +135,11 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_blk = in_group / gsz;
 }
 
-template <int CG, int BN, bool A_MN, bool B_MN, typename OutT>
+template <int CG, int BN, bool A_MN, bool B_MN, typename OutT, bool FUSED = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                    const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmap_b, const GemmParams p,
+                    const __grid_constant__ FusedParams fp) {
   using Cfg = GemmCfg<CG, BN>;
   constexpr int kStages = Cfg::kStages;
   constexpr int kLoadN = Cfg::kLoadN;
@@ -87,8 +157,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
   const bool is_leader = cta_rank == 0;
-  const int cluster_id = blockIdx.x / CG;
-  const int num_clusters = gridDim.x / CG;
+  const int n_comm = FUSED ? fp.n_comm : 0;
+  const int cluster_id = (int)(blockIdx.x / CG) - n_comm;   // < 0: communication CTA
+  const int num_clusters = (int)(gridDim.x / CG) - n_comm;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -113,7 +184,68 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_addr));
 
-  if (warp == 0) {
+  if (FUSED && cluster_id < 0) {
+    // ===================== communication CTAs (all-gather prologue) =====================
+    // One thread streams peer chunks through the smem ring with TMA bulk copies; every sub-chunk of
+    // `rows_per_flag` rows gets its ready flag once its bytes are in local memory.
+    if (threadIdx.x == 0) {
+      const int my = blockIdx.x;                      // 0 .. n_comm * CG - 1
+      const int n_ctas = n_comm * CG;
+      const int W = fp.world;
+      // arrive: tell every peer that our chunk is complete (stream order put its producer before this kernel)
+      if (my == 0) {
+        __threadfence_system();
+        for (int t = 0; t < W; ++t) st_release_sys_u32(fp.sig[t] + ((size_t)fp.channel * 2 + 0) * 32 + fp.rank, fp.seq);
+      }
+      const long long sub_per_chunk = fp.chunk_rows / fp.rows_per_flag;
+      const long long sub_bytes = (long long)fp.rows_per_flag * fp.row_bytes;
+      constexpr uint32_t kPiece = Cfg::kStageBytes;   // bytes per ring slot
+      uint32_t phases = 0;                            // per-slot mbarrier parity
+      for (int dp = 1; dp < W; ++dp) {
+        const int peer = (fp.rank + dp) % W;
+        spin_flag(fp.sig[fp.rank] + ((size_t)fp.channel * 2 + 0) * 32 + peer, fp.seq, true);  // peer's chunk is ready
+        for (long long sc = my; sc < sub_per_chunk; sc += n_ctas) {
+          const long long off = ((long long)peer * fp.chunk_rows + sc * fp.rows_per_flag) * fp.row_bytes;
+          const char* src = reinterpret_cast<const char*>(fp.a_src[peer]) + off;
+          char* dst = reinterpret_cast<char*>(fp.a_dst) + off;
+          for (long long b0 = 0; b0 < sub_bytes; b0 += (long long)kPiece * kStages) {
+            // batch: up to kStages peer loads in flight, then drain them to local memory in order
+            int nb = 0;
+            for (; nb < kStages && b0 + (long long)nb * kPiece < sub_bytes; ++nb) {
+              const long long b = b0 + (long long)nb * kPiece;
+              const uint32_t n = (uint32_t)((sub_bytes - b) < kPiece ? (sub_bytes - b) : kPiece);
+              mbar_expect_tx(full_bar(nb), n);
+              bulk_g2s(smem_base + nb * Cfg::kStageBytes, src + b, n, full_bar(nb));
+            }
+            for (int i = 0; i < nb; ++i) {
+              const long long b = b0 + (long long)i * kPiece;
+              const uint32_t n = (uint32_t)((sub_bytes - b) < kPiece ? (sub_bytes - b) : kPiece);
+              mbar_wait(full_bar(i), (phases >> i) & 1u);
+              phases ^= (1u << i);
+              bulk_s2g(dst + b, smem_base + i * Cfg::kStageBytes, n);
+              tma_store_commit();
+            }
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // slots may be refilled
+          }
+          // all bytes of this sub-chunk are in local memory -> publish
+          asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+          fence_proxy_async_all();
+          __threadfence();
+          st_release_gpu_u32(fp.a_flags + (long long)peer * sub_per_chunk + sc, fp.epoch);
+        }
+      }
+      // depart: peers may overwrite their chunk only after everybody stopped reading it
+      __threadfence();
+      const uint32_t done = atomicAdd(fp.counter + fp.channel, 1u) + 1u;
+      if (done == (uint32_t)n_ctas) {
+        fp.counter[fp.channel] = 0;
+        __threadfence_system();
+        for (int t = 0; t < W; ++t) st_release_sys_u32(fp.sig[t] + ((size_t)fp.channel * 2 + 1) * 32 + fp.rank, fp.seq);
+        for (int t = 0; t < W; ++t) spin_flag(fp.sig[fp.rank] + ((size_t)fp.channel * 2 + 1) * 32 + t, fp.seq, true);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 0) {
     if (lane == 0) {
       // ===================== TMA producer =====================
       int stage = 0;
@@ -122,8 +254,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
         int m_blk, n_blk;
         tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+        if constexpr (FUSED) m_blk = (m_blk + fp.m_rot) % p.num_m_blocks;
         const int m0 = (m_blk * CG + (int)cta_rank) * kBlockM;
         const int n0 = n_blk * BN + (int)cta_rank * kLoadN;
+        if constexpr (FUSED) {
+          if (fp.a_flags != nullptr && m0 < p.M) {
+            // rows [m0, m0 + 128) of the gathered A: wait until their sub-chunk(s) have landed (local chunk: always)
+            const long long r_last = (long long)(m0 + kBlockM - 1 < p.M ? m0 + kBlockM - 1 : p.M - 1);
+            for (long long f = m0 / fp.rows_per_flag; f <= r_last / fp.rows_per_flag; ++f) {
+              const long long owner = f * fp.rows_per_flag / fp.chunk_rows;
+              if (owner != fp.rank) spin_flag(fp.a_flags + f, fp.epoch, false);
+            }
+            fence_proxy_async_all();
+          }
+        }
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
@@ -199,6 +343,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
       int m_blk, n_blk;
       tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+      if constexpr (FUSED) m_blk = (m_blk + fp.m_rot) % p.num_m_blocks;
       const int row = (m_blk * CG + (int)cta_rank) * kBlockM + quarter * 32 + lane;
       const int n_tile0 = n_blk * BN;
       mbar_wait(tfull_bar(as), aphase);
@@ -206,6 +351,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN;
       const bool row_ok = row < p.M;
       OutT* drow = reinterpret_cast<OutT*>(p.D) + (long long)row * p.ldd;
+      if constexpr (FUSED) {
+        if (fp.d_chunk_rows > 0 && row_ok) {   // GEMM -> reduce-scatter: this row belongs to rank `owner`
+          const long long owner = row / fp.d_chunk_rows;
+          drow = reinterpret_cast<OutT*>(fp.d_ptrs[owner]) +
+                 ((long long)fp.rank * fp.d_chunk_rows + (row - owner * fp.d_chunk_rows)) * p.ldd;
+        }
+      }
       const __nv_bfloat16* rrow = p.residual ? p.residual + (long long)row * p.ldr : nullptr;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
@@ -406,7 +558,8 @@ static int launch_gemm(const void* A, const void* B, const GemmParams& p0, long 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  FusedParams nofuse = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, nofuse));
   return B200_OK;
 }
 
@@ -428,6 +581,60 @@ static int dispatch_cfg(int config, int a_mn, int b_mn, const void* A, const voi
     case 2: return dispatch_major<1, 256, OutT>(a_mn, b_mn, A, B, p, lda, ldb, max_ctas, s);
     default: return dispatch_major<2, 256, OutT>(a_mn, b_mn, A, B, p, lda, ldb, max_ctas, s);
   }
+}
+
+// Fused variants always use the 2-CTA 256x256 configuration, bf16 output.
+template <bool B_MN>
+static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0, long long lda, long long ldb,
+                             const FusedParams& fp, cudaStream_t stream) {
+  constexpr int CG = 2, BN = 256;
+  using Cfg = GemmCfg<CG, BN>;
+  GemmParams p = p0;
+  p.num_m_blocks = ceil_div(p.M, kBlockM * CG);
+  p.num_n_blocks = ceil_div(p.N, BN);
+  p.num_k_blocks = ceil_div(p.K, kBlockK);
+  p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  CUtensorMap ta, tb;
+  {
+    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.M};
+    const uint64_t str[1] = {(uint64_t)lda * 2};
+    const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)kBlockM};
+    if (int rc = b200_make_tmap(&ta, A, 2, 2, dims, str, box, 1)) return rc;
+  }
+  if (!B_MN) {
+    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N};
+    const uint64_t str[1] = {(uint64_t)ldb * 2};
+    const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)Cfg::kLoadN};
+    if (int rc = b200_make_tmap(&tb, B, 2, 2, dims, str, box, 1)) return rc;
+  } else {
+    const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.K};
+    const uint64_t str[1] = {(uint64_t)ldb * 2};
+    const uint32_t box[2] = {64u, (uint32_t)kBlockK};
+    if (int rc = b200_make_tmap(&tb, B, 2, 2, dims, str, box, 1)) return rc;
+  }
+  auto kern = gemm_tcgen05_kernel<CG, BN, false, B_MN, __nv_bfloat16, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int clusters = b200_sm_count() / CG;  // comm clusters + GEMM clusters: all resident (one CTA per SM)
+  if (clusters - fp.n_comm > p.num_tiles) clusters = p.num_tiles + fp.n_comm;
+  if (clusters <= fp.n_comm) clusters = fp.n_comm + 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(clusters * CG);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  return B200_OK;
 }
 
 // Wave-quantisation-aware choice between the three tile configurations.
@@ -495,4 +702,78 @@ B200_API int b200_gemm_bf16(const void* A, const void* B, void* D, int M, int N,
     return dispatch_cfg<float>(config, a_mn_major, b_mn_major, A, B, p, lda, ldb, max_ctas, stream);
   return dispatch_cfg<__nv_bfloat16>(config, a_mn_major, b_mn_major, A, B, p, lda, ldb, max_ctas,
                                      stream);
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// Fused all-gather -> GEMM  (ColwiseParallel after a sequence-parallel region).
+//   D[M, N] = act(X_full . B^T + bias) + residual, where X_full [M, K] is the concatenation over ranks of the
+//   [M / world, K] chunks each rank wrote into ITS copy of a symmetric buffer (a_ptrs[r] = rank r's buffer as mapped
+//   here; this rank's chunk must already sit at rows [rank * M/world, ...) of a_ptrs[rank]).  Communication CTAs inside
+//   the GEMM grid pull the peers' chunks over NVLink while the tensor cores start on the local chunk.
+//   flags: local uint32[M / rows_per_flag] (zero-initialised once); epoch/seq must increase on every call per channel.
+//   Requirements: K % 8 == 0, (M / world) % 256 == 0, (M / world) % rows_per_flag == 0, bf16.
+B200_API int b200_ag_gemm_bf16(const void* const* a_ptrs, const void* B, void* D, int M, int N, int K, long long ldb,
+                               long long ldd, int b_mn_major, const void* bias, const void* residual, long long ldr,
+                               int act, void* flags, int rows_per_flag, unsigned epoch, int n_comm_clusters,
+                               const void* const* sig_ptrs, void* counter, int channel, unsigned seq, int world,
+                               int rank, cudaStream_t stream) {
+  using namespace b200;
+  if (world < 1 || world > 8 || M % world || (M / world) % 256 || (M / world) % rows_per_flag || (K & 7) || (N & 7)) {
+    b200_set_error("ag_gemm: unsupported geometry M=%d N=%d K=%d world=%d rows_per_flag=%d", M, N, K, world, rows_per_flag);
+    return B200_ERR_SHAPE;
+  }
+  GemmParams p = {};
+  p.M = M; p.N = N; p.K = K; p.D = D; p.ldd = ldd;
+  p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
+  p.ldr = ldr; p.alpha = 1.f; p.act = act; p.accumulate = 0;
+  FusedParams fp = {};
+  fp.a_flags = reinterpret_cast<uint32_t*>(flags);
+  fp.rows_per_flag = rows_per_flag;
+  fp.epoch = epoch;
+  fp.n_comm = world > 1 ? (n_comm_clusters > 0 ? n_comm_clusters : 4) : 0;
+  for (int i = 0; i < world; ++i) {
+    fp.a_src[i] = a_ptrs[i];
+    fp.sig[i] = reinterpret_cast<uint32_t*>(const_cast<void*>(sig_ptrs[i]));
+  }
+  fp.a_dst = const_cast<void*>(a_ptrs[rank]);
+  fp.chunk_rows = M / world;
+  fp.row_bytes = (long long)K * 2;
+  fp.counter = reinterpret_cast<uint32_t*>(counter);
+  fp.channel = channel; fp.seq = seq; fp.world = world; fp.rank = rank;
+  fp.d_chunk_rows = 0;
+  fp.m_rot = (int)((long long)rank * (M / world) / (kBlockM * 2));  // start with the local chunk
+  if (world == 1) fp.a_flags = nullptr;
+  if (b_mn_major) return launch_gemm_fused<true>(a_ptrs[rank], B, p, K, ldb, fp, stream);
+  return launch_gemm_fused<false>(a_ptrs[rank], B, p, K, ldb, fp, stream);
+}
+
+// Fused GEMM -> reduce-scatter, step 1  (RowwiseParallel with sequence-sharded output; rows A7, A10, A12).
+//   partial[M, N] = A . B^T is never materialised locally: each output row is stored into the staging buffer of the
+//   rank that owns it, at slab `rank` (stage_ptrs[o] = rank o's staging [world, M / world, N] bf16, row stride N).
+//   Follow with b200_comm_slab_reduce on every rank to obtain the reduced [M / world, N] chunk.
+//   `residual` (optional, local [M, N] bf16, row stride ldr) is added to the partial before it is scattered.
+B200_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* stage_ptrs, int M, int N, int K,
+                               long long lda, long long ldb, int b_mn_major, const void* residual, long long ldr,
+                               int world, int rank, cudaStream_t stream) {
+  using namespace b200;
+  if (world < 1 || world > 8 || M % world || (K & 7) || (N & 7) || (lda & 7) || (ldb & 7)) {
+    b200_set_error("gemm_rs: unsupported geometry M=%d N=%d K=%d world=%d", M, N, K, world);
+    return B200_ERR_SHAPE;
+  }
+  GemmParams p = {};
+  p.M = M; p.N = N; p.K = K; p.D = const_cast<void*>(stage_ptrs[rank]); p.ldd = N;
+  p.alpha = 1.f;
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
+  p.ldr = ldr;
+  FusedParams fp = {};
+  fp.n_comm = 0;
+  fp.world = world; fp.rank = rank;
+  for (int i = 0; i < world; ++i) fp.d_ptrs[i] = const_cast<void*>(stage_ptrs[i]);
+  fp.d_chunk_rows = M / world;
+  const int blocks_per_chunk = ceil_div(M / world, kBlockM * 2);
+  fp.m_rot = ((rank + 1) % world) * blocks_per_chunk;  // first the neighbour's rows, own rows last
+  if (b_mn_major) return launch_gemm_fused<true>(A, B, p, lda, ldb, fp, stream);
+  return launch_gemm_fused<false>(A, B, p, lda, ldb, fp, stream);
 }
