@@ -75,7 +75,7 @@ def _default_units(module: nn.Module):
 class FSDP(nn.Module):
     def __init__(self, module: nn.Module, process_group=None, units: Optional[List] = None,
                  reshard_after_forward: bool = True, fused_optimizer: bool = True,
-                 comm_max_ctas: int = 32, sync_module_states: bool = True):
+                 comm_max_ctas: int = 64, sync_module_states: bool = True):
         super().__init__()
         self.module = module
         self.comm = get_communicator(process_group)

@@ -148,15 +148,15 @@ template <typename T> struct Acc8 {
 // Sum `world` peers' 8-element chunks at element offset `off` for kU consecutive grid-strided chunks:
 // all kU * world 128-bit (bf16) / 2x128-bit (fp32) loads are issued before the first add, so one
 // thread keeps kU * world NVLink requests in flight (latency ~2 us needs ~1 MB in flight per GPU).
-template <typename T, int kU>
+template <typename T, int kU, int kW = kMaxRanks>
 __device__ __forceinline__ void peer_sum(const CommCtx& c, long long off, const long long (&idx)[kU],
                                          const bool (&ok)[kU], float (&acc)[kU][8]) {
   constexpr int kV = sizeof(T) == 2 ? 1 : 2;
-  uint4 raw[kU][kMaxRanks][kV];
+  uint4 raw[kU][kW][kV];
 #pragma unroll
   for (int u = 0; u < kU; ++u)
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t)
+    for (int t = 0; t < kW; ++t)
       if (t < c.world && ok[u]) {
         const T* p = reinterpret_cast<const T*>(c.data[(t + c.rank) % c.world]) + off + idx[u] * 8;
 #pragma unroll
@@ -167,7 +167,7 @@ __device__ __forceinline__ void peer_sum(const CommCtx& c, long long off, const 
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t)
+    for (int t = 0; t < kW; ++t)
       if (t < c.world && ok[u]) {
         if constexpr (sizeof(T) == 2) {
           const uint4 r = raw[u][t][0];
@@ -196,10 +196,11 @@ __global__ void __launch_bounds__(512, 1) comm_allgather_kernel(CommCtx c, uint4
   comm_arrive_and_wait(c);
   const long long total = n16 * c.world;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += stride * 4) {
-    uint4 v[4];
+  constexpr int kAgU = 16;  // 256 bytes in flight per thread
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += stride * kAgU) {
+    uint4 v[kAgU];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kAgU; ++u) {
       const long long k = i + u * stride;
       if (k < total) {
         const int t = (int)(k / n16);
@@ -208,7 +209,7 @@ __global__ void __launch_bounds__(512, 1) comm_allgather_kernel(CommCtx c, uint4
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kAgU; ++u) {
       const long long k = i + u * stride;
       if (k < total) {
         const int t = (int)(k / n16);
@@ -222,12 +223,12 @@ __global__ void __launch_bounds__(512, 1) comm_allgather_kernel(CommCtx c, uint4
 
 // ------------------------------ reduce-scatter (pull) ------------------------
 // out[i] = scale * sum_t peer t's data[in_off + rank * n + i],  i in [0, n)  (n in elements, % 8 == 0)
-template <typename TIn, typename TOut>
+template <typename TIn, typename TOut, int kW>
 __global__ void __launch_bounds__(512, 1) comm_reducescatter_kernel(CommCtx c, TOut* __restrict__ out, long long in_off,
                                           long long n, float scale) {
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
-  constexpr int kU = sizeof(TIn) == 2 ? 2 : 1;
+  constexpr int kU = (sizeof(TIn) == 2 ? 16 : 8) / kW;   // ~16 peer requests in flight per thread
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
     long long idx[kU];
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(512, 1) comm_reducescatter_kernel(CommCtx c, T
     float acc[kU][8];
 #pragma unroll
     for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < n8; }
-    peer_sum<TIn, kU>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc);
 #pragma unroll
     for (int u = 0; u < kU; ++u)
       if (ok[u]) {
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(512, 1) comm_reducescatter_kernel(CommCtx c, T
 
 // reduce-scatter fused with the sharded AdamW step (FSDP gradient path):
 // the summed gradient never touches HBM; master weight, moments and the bf16 shard are updated in place.
-template <typename TIn>
+template <typename TIn, int kW>
 __global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long long in_off, long long n, float grad_scale,
                                      float* __restrict__ master, __nv_bfloat16* __restrict__ lowp,
                                      float* __restrict__ m, float* __restrict__ v, float lr, float beta1,
@@ -257,7 +258,7 @@ __global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long l
   comm_arrive_and_wait(c);
   const long long n8 = n >> 3;
   const float step_size = lr / bc1, decay = 1.f - lr * wd;
-  constexpr int kU = sizeof(TIn) == 2 ? 2 : 1;
+  constexpr int kU = (sizeof(TIn) == 2 ? 16 : 8) / kW;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n8; i0 += stride * kU) {
     long long idx[kU];
@@ -265,7 +266,7 @@ __global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long l
     float acc[kU][8];
 #pragma unroll
     for (int u = 0; u < kU; ++u) { idx[u] = i0 + u * stride; ok[u] = idx[u] < n8; }
-    peer_sum<TIn, kU>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc);
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       if (!ok[u]) continue;
@@ -507,7 +508,7 @@ B200_API int b200_comm_allgather(COMM_ARGS, void* out, long long in_off_bytes, l
   COMM_CHECK_WORLD();
   if ((bytes | in_off_bytes) & 15) { b200_set_error("allgather: sizes must be multiples of 16 bytes"); return B200_ERR_SHAPE; }
   const long long n16 = bytes >> 4;
-  comm_allgather_kernel<<<comm_grid(n16 * world / 4, 512, max_ctas), 512, 0, stream>>>(
+  comm_allgather_kernel<<<comm_grid(n16 * world / 16, 512, max_ctas), 512, 0, stream>>>(
       COMM_CTX, (uint4*)out, in_off_bytes >> 4, n16);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -519,7 +520,12 @@ B200_API int b200_comm_reducescatter(COMM_ARGS, void* out, long long in_off, lon
   COMM_CHECK_WORLD();
   if (n & 7) { b200_set_error("reducescatter: shard elements must be a multiple of 8"); return B200_ERR_SHAPE; }
   const int grid = comm_grid(n >> 3, 512, max_ctas);
-#define RS(TI, TO) comm_reducescatter_kernel<TI, TO><<<grid, 512, 0, stream>>>(COMM_CTX, (TO*)out, in_off, n, scale)
+#define RS(TI, TO)                                                                                            \
+  do {                                                                                                        \
+    if (world <= 2) comm_reducescatter_kernel<TI, TO, 2><<<grid, 512, 0, stream>>>(COMM_CTX, (TO*)out, in_off, n, scale);      \
+    else if (world <= 4) comm_reducescatter_kernel<TI, TO, 4><<<grid, 512, 0, stream>>>(COMM_CTX, (TO*)out, in_off, n, scale); \
+    else comm_reducescatter_kernel<TI, TO, 8><<<grid, 512, 0, stream>>>(COMM_CTX, (TO*)out, in_off, n, scale);                 \
+  } while (0)
   if (in_dtype == 0 && out_dtype == 0) RS(__nv_bfloat16, __nv_bfloat16);
   else if (in_dtype == 0 && out_dtype == 1) RS(__nv_bfloat16, float);
   else if (in_dtype == 1 && out_dtype == 1) RS(float, float);
@@ -537,12 +543,11 @@ B200_API int b200_comm_rs_adamw(COMM_ARGS, long long in_off, long long n, float 
   COMM_CHECK_WORLD();
   if (n & 7) { b200_set_error("rs_adamw: shard elements must be a multiple of 8"); return B200_ERR_SHAPE; }
   const int grid = comm_grid(n >> 3, 512, max_ctas);
-  if (in_dtype == 0)
-    comm_rs_adamw_kernel<__nv_bfloat16><<<grid, 512, 0, stream>>>(COMM_CTX, in_off, n, grad_scale, master,
-        (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, sqrtf(bc2));
-  else
-    comm_rs_adamw_kernel<float><<<grid, 512, 0, stream>>>(COMM_CTX, in_off, n, grad_scale, master,
-        (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, sqrtf(bc2));
+#define RSA(TI, KW) comm_rs_adamw_kernel<TI, KW><<<grid, 512, 0, stream>>>(COMM_CTX, in_off, n, grad_scale, master, \
+        (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, sqrtf(bc2))
+  if (in_dtype == 0) { if (world <= 2) RSA(__nv_bfloat16, 2); else if (world <= 4) RSA(__nv_bfloat16, 4); else RSA(__nv_bfloat16, 8); }
+  else { if (world <= 2) RSA(float, 2); else if (world <= 4) RSA(float, 4); else RSA(float, 8); }
+#undef RSA
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -14,7 +14,7 @@
 
 namespace b200 {
 
-constexpr int kFbThreads = 192;
+constexpr int kFbThreads = 320;  // loader + MMA warps, 8 compute warps (two per TMEM lane quarter, 64 columns each)
 constexpr int kFbBlock = 128;
 
 struct AttnBwdParams {
@@ -116,7 +116,7 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
     tma_prefetch_desc(&tmap_v); tma_prefetch_desc(&tmap_do);
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
-    mbar_init(sdp_full, 1); mbar_init(pds_ready, 4); mbar_init(acc_done, 1);
+    mbar_init(sdp_full, 1); mbar_init(pds_ready, 8); mbar_init(acc_done, 1);
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc<1>(tmem_ptr_addr, 512); tmem_relinquish<1>(); }
@@ -188,8 +188,9 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
     __syncwarp();
   } else {
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;            // which 64 query columns of the 128-wide tile this warp handles
     const int row = quarter * 32 + lane;         // key row inside the block
-    const int ct = (warp - 2) * 32 + lane;       // 0..127 index among compute threads
+    const int ct = (warp - 2) * 32 + lane;       // 0..255 index among compute threads
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
     const float sl2 = a.scale * kLog2e;
     const int kv_pos = kv0 + row + a.k_offset - a.q_offset;  // visible to query q iff kv_pos <= q
@@ -199,25 +200,27 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const int q0 = (i_start + it % per_head) * kFbBlock;
       // stage LSE / delta for this query block (the buffer of iteration it-2 is free: its
       // readers all passed pds_ready(it-2) before sdp_full(it-1) could complete)
-      {
+      if (ct < 128) {
         const int q = q0 + ct;
         const long long off = ((long long)b * a.H + h) * a.Sq + q;
         float l_ = q < a.Sq ? p.LSE[off] : INFINITY;
         s_lse[st * 128 + ct] = (l_ == -INFINITY) ? INFINITY : l_ * kLog2e;  // empty rows: P = 0
         s_delta[st * 128 + ct] = q < a.Sq ? p.Delta[off] : 0.f;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       const bool need_mask = a.causal && (q0 + a.q_offset < kv0 + kFbBlock - 1 + a.k_offset);
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
-      const float* lse_s = s_lse + st * 128;
-      const float* del_s = s_delta + st * 128;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t rs[32], rd[32];
-        tmem_ld_32x32(tS + lane_off + c * 32, rs);
-        tmem_ld_32x32(tDP + lane_off + c * 32, rd);
-        tmem_ld_wait();
+      const float* lse_s = s_lse + st * 128 + half * 64;
+      const float* del_s = s_delta + st * 128 + half * 64;
+      const uint32_t cs = tS + lane_off + half * 64, cd = tDP + lane_off + half * 64;
+      uint32_t rs0[32], rs1[32], rd0[32], rd1[32];
+      tmem_ld_32x32(cs, rs0);
+      tmem_ld_32x32(cs + 32, rs1);
+      tmem_ld_32x32(cd, rd0);
+      tmem_ld_32x32(cd + 32, rd1);
+      tmem_ld_wait();
+      auto chunk = [&](uint32_t (&rs)[32], uint32_t (&rd)[32], int c) {
         uint32_t pk[16], dk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
@@ -225,17 +228,22 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
           float p0 = exp2f(fmaf(__uint_as_float(rs[i]), sl2, -lse_s[q]));
           float p1 = exp2f(fmaf(__uint_as_float(rs[i + 1]), sl2, -lse_s[q + 1]));
           if (need_mask) {
-            if (kv_pos > q0 + q) p0 = 0.f;
-            if (kv_pos > q0 + q + 1) p1 = 0.f;
+            if (kv_pos > q0 + half * 64 + q) p0 = 0.f;
+            if (kv_pos > q0 + half * 64 + q + 1) p1 = 0.f;
           }
           const float d0 = p0 * (__uint_as_float(rd[i]) - del_s[q]);
           const float d1 = p1 * (__uint_as_float(rd[i + 1]) - del_s[q + 1]);
           pk[i >> 1] = pack_bf16(p0, p1);
           dk[i >> 1] = pack_bf16(d0, d1);
         }
-        tmem_st_32x16(tS + lane_off + c * 16, pk);
-        tmem_st_32x16(tDP + lane_off + c * 16, dk);
-      }
+        tmem_st_32x16(tS + lane_off + half * 32 + c * 16, pk);
+        tmem_st_32x16(tDP + lane_off + half * 32 + c * 16, dk);
+      };
+      // NOTE: P / dS (bf16, 64 columns in total) alias the first 64 fp32 columns of S / dP.  Half 1 reads columns
+      // 64..127 but writes 32..63, which half 0 still reads: everybody finishes reading before anybody writes.
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      chunk(rs0, rd0, 0);
+      chunk(rs1, rd1, 1);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -249,7 +257,7 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
       mbar_wait(acc_done, 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = half; c < HD / 32; c += 2) {
         uint32_t r[32];
         tmem_ld_32x32(tDV + lane_off + c * 32, r);
         tmem_ld_wait();
@@ -258,7 +266,7 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
         tmem_ld_wait();
         if (kv < a.Sk) store_chunk_bf16(dkrow + c * 32, r, a.scale);
       }
-    } else if (kv < a.Sk) {
+    } else if (kv < a.Sk && half == 0) {
       for (int c = 0; c < HD / 8; ++c) {
         st_v4(dkrow + c * 8, make_uint4(0, 0, 0, 0));
         st_v4(dvrow + c * 8, make_uint4(0, 0, 0, 0));
@@ -309,7 +317,7 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
     tma_prefetch_desc(&tmap_v); tma_prefetch_desc(&tmap_do);
     mbar_init(qdo_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 1); }
-    mbar_init(sdp_full, 1); mbar_init(ds_ready, 4); mbar_init(acc_done, 1);
+    mbar_init(sdp_full, 1); mbar_init(ds_ready, 8); mbar_init(acc_done, 1);
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc<1>(tmem_ptr_addr, 512); tmem_relinquish<1>(); }
@@ -375,6 +383,7 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
     __syncwarp();
   } else {
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = quarter * 32 + lane;
     const int q_idx = q0 + row;
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
@@ -390,27 +399,31 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
                              (a.causal && (kv0 + kFbBlock - 1 > q0 + a.q_offset - a.k_offset));
       mbar_wait(sdp_full, j & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t rs[32], rd[32];
-        tmem_ld_32x32(tS + lane_off + c * 32, rs);
-        tmem_ld_32x32(tDP + lane_off + c * 32, rd);
-        tmem_ld_wait();
+      const uint32_t cs = tS + lane_off + half * 64, cd = tDP + lane_off + half * 64;
+      uint32_t rs0[32], rs1[32], rd0[32], rd1[32];
+      tmem_ld_32x32(cs, rs0);
+      tmem_ld_32x32(cs + 32, rs1);
+      tmem_ld_32x32(cd, rd0);
+      tmem_ld_32x32(cd + 32, rd1);
+      tmem_ld_wait();
+      auto chunk = [&](uint32_t (&rs)[32], uint32_t (&rd)[32], int c) {
         uint32_t dk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           float p0 = exp2f(fmaf(__uint_as_float(rs[i]), sl2, -lse2));
           float p1 = exp2f(fmaf(__uint_as_float(rs[i + 1]), sl2, -lse2));
           if (need_mask) {
-            const int col = kv0 + c * 32 + i;
+            const int col = kv0 + half * 64 + c * 32 + i;
             if (!(col < a.Sk && (!a.causal || col <= q_pos))) p0 = 0.f;
             if (!(col + 1 < a.Sk && (!a.causal || col + 1 <= q_pos))) p1 = 0.f;
           }
-          dk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rd[i]) - delta),
-                                 p1 * (__uint_as_float(rd[i + 1]) - delta));
+          dk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rd[i]) - delta), p1 * (__uint_as_float(rd[i + 1]) - delta));
         }
-        tmem_st_32x16(tDP + lane_off + c * 16, dk);
-      }
+        tmem_st_32x16(tDP + lane_off + half * 32 + c * 16, dk);
+      };
+      asm volatile("bar.sync 2, 256;" ::: "memory");  // dS aliases dP columns another warp may still be reading
+      chunk(rs0, rd0, 0);
+      chunk(rs1, rd1, 1);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -421,13 +434,13 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
       mbar_wait(acc_done, 0);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = half; c < HD / 32; c += 2) {
         uint32_t r[32];
         tmem_ld_32x32(tDQ + lane_off + c * 32, r);
         tmem_ld_wait();
         if (q_idx < a.Sq) store_chunk_bf16(dqrow + c * 32, r, a.scale);
       }
-    } else if (q_idx < a.Sq) {
+    } else if (q_idx < a.Sq && half == 0) {
       for (int c = 0; c < HD / 8; ++c) st_v4(dqrow + c * 8, make_uint4(0, 0, 0, 0));
     }
   }

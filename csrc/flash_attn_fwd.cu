@@ -1,12 +1,14 @@
-// Flash-attention forward on tcgen05: S = Q K^T and O += P V both run on the 5th-gen
-// tensor cores with S/P and O resident in TMEM; K/V tiles stream through a TMA ring.
-//   warp 0   : TMA loader (Q once, K/V double-buffered)
-//   warp 1   : MMA issuer  (QK^T for block j+1 is issued before PV of block j, so the
-//              tensor cores work on the next scores while softmax handles the current ones)
-//   warp 2-5 : softmax, one thread per query row (TMEM lane == row: no shuffles), writes P
-//              as packed bf16 back INTO the S columns (TS-MMA reads A from TMEM), and rescales
-//              O lazily (only when the running max moves by more than 2^8).
-// Returns O (bf16) and LSE (fp32); q_offset/k_offset let ring-attention call it on chunks.
+// Flash-attention forward on tcgen05: S = Q K^T and O += P V both run on the 5th-gen tensor cores with S/P and O
+// resident in TMEM; K/V tiles stream through a TMA ring.  One CTA owns 256 query rows as two 128-row tiles that
+// ping-pong on the tensor cores (while tile A's softmax runs on the CUDA cores, tile B's MMAs run, and vice versa):
+//   warp 0    : TMA loader (both Q tiles once, K/V double-buffered, shared by the two tiles)
+//   warp 1    : MMA issuer: PV_A(j), QK_A(j+1), PV_B(j), QK_B(j+1), ... (one thread, in-order tensor pipe)
+//   warp 2-5  : softmax of tile A, warp 6-9: softmax of tile B.  One thread per query row (TMEM lane == row, no
+//               shuffles); the whole 128-wide score row is read into registers with four back-to-back tcgen05.ld,
+//               P goes back INTO the S columns as packed bf16 (the PV MMA reads its A operand from TMEM), and O is
+//               rescaled lazily (only when the running max moves by more than 2^8).
+// TMEM: S_A | S_B | O_A | O_B = 4 x 128 columns.  Returns O (bf16) and LSE (fp32); q_offset / k_offset let ring
+// attention call it on chunks.
 //
 // Replaces F.scaled_dot_product_attention(q, k, v, is_causal=True)
 //   (/root/reference/fsdp_tp/llama2_model.py:218-223) and the explicit softmax(QK^T)V of
@@ -15,14 +17,15 @@
 
 namespace b200 {
 
-constexpr int kFaThreads = 192;
-constexpr int kFaBlock = 128;  // query rows per CTA == keys per KV block
+constexpr int kFaThreads = 320;
+constexpr int kFaBlock = 128;   // rows per tile == keys per KV block
+constexpr int kFaTiles = 2;     // query tiles per CTA
 
 template <int HD>
 struct FaCfg {
   static constexpr int kHalves = HD / 64;
   static constexpr int kTileBytes = kFaBlock * HD * 2;
-  static constexpr int kSmemBytes = 5 * kTileBytes + 1024 + 256;  // Q + 2 K + 2 V
+  static constexpr int kSmemBytes = 6 * kTileBytes + 1024 + 256;  // 2 Q + 2 K + 2 V
 };
 
 template <int HD>
@@ -34,33 +37,39 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
   constexpr int kTile = Cfg::kTileBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = smem_base;
-  auto sK = [&](int s) { return smem_base + kTile * (1 + s); };
-  auto sV = [&](int s) { return smem_base + kTile * (3 + s); };
-  const uint32_t bar = smem_base + 5 * kTile;
+  auto sQ = [&](int t) { return smem_base + kTile * t; };
+  auto sK = [&](int s) { return smem_base + kTile * (2 + s); };
+  auto sV = [&](int s) { return smem_base + kTile * (4 + s); };
+  const uint32_t bar = smem_base + 6 * kTile;
   const uint32_t q_full = bar;
   auto k_full = [&](int s) { return bar + 8u * (1 + s); };
   auto k_empty = [&](int s) { return bar + 8u * (3 + s); };
   auto v_full = [&](int s) { return bar + 8u * (5 + s); };
   auto v_empty = [&](int s) { return bar + 8u * (7 + s); };
-  auto s_full = [&](int s) { return bar + 8u * (9 + s); };
-  auto p_ready = [&](int s) { return bar + 8u * (11 + s); };
-  auto pv_done = [&](int s) { return bar + 8u * (13 + s); };
+  auto s_full = [&](int t) { return bar + 8u * (9 + t); };
+  auto p_ready = [&](int t) { return bar + 8u * (11 + t); };
+  auto pv_done = [&](int t) { return bar + 8u * (13 + t); };
   const uint32_t tmem_ptr_addr = bar + 8u * 15;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
   const int h = blockIdx.y, b = blockIdx.z;
   const int hk = h / (p.H / p.Hkv);
-  const int q0 = q_blk * kFaBlock;
+  const int q_base = q_blk * kFaBlock * kFaTiles;
 
-  // number of KV blocks this query block attends to
-  int kv_limit = p.Sk;
-  if (p.causal) {
-    const int lim = q0 + kFaBlock - 1 + p.q_offset - p.k_offset + 1;
-    kv_limit = lim < kv_limit ? lim : kv_limit;
+  // KV blocks each tile attends to
+  int n_blk[kFaTiles];
+#pragma unroll
+  for (int t = 0; t < kFaTiles; ++t) {
+    const int q0 = q_base + t * kFaBlock;
+    int lim = p.Sk;
+    if (p.causal) {
+      const int c = q0 + kFaBlock + p.q_offset - p.k_offset;
+      lim = c < lim ? c : lim;
+    }
+    n_blk[t] = (q0 < p.Sq && lim > 0) ? (lim + kFaBlock - 1) / kFaBlock : 0;
   }
-  const int n_blocks = kv_limit > 0 ? (kv_limit + kFaBlock - 1) / kFaBlock : 0;
+  const int n_max = n_blk[0] > n_blk[1] ? n_blk[0] : n_blk[1];
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -83,16 +92,19 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_addr));
-  const uint32_t tO = tmem_base + 256;
+  auto tS = [&](int t) { return tmem_base + t * 128; };
+  auto tO = [&](int t) { return tmem_base + 256 + t * 128; };
 
   if (warp == 0) {
-    if (lane == 0 && n_blocks > 0) {
+    if (lane == 0 && n_max > 0) {
       // ===================== loader =====================
-      mbar_expect_tx(q_full, kTile);
+      mbar_expect_tx(q_full, kFaTiles * kTile);   // rows past Sq are zero-filled by TMA
 #pragma unroll
-      for (int hh = 0; hh < Cfg::kHalves; ++hh)
-        tma_load_4d(sQ + hh * 16384, &tmap_q, q_full, hh * 64, q0, h, b, kEvictFirst);
-      for (int j = 0; j < n_blocks; ++j) {
+      for (int t = 0; t < kFaTiles; ++t)
+#pragma unroll
+        for (int hh = 0; hh < Cfg::kHalves; ++hh)
+          tma_load_4d(sQ(t) + hh * 16384, &tmap_q, q_full, hh * 64, q_base + t * kFaBlock, h, b, kEvictFirst);
+      for (int j = 0; j < n_max; ++j) {
         const int st = j & 1;
         const uint32_t par = ((j >> 1) & 1) ^ 1u;
         const int kv0 = j * kFaBlock;
@@ -110,79 +122,101 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && n_blocks > 0) {
+    if (lane == 0 && n_max > 0) {
       // ===================== MMA issuer =====================
       constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, HD, false, true);
-      auto issue_qk = [&](int j) {
+      auto issue_qk = [&](int t, int j) {
         const int st = j & 1;
-        mbar_wait(k_full(st), (j >> 1) & 1);
-        tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
           const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tmem_base + st * 128, umma_smem_desc_sw128(sQ + off, 16, 1024),
+          umma_f16_ss<1>(tS(t), umma_smem_desc_sw128(sQ(t) + off, 16, 1024),
                          umma_smem_desc_sw128(sK(st) + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
         }
-        umma_commit(s_full(st));
-        umma_commit(k_empty(st));
+        umma_commit(s_full(t));
+      };
+      auto issue_pv = [&](int t, int j) {
+        const int st = j & 1;
+#pragma unroll
+        for (int kk = 0; kk < kFaBlock / 16; ++kk)
+          umma_f16_ts<1>(tO(t), tS(t) + kk * 8, umma_smem_desc_sw128(sV(st) + kk * 2048, 16384, 1024), idesc_pv,
+                         (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(pv_done(t));
       };
       mbar_wait(q_full, 0);
-      issue_qk(0);
-      for (int j = 0; j < n_blocks; ++j) {
-        const int st = j & 1;
-        if (j + 1 < n_blocks) issue_qk(j + 1);
-        mbar_wait(p_ready(st), (j >> 1) & 1);
-        mbar_wait(v_full(st), (j >> 1) & 1);
-        tc_fence_after();
+      mbar_wait(k_full(0), 0);
+      tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < kFaBlock / 16; ++kk) {
-          umma_f16_ts<1>(tO, tmem_base + st * 128 + kk * 8,
-                         umma_smem_desc_sw128(sV(st) + kk * 2048, 16384, 1024), idesc_pv,
-                         (j > 0 || kk > 0) ? 1u : 0u);
+      for (int t = 0; t < kFaTiles; ++t)
+        if (n_blk[t] > 0) issue_qk(t, 0);
+      umma_commit(k_empty(0));
+      for (int j = 0; j < n_max; ++j) {
+        const int st = j & 1;
+        const bool more = j + 1 < n_max;
+        if (more) {
+          mbar_wait(k_full((j + 1) & 1), ((j + 1) >> 1) & 1);
+        }
+        mbar_wait(v_full(st), (j >> 1) & 1);
+#pragma unroll
+        for (int t = 0; t < kFaTiles; ++t) {
+          if (j < n_blk[t]) {
+            mbar_wait(p_ready(t), j & 1);
+            tc_fence_after();
+            issue_pv(t, j);
+            if (j + 1 < n_blk[t]) issue_qk(t, j + 1);   // overwrites S_t/P_t only after PV_t(j) (in-order pipe)
+          }
         }
         umma_commit(v_empty(st));
-        umma_commit(pv_done(st));
+        if (more) umma_commit(k_empty((j + 1) & 1));
       }
     }
     __syncwarp();
   } else {
     // ===================== softmax / correction / epilogue =====================
+    const int t = (warp - 2) >> 2;           // which query tile this warpgroup owns
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
+    const int q0 = q_base + t * kFaBlock;
     const int q_idx = q0 + row;
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
     const float sl2 = p.scale * kLog2e;
     float m_used = -INFINITY;  // max used for scaling (raw score units)
     float l_run = 0.f;
     const int q_pos = q_idx + p.q_offset - p.k_offset;  // key j visible iff j <= q_pos (causal)
+    const int nb = n_blk[t];
+    const uint32_t s_addr = tS(t) + lane_off;
+    const uint32_t o_addr = tO(t) + lane_off;
 
-    for (int j = 0; j < n_blocks; ++j) {
-      const int st = j & 1;
+    for (int j = 0; j < nb; ++j) {
       const int kv0 = j * kFaBlock;
       const bool need_mask = (kv0 + kFaBlock > p.Sk) ||
                              (p.causal && (kv0 + kFaBlock - 1 > q0 + p.q_offset - p.k_offset));
-      mbar_wait(s_full(st), (j >> 1) & 1);
+      mbar_wait(s_full(t), j & 1);
       tc_fence_after();
-      const uint32_t tS = tmem_base + lane_off + st * 128;
-      // ---- pass 1: block row max ----
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + c * 32, r);
-        tmem_ld_wait();
-        if (need_mask) {
+      // ---- whole score row into registers: four loads in flight, one wait ----
+      uint32_t r0[32], r1[32], r2[32], r3[32];
+      tmem_ld_32x32(s_addr, r0);
+      tmem_ld_32x32(s_addr + 32, r1);
+      tmem_ld_32x32(s_addr + 64, r2);
+      tmem_ld_32x32(s_addr + 96, r3);
+      tmem_ld_wait();
+      if (need_mask) {
+        const uint32_t ninf = __float_as_uint(-INFINITY);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int col = kv0 + c * 32 + i;
-            const bool ok = col < p.Sk && (!p.causal || col <= q_pos);
-            mx = fmaxf(mx, ok ? __uint_as_float(r[i]) : -INFINITY);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        for (int i = 0; i < 32; ++i) {
+          const int c = kv0 + i;
+          if (!(c < p.Sk && (!p.causal || c <= q_pos))) r0[i] = ninf;
+          if (!(c + 32 < p.Sk && (!p.causal || c + 32 <= q_pos))) r1[i] = ninf;
+          if (!(c + 64 < p.Sk && (!p.causal || c + 64 <= q_pos))) r2[i] = ninf;
+          if (!(c + 96 < p.Sk && (!p.causal || c + 96 <= q_pos))) r3[i] = ninf;
         }
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(r0[i]), __uint_as_float(r1[i])),
+                             fmaxf(__uint_as_float(r2[i]), __uint_as_float(r3[i]))));
       }
       // ---- lazy rescale decision ----
       float alpha = 1.f;
@@ -194,62 +228,55 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
       l_run *= alpha;
       if (j > 0 && __any_sync(0xffffffffu, rescale)) {
-        const int pj = j - 1;
-        mbar_wait(pv_done(pj & 1), (pj >> 1) & 1);
+        mbar_wait(pv_done(t), (j - 1) & 1);
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < HD / 32; ++c) {
           uint32_t r[32];
-          tmem_ld_32x32(tO + lane_off + c * 32, r);
+          tmem_ld_32x32(o_addr + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x32(tO + lane_off + c * 32, r);
+          tmem_st_32x32(o_addr + c * 32, r);
         }
         tmem_st_wait();
       }
-      // ---- pass 2: P = exp2((S - m) * scale), row sum, packed bf16 back into the S columns ----
+      // ---- P = exp2((S - m) * scale), row sum, packed bf16 back into the S columns ----
       const float mneg = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
       float lsum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + c * 32, r);
-        tmem_ld_wait();
+      auto do_chunk = [&](uint32_t (&r)[32], int c) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-          float p0 = exp2f(fmaf(s0, sl2, mneg)), p1 = exp2f(fmaf(s1, sl2, mneg));
-          if (need_mask) {
-            const int col = kv0 + c * 32 + i;
-            if (!(col < p.Sk && (!p.causal || col <= q_pos))) p0 = 0.f;
-            if (!(col + 1 < p.Sk && (!p.causal || col + 1 <= q_pos))) p1 = 0.f;
-          }
+          const float p0 = exp2f(fmaf(__uint_as_float(r[i]), sl2, mneg));      // exp2(-inf) == 0 for masked keys
+          const float p1 = exp2f(fmaf(__uint_as_float(r[i + 1]), sl2, mneg));
           lsum += p0 + p1;
           pk[i >> 1] = pack_bf16(p0, p1);
         }
-        tmem_st_32x16(tS + c * 16, pk);
-      }
+        tmem_st_32x16(s_addr + c * 16, pk);
+      };
+      do_chunk(r0, 0);
+      do_chunk(r1, 1);
+      do_chunk(r2, 2);
+      do_chunk(r3, 3);
       l_run += lsum;
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_ready(st));
+      if (lane == 0) mbar_arrive(p_ready(t));
     }
 
     // ---- epilogue: O / l -> bf16 global, LSE ----
     __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.O) + (long long)b * p.o_sb +
                           (long long)q_idx * p.o_ss + (long long)h * p.o_sh;
-    if (n_blocks > 0) {
-      const int lj = n_blocks - 1;
-      mbar_wait(pv_done(lj & 1), (lj >> 1) & 1);
+    if (nb > 0) {
+      mbar_wait(pv_done(t), (nb - 1) & 1);
       tc_fence_after();
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
 #pragma unroll 1
       for (int c = 0; c < HD / 32; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(tO + lane_off + c * 32, r);
+        tmem_ld_32x32(o_addr + c * 32, r);
         tmem_ld_wait();
         if (q_idx < p.Sq) {
 #pragma unroll
@@ -294,7 +321,7 @@ static int launch_fa_fwd(const void* Q, const void* K, const void* V, const Attn
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
-  dim3 grid(ceil_div(p.Sq, kFaBlock), p.H, p.B);
+  dim3 grid(ceil_div(p.Sq, kFaBlock * kFaTiles), p.H, p.B);
   kern<<<grid, kFaThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -307,7 +334,7 @@ using namespace b200;
 static bool al16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
 
 // Strides are in elements.  Supported on the tensor-core path: hd in {64, 128}, bf16,
-// all strides multiples of 8.  Returns B200_ERR_SHAPE otherwise (callers use b200_attn_simt_*).
+// all strides multiples of 8.  Returns B200_ERR_SHAPE otherwise.
 B200_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, void* O, float* LSE,
                                  int B, int H, int Hkv, int Sq, int Sk, int hd,
                                  long long q_sb, long long q_ss, long long q_sh,
