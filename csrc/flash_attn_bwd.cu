@@ -1,4 +1,6 @@
-// Flash-attention backward on tcgen05, as two deterministic kernels (no atomics):
+// Flash-attention backward on tcgen05, as two deterministic kernels (no atomics).  Both stream the non-resident
+// dimension in 64-wide steps with S / dP DOUBLE-BUFFERED in TMEM, so the tensor cores compute step j+1 while the CUDA
+// cores turn step j's scores into P / dS (the TMEM -> register read of S and dP is the binding resource):
 //   dkv kernel: one CTA per (batch, kv-head, 128-key block); loops over query blocks (and over
 //               the query heads of a GQA group) accumulating dK and dV in TMEM.
 //               S^T = K Q^T, dP^T = V dO^T, dV += P^T dO, dK += dS^T Q
@@ -28,11 +30,16 @@ struct AttnBwdParams {
   void* dQ; void* dK; void* dV;       // bf16
 };
 
+constexpr int kFbSub = 64;      // width of the streamed dimension per pipeline step (keys in dq, queries in dkv)
+constexpr int kFbStages = 3;    // smem ring depth for the streamed (sub-block) tiles
+
 template <int HD>
 struct FbCfg {
   static constexpr int kHalves = HD / 64;
-  static constexpr int kTile = kFbBlock * HD * 2;
-  static constexpr int kSmemBytes = 6 * kTile + 2 * 2 * 128 * 4 + 1024 + 256;
+  static constexpr int kTile = kFbBlock * HD * 2;       // resident 128-row tile
+  static constexpr int kSubTile = kFbSub * HD * 2;      // streamed 64-row tile
+  // 2 resident tiles + ring of (2 streamed tiles) + LSE/delta staging + barriers
+  static constexpr int kSmemBytes = 2 * kTile + kFbStages * 2 * kSubTile + 2048 + 1024 + 256;
 };
 
 // delta[b,h,q] = sum_d dO[b,q,h,d] * O[b,q,h,d]    (one warp per row)
@@ -74,6 +81,9 @@ __device__ __forceinline__ void store_chunk_bf16(__nv_bfloat16* dst, const uint3
 }
 
 // ============================== dK / dV ======================================
+// CTA = (batch, kv head, 128 keys).  TMEM: dV [0,128) | dK [128,256) | {S^T_b [64] , dP^T_b [64]} x 2 buffers.
+// P^T / dS^T (bf16) are written back over the columns each thread has just read (first 16 of its 32), so the TS-MMA
+// reads its A operand at tmem + {0, 8, 32, 40} for the four 16-query K steps.
 template <int HD>
 __global__ void __launch_bounds__(kFbThreads, 1)
 flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
@@ -81,32 +91,34 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
                           const __grid_constant__ CUtensorMap tmap_v,
                           const __grid_constant__ CUtensorMap tmap_do, const AttnBwdParams p) {
   using Cfg = FbCfg<HD>;
-  constexpr int kTile = Cfg::kTile;
+  constexpr int kTile = Cfg::kTile, kSub = Cfg::kSubTile;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sK = smem_base, sV = smem_base + kTile;
-  auto sQ = [&](int s) { return smem_base + kTile * (2 + 2 * s); };
-  auto sDO = [&](int s) { return smem_base + kTile * (3 + 2 * s); };
+  auto sQ = [&](int s) { return smem_base + 2 * kTile + (2 * s) * kSub; };
+  auto sDO = [&](int s) { return smem_base + 2 * kTile + (2 * s + 1) * kSub; };
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  float* s_lse = reinterpret_cast<float*>(smem_gen + 6 * kTile);  // [2][128]
-  float* s_delta = s_lse + 256;                                    // [2][128]
-  const uint32_t bar = smem_base + 6 * kTile + 2048;
+  float* s_lse = reinterpret_cast<float*>(smem_gen + 2 * kTile + kFbStages * 2 * kSub);  // [2][64]
+  float* s_delta = s_lse + 128;                                                            // [2][64]
+  const uint32_t bar = smem_base + 2 * kTile + kFbStages * 2 * kSub + 2048;
   const uint32_t kv_full = bar;
   auto qdo_full = [&](int s) { return bar + 8u * (1 + s); };
-  auto qdo_empty = [&](int s) { return bar + 8u * (3 + s); };
-  const uint32_t sdp_full = bar + 8u * 5, pds_ready = bar + 8u * 6, acc_done = bar + 8u * 7;
-  const uint32_t tmem_ptr_addr = bar + 8u * 8;
+  auto qdo_empty = [&](int s) { return bar + 8u * (1 + kFbStages + s); };
+  auto sdp_full = [&](int b_) { return bar + 8u * (1 + 2 * kFbStages + b_); };
+  auto pds_ready = [&](int b_) { return bar + 8u * (3 + 2 * kFbStages + b_); };
+  const uint32_t acc_done = bar + 8u * (5 + 2 * kFbStages);
+  const uint32_t tmem_ptr_addr = bar + 8u * (6 + 2 * kFbStages);
 
   const AttnParams& a = p.a;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kv_blk = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
   const int kv0 = kv_blk * kFbBlock;
   const int G = a.H / a.Hkv;
-  const int nq = (a.Sq + kFbBlock - 1) / kFbBlock;
+  const int nq = (a.Sq + kFbSub - 1) / kFbSub;              // 64-query steps
   int i_start = 0;
   if (a.causal) {
-    const int d = kv0 + a.k_offset - a.q_offset;
-    i_start = d <= 0 ? 0 : d / kFbBlock;
+    const int d = kv0 + a.k_offset - a.q_offset;            // first query position that can see key kv0
+    i_start = d <= 0 ? 0 : d / kFbSub;
   }
   const int per_head = nq > i_start ? nq - i_start : 0;
   const int n_iters = per_head * G;
@@ -115,8 +127,9 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
     tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k);
     tma_prefetch_desc(&tmap_v); tma_prefetch_desc(&tmap_do);
     mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
-    mbar_init(sdp_full, 1); mbar_init(pds_ready, 8); mbar_init(acc_done, 1);
+    for (int s = 0; s < kFbStages; ++s) { mbar_init(qdo_full(s), 1); mbar_init(qdo_empty(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(sdp_full(s), 1); mbar_init(pds_ready(s), 8); }
+    mbar_init(acc_done, 1);
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc<1>(tmem_ptr_addr, 512); tmem_relinquish<1>(); }
@@ -125,7 +138,9 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_addr));
-  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + HD;
+  const uint32_t tDV = tmem_base, tDK = tmem_base + 128;
+  auto tS = [&](int b_) { return tmem_base + 256 + b_ * 128; };
+  auto tDP = [&](int b_) { return tmem_base + 256 + b_ * 128 + 64; };
 
   if (warp == 0) {
     if (lane == 0 && n_iters > 0) {
@@ -136,118 +151,121 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
         tma_load_4d(sV + hh * 16384, &tmap_v, kv_full, hh * 64, kv0, hk, b, kEvictFirst);
       }
       for (int it = 0; it < n_iters; ++it) {
-        const int st = it & 1;
+        const int st = it % kFbStages;
         const int h = hk * G + it / per_head;
-        const int q0 = (i_start + it % per_head) * kFbBlock;
-        mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1u);
-        mbar_expect_tx(qdo_full(st), 2 * kTile);
+        const int q0 = (i_start + it % per_head) * kFbSub;
+        mbar_wait(qdo_empty(st), ((it / kFbStages) & 1) ^ 1u);
+        mbar_expect_tx(qdo_full(st), 2 * kSub);
 #pragma unroll
         for (int hh = 0; hh < Cfg::kHalves; ++hh) {
-          tma_load_4d(sQ(st) + hh * 16384, &tmap_q, qdo_full(st), hh * 64, q0, h, b, kEvictLast);
-          tma_load_4d(sDO(st) + hh * 16384, &tmap_do, qdo_full(st), hh * 64, q0, h, b, kEvictLast);
+          tma_load_4d(sQ(st) + hh * 8192, &tmap_q, qdo_full(st), hh * 64, q0, h, b, kEvictLast);
+          tma_load_4d(sDO(st) + hh * 8192, &tmap_do, qdo_full(st), hh * 64, q0, h, b, kEvictLast);
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0 && n_iters > 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // K-major x K-major
-      constexpr uint32_t idesc_acc = umma_idesc_bf16(128, HD, false, true);   // TMEM A x MN-major B
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, kFbSub, false, false);  // [128 keys] x [64 queries], K = hd
+      constexpr uint32_t idesc_acc = umma_idesc_bf16(128, HD, false, true);     // TMEM A x MN-major B, K = 64 queries
+      auto issue_sdp = [&](int it) {
+        const int st = it % kFbStages, bb = it & 1;
+        mbar_wait(qdo_full(st), (it / kFbStages) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;   // resident 128-row tiles: 16 KB per hd half
+          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;    // streamed 64-row tiles: 8 KB per hd half
+          umma_f16_ss<1>(tS(bb), umma_smem_desc_sw128(sK + offa, 16, 1024),
+                         umma_smem_desc_sw128(sQ(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        }
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_f16_ss<1>(tDP(bb), umma_smem_desc_sw128(sV + offa, 16, 1024),
+                         umma_smem_desc_sw128(sDO(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(sdp_full(bb));
+      };
       mbar_wait(kv_full, 0);
+      issue_sdp(0);
+      if (n_iters > 1) issue_sdp(1);
       for (int it = 0; it < n_iters; ++it) {
-        const int st = it & 1;
-        mbar_wait(qdo_full(st), (it >> 1) & 1);
+        const int st = it % kFbStages, bb = it & 1;
+        mbar_wait(pds_ready(bb), (it >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tS, umma_smem_desc_sw128(sK + off, 16, 1024),
-                         umma_smem_desc_sw128(sQ(st) + off, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < kFbSub / 16; ++kk) {
+          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;      // P^T / dS^T live where each half read its scores
+          umma_f16_ts<1>(tDV, tS(bb) + acol, umma_smem_desc_sw128(sDO(st) + kk * 2048, 8192, 1024), idesc_acc,
+                         (it > 0 || kk > 0) ? 1u : 0u);
         }
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tDP, umma_smem_desc_sw128(sV + off, 16, 1024),
-                         umma_smem_desc_sw128(sDO(st) + off, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < kFbSub / 16; ++kk) {
+          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
+          umma_f16_ts<1>(tDK, tDP(bb) + acol, umma_smem_desc_sw128(sQ(st) + kk * 2048, 8192, 1024), idesc_acc,
+                         (it > 0 || kk > 0) ? 1u : 0u);
         }
-        umma_commit(sdp_full);
-        mbar_wait(pds_ready, it & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int kk = 0; kk < kFbBlock / 16; ++kk)
-          umma_f16_ts<1>(tDV, tS + kk * 8, umma_smem_desc_sw128(sDO(st) + kk * 2048, 16384, 1024),
-                         idesc_acc, (it > 0 || kk > 0) ? 1u : 0u);
-#pragma unroll
-        for (int kk = 0; kk < kFbBlock / 16; ++kk)
-          umma_f16_ts<1>(tDK, tDP + kk * 8, umma_smem_desc_sw128(sQ(st) + kk * 2048, 16384, 1024),
-                         idesc_acc, (it > 0 || kk > 0) ? 1u : 0u);
         umma_commit(qdo_empty(st));
+        if (it + 2 < n_iters) issue_sdp(it + 2);   // reuses buffer bb: ordered after the two MMAs above
       }
       umma_commit(acc_done);
     }
     __syncwarp();
   } else {
     const int quarter = warp & 3;
-    const int half = (warp - 2) >> 2;            // which 64 query columns of the 128-wide tile this warp handles
+    const int half = (warp - 2) >> 2;            // which 32 of the 64 query columns this warp handles
     const int row = quarter * 32 + lane;         // key row inside the block
     const int ct = (warp - 2) * 32 + lane;       // 0..255 index among compute threads
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
     const float sl2 = a.scale * kLog2e;
     const int kv_pos = kv0 + row + a.k_offset - a.q_offset;  // visible to query q iff kv_pos <= q
     for (int it = 0; it < n_iters; ++it) {
-      const int st = it & 1;
+      const int bb = it & 1;
       const int h = hk * G + it / per_head;
-      const int q0 = (i_start + it % per_head) * kFbBlock;
-      // stage LSE / delta for this query block (the buffer of iteration it-2 is free: its
-      // readers all passed pds_ready(it-2) before sdp_full(it-1) could complete)
-      if (ct < 128) {
+      const int q0 = (i_start + it % per_head) * kFbSub;
+      if (ct < kFbSub) {   // stage LSE / delta of these 64 queries (buffer bb was last read two steps ago)
         const int q = q0 + ct;
         const long long off = ((long long)b * a.H + h) * a.Sq + q;
-        float l_ = q < a.Sq ? p.LSE[off] : INFINITY;
-        s_lse[st * 128 + ct] = (l_ == -INFINITY) ? INFINITY : l_ * kLog2e;  // empty rows: P = 0
-        s_delta[st * 128 + ct] = q < a.Sq ? p.Delta[off] : 0.f;
+        const float l_ = q < a.Sq ? p.LSE[off] : INFINITY;
+        s_lse[bb * 64 + ct] = (l_ == -INFINITY) ? -INFINITY : -l_ * kLog2e;  // NEGATED; empty rows: P = exp2(-inf) = 0
+        s_delta[bb * 64 + ct] = q < a.Sq ? -p.Delta[off] : 0.f;                // NEGATED
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const bool need_mask = a.causal && (q0 + a.q_offset < kv0 + kFbBlock - 1 + a.k_offset);
-      mbar_wait(sdp_full, it & 1);
+      mbar_wait(sdp_full(bb), (it >> 1) & 1);
       tc_fence_after();
-      const float* lse_s = s_lse + st * 128 + half * 64;
-      const float* del_s = s_delta + st * 128 + half * 64;
-      const uint32_t cs = tS + lane_off + half * 64, cd = tDP + lane_off + half * 64;
-      uint32_t rs0[32], rs1[32], rd0[32], rd1[32];
-      tmem_ld_32x32(cs, rs0);
-      tmem_ld_32x32(cs + 32, rs1);
-      tmem_ld_32x32(cd, rd0);
-      tmem_ld_32x32(cd + 32, rd1);
+      const float* lse_s = s_lse + bb * 64 + half * 32;
+      const float* del_s = s_delta + bb * 64 + half * 32;
+      const uint32_t cs = tS(bb) + lane_off + half * 32, cd = tDP(bb) + lane_off + half * 32;
+      uint32_t rs[32], rd[32];
+      tmem_ld_32x32(cs, rs);
+      tmem_ld_32x32(cd, rd);
       tmem_ld_wait();
-      auto chunk = [&](uint32_t (&rs)[32], uint32_t (&rd)[32], int c) {
-        uint32_t pk[16], dk[16];
+      uint32_t pk[16], dk[16];
+      const uint64_t sl2_2 = f2_pack(sl2, sl2);
+      const uint64_t* lse2p = reinterpret_cast<const uint64_t*>(lse_s);   // (-lse[i], -lse[i+1]) pairs
+      const uint64_t* del2p = reinterpret_cast<const uint64_t*>(del_s);   // (-delta[i], -delta[i+1]) pairs
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const int q = c * 32 + i;
-          float p0 = exp2f(fmaf(__uint_as_float(rs[i]), sl2, -lse_s[q]));
-          float p1 = exp2f(fmaf(__uint_as_float(rs[i + 1]), sl2, -lse_s[q + 1]));
-          if (need_mask) {
-            if (kv_pos > q0 + half * 64 + q) p0 = 0.f;
-            if (kv_pos > q0 + half * 64 + q + 1) p1 = 0.f;
-          }
-          const float d0 = p0 * (__uint_as_float(rd[i]) - del_s[q]);
-          const float d1 = p1 * (__uint_as_float(rd[i + 1]) - del_s[q + 1]);
-          pk[i >> 1] = pack_bf16(p0, p1);
-          dk[i >> 1] = pack_bf16(d0, d1);
+      for (int i = 0; i < 32; i += 2) {
+        float t0, t1, d0, d1;
+        f2_unpack(ffma2(f2_pack_u(rs[i], rs[i + 1]), sl2_2, lse2p[i >> 1]), t0, t1);
+        float p0 = ex2_approx(t0), p1 = ex2_approx(t1);
+        if (need_mask) {
+          if (kv_pos > q0 + half * 32 + i) p0 = 0.f;
+          if (kv_pos > q0 + half * 32 + i + 1) p1 = 0.f;
         }
-        tmem_st_32x16(tS + lane_off + half * 32 + c * 16, pk);
-        tmem_st_32x16(tDP + lane_off + half * 32 + c * 16, dk);
-      };
-      // NOTE: P / dS (bf16, 64 columns in total) alias the first 64 fp32 columns of S / dP.  Half 1 reads columns
-      // 64..127 but writes 32..63, which half 0 still reads: everybody finishes reading before anybody writes.
-      asm volatile("bar.sync 2, 256;" ::: "memory");
-      chunk(rs0, rd0, 0);
-      chunk(rs1, rd1, 1);
+        f2_unpack(fmul2(f2_pack(p0, p1), fadd2(f2_pack_u(rd[i], rd[i + 1]), del2p[i >> 1])), d0, d1);
+        pk[i >> 1] = pack_bf16(p0, p1);
+        dk[i >> 1] = pack_bf16(d0, d1);
+      }
+      tmem_st_32x16(cs, pk);    // over the first 16 of the 32 columns this thread just read
+      tmem_st_32x16(cd, dk);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pds_ready);
+      if (lane == 0) mbar_arrive(pds_ready(bb));
     }
     // ---- epilogue ----
     const int kv = kv0 + row;
@@ -279,6 +297,7 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
 }
 
 // ============================== dQ ===========================================
+// CTA = (batch, head, 128 queries); keys stream in 64-wide steps.  TMEM: dQ [0,128) | {S_b [64], dP_b [64]} x 2.
 template <int HD>
 __global__ void __launch_bounds__(kFbThreads, 1)
 flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
@@ -286,18 +305,20 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
                          const __grid_constant__ CUtensorMap tmap_v,
                          const __grid_constant__ CUtensorMap tmap_do, const AttnBwdParams p) {
   using Cfg = FbCfg<HD>;
-  constexpr int kTile = Cfg::kTile;
+  constexpr int kTile = Cfg::kTile, kSub = Cfg::kSubTile;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = smem_base, sDO = smem_base + kTile;
-  auto sK = [&](int s) { return smem_base + kTile * (2 + 2 * s); };
-  auto sV = [&](int s) { return smem_base + kTile * (3 + 2 * s); };
-  const uint32_t bar = smem_base + 6 * kTile + 2048;
+  auto sK = [&](int s) { return smem_base + 2 * kTile + (2 * s) * kSub; };
+  auto sV = [&](int s) { return smem_base + 2 * kTile + (2 * s + 1) * kSub; };
+  const uint32_t bar = smem_base + 2 * kTile + kFbStages * 2 * kSub + 2048;
   const uint32_t qdo_full = bar;
   auto kv_full = [&](int s) { return bar + 8u * (1 + s); };
-  auto kv_empty = [&](int s) { return bar + 8u * (3 + s); };
-  const uint32_t sdp_full = bar + 8u * 5, ds_ready = bar + 8u * 6, acc_done = bar + 8u * 7;
-  const uint32_t tmem_ptr_addr = bar + 8u * 8;
+  auto kv_empty = [&](int s) { return bar + 8u * (1 + kFbStages + s); };
+  auto sdp_full = [&](int b_) { return bar + 8u * (1 + 2 * kFbStages + b_); };
+  auto ds_ready = [&](int b_) { return bar + 8u * (3 + 2 * kFbStages + b_); };
+  const uint32_t acc_done = bar + 8u * (5 + 2 * kFbStages);
+  const uint32_t tmem_ptr_addr = bar + 8u * (6 + 2 * kFbStages);
 
   const AttnParams& a = p.a;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -310,14 +331,15 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const int lim = q0 + kFbBlock + a.q_offset - a.k_offset;
     kv_limit = lim < kv_limit ? lim : kv_limit;
   }
-  const int n_blocks = kv_limit > 0 ? (kv_limit + kFbBlock - 1) / kFbBlock : 0;
+  const int n_blocks = kv_limit > 0 ? (kv_limit + kFbSub - 1) / kFbSub : 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_q); tma_prefetch_desc(&tmap_k);
     tma_prefetch_desc(&tmap_v); tma_prefetch_desc(&tmap_do);
     mbar_init(qdo_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 1); }
-    mbar_init(sdp_full, 1); mbar_init(ds_ready, 8); mbar_init(acc_done, 1);
+    for (int s = 0; s < kFbStages; ++s) { mbar_init(kv_full(s), 1); mbar_init(kv_empty(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(sdp_full(s), 1); mbar_init(ds_ready(s), 8); }
+    mbar_init(acc_done, 1);
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc<1>(tmem_ptr_addr, 512); tmem_relinquish<1>(); }
@@ -326,7 +348,9 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_addr));
-  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDQ = tmem_base + 256;
+  const uint32_t tDQ = tmem_base;
+  auto tS = [&](int b_) { return tmem_base + 128 + b_ * 128; };
+  auto tDP = [&](int b_) { return tmem_base + 128 + b_ * 128 + 64; };
 
   if (warp == 0) {
     if (lane == 0 && n_blocks > 0) {
@@ -337,46 +361,56 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
         tma_load_4d(sDO + hh * 16384, &tmap_do, qdo_full, hh * 64, q0, h, b, kEvictFirst);
       }
       for (int j = 0; j < n_blocks; ++j) {
-        const int st = j & 1;
-        mbar_wait(kv_empty(st), ((j >> 1) & 1) ^ 1u);
-        mbar_expect_tx(kv_full(st), 2 * kTile);
+        const int st = j % kFbStages;
+        mbar_wait(kv_empty(st), ((j / kFbStages) & 1) ^ 1u);
+        mbar_expect_tx(kv_full(st), 2 * kSub);
 #pragma unroll
         for (int hh = 0; hh < Cfg::kHalves; ++hh) {
-          tma_load_4d(sK(st) + hh * 16384, &tmap_k, kv_full(st), hh * 64, j * kFbBlock, hk, b, kEvictLast);
-          tma_load_4d(sV(st) + hh * 16384, &tmap_v, kv_full(st), hh * 64, j * kFbBlock, hk, b, kEvictLast);
+          tma_load_4d(sK(st) + hh * 8192, &tmap_k, kv_full(st), hh * 64, j * kFbSub, hk, b, kEvictLast);
+          tma_load_4d(sV(st) + hh * 8192, &tmap_v, kv_full(st), hh * 64, j * kFbSub, hk, b, kEvictLast);
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0 && n_blocks > 0) {
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, kFbSub, false, false);
       constexpr uint32_t idesc_acc = umma_idesc_bf16(128, HD, false, true);
+      auto issue_sdp = [&](int j) {
+        const int st = j % kFbStages, bb = j & 1;
+        mbar_wait(kv_full(st), (j / kFbStages) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_f16_ss<1>(tS(bb), umma_smem_desc_sw128(sQ + offa, 16, 1024),
+                         umma_smem_desc_sw128(sK(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        }
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
+          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
+          umma_f16_ss<1>(tDP(bb), umma_smem_desc_sw128(sDO + offa, 16, 1024),
+                         umma_smem_desc_sw128(sV(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(sdp_full(bb));
+      };
       mbar_wait(qdo_full, 0);
+      issue_sdp(0);
+      if (n_blocks > 1) issue_sdp(1);
       for (int j = 0; j < n_blocks; ++j) {
-        const int st = j & 1;
-        mbar_wait(kv_full(st), (j >> 1) & 1);
+        const int st = j % kFbStages, bb = j & 1;
+        mbar_wait(ds_ready(bb), (j >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tS, umma_smem_desc_sw128(sQ + off, 16, 1024),
-                         umma_smem_desc_sw128(sK(st) + off, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < kFbSub / 16; ++kk) {
+          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
+          umma_f16_ts<1>(tDQ, tDP(bb) + acol, umma_smem_desc_sw128(sK(st) + kk * 2048, 8192, 1024), idesc_acc,
+                         (j > 0 || kk > 0) ? 1u : 0u);
         }
-#pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tDP, umma_smem_desc_sw128(sDO + off, 16, 1024),
-                         umma_smem_desc_sw128(sV(st) + off, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
-        }
-        umma_commit(sdp_full);
-        mbar_wait(ds_ready, j & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int kk = 0; kk < kFbBlock / 16; ++kk)
-          umma_f16_ts<1>(tDQ, tDP + kk * 8, umma_smem_desc_sw128(sK(st) + kk * 2048, 16384, 1024),
-                         idesc_acc, (j > 0 || kk > 0) ? 1u : 0u);
         umma_commit(kv_empty(st));
+        if (j + 2 < n_blocks) issue_sdp(j + 2);
       }
       umma_commit(acc_done);
     }
@@ -394,40 +428,37 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const float delta = q_idx < a.Sq ? p.Delta[roff] : 0.f;
     const int q_pos = q_idx + a.q_offset - a.k_offset;
     for (int j = 0; j < n_blocks; ++j) {
-      const int kv0 = j * kFbBlock;
-      const bool need_mask = (kv0 + kFbBlock > a.Sk) ||
-                             (a.causal && (kv0 + kFbBlock - 1 > q0 + a.q_offset - a.k_offset));
-      mbar_wait(sdp_full, j & 1);
+      const int bb = j & 1;
+      const int kv0 = j * kFbSub;
+      const bool need_mask = (kv0 + kFbSub > a.Sk) ||
+                             (a.causal && (kv0 + kFbSub - 1 > q0 + a.q_offset - a.k_offset));
+      mbar_wait(sdp_full(bb), (j >> 1) & 1);
       tc_fence_after();
-      const uint32_t cs = tS + lane_off + half * 64, cd = tDP + lane_off + half * 64;
-      uint32_t rs0[32], rs1[32], rd0[32], rd1[32];
-      tmem_ld_32x32(cs, rs0);
-      tmem_ld_32x32(cs + 32, rs1);
-      tmem_ld_32x32(cd, rd0);
-      tmem_ld_32x32(cd + 32, rd1);
+      const uint32_t cs = tS(bb) + lane_off + half * 32, cd = tDP(bb) + lane_off + half * 32;
+      uint32_t rs[32], rd[32];
+      tmem_ld_32x32(cs, rs);
+      tmem_ld_32x32(cd, rd);
       tmem_ld_wait();
-      auto chunk = [&](uint32_t (&rs)[32], uint32_t (&rd)[32], int c) {
-        uint32_t dk[16];
+      uint32_t dk[16];
+      const uint64_t sl2_2 = f2_pack(sl2, sl2), nlse_2 = f2_pack(-lse2, -lse2), ndel_2 = f2_pack(-delta, -delta);
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = exp2f(fmaf(__uint_as_float(rs[i]), sl2, -lse2));
-          float p1 = exp2f(fmaf(__uint_as_float(rs[i + 1]), sl2, -lse2));
-          if (need_mask) {
-            const int col = kv0 + half * 64 + c * 32 + i;
-            if (!(col < a.Sk && (!a.causal || col <= q_pos))) p0 = 0.f;
-            if (!(col + 1 < a.Sk && (!a.causal || col + 1 <= q_pos))) p1 = 0.f;
-          }
-          dk[i >> 1] = pack_bf16(p0 * (__uint_as_float(rd[i]) - delta), p1 * (__uint_as_float(rd[i + 1]) - delta));
+      for (int i = 0; i < 32; i += 2) {
+        float t0, t1, d0, d1;
+        f2_unpack(ffma2(f2_pack_u(rs[i], rs[i + 1]), sl2_2, nlse_2), t0, t1);
+        float p0 = ex2_approx(t0), p1 = ex2_approx(t1);
+        if (need_mask) {
+          const int col = kv0 + half * 32 + i;
+          if (!(col < a.Sk && (!a.causal || col <= q_pos))) p0 = 0.f;
+          if (!(col + 1 < a.Sk && (!a.causal || col + 1 <= q_pos))) p1 = 0.f;
         }
-        tmem_st_32x16(tDP + lane_off + half * 32 + c * 16, dk);
-      };
-      asm volatile("bar.sync 2, 256;" ::: "memory");  // dS aliases dP columns another warp may still be reading
-      chunk(rs0, rd0, 0);
-      chunk(rs1, rd1, 1);
+        f2_unpack(fmul2(f2_pack(p0, p1), fadd2(f2_pack_u(rd[i], rd[i + 1]), ndel_2)), d0, d1);
+        dk[i >> 1] = pack_bf16(d0, d1);
+      }
+      tmem_st_32x16(cd, dk);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(ds_ready);
+      if (lane == 0) mbar_arrive(ds_ready(bb));
     }
     __nv_bfloat16* dqrow = reinterpret_cast<__nv_bfloat16*>(p.dQ) + (long long)b * p.dq_sb + (long long)q_idx * p.dq_ss + (long long)h * p.dq_sh;
     if (n_blocks > 0) {
@@ -454,11 +485,16 @@ static int launch_fa_bwd(const void* Q, const void* K, const void* V, const void
                          const AttnBwdParams& p, cudaStream_t stream) {
   using Cfg = FbCfg<HD>;
   const AttnParams& a = p.a;
-  CUtensorMap tq, tk, tv, tdo;
+  // resident tiles are 128 rows, streamed tiles 64 rows: each tensor needs both box shapes
+  CUtensorMap tq, tk, tv, tdo, tq64, tk64, tv64, tdo64;
   if (int rc = make_attn_tmap(&tq, Q, a.B, a.Sq, a.H, HD, a.q_sb, a.q_ss, a.q_sh, kFbBlock)) return rc;
   if (int rc = make_attn_tmap(&tk, K, a.B, a.Sk, a.Hkv, HD, a.k_sb, a.k_ss, a.k_sh, kFbBlock)) return rc;
   if (int rc = make_attn_tmap(&tv, V, a.B, a.Sk, a.Hkv, HD, a.v_sb, a.v_ss, a.v_sh, kFbBlock)) return rc;
   if (int rc = make_attn_tmap(&tdo, dO, a.B, a.Sq, a.H, HD, p.do_sb, p.do_ss, p.do_sh, kFbBlock)) return rc;
+  if (int rc = make_attn_tmap(&tq64, Q, a.B, a.Sq, a.H, HD, a.q_sb, a.q_ss, a.q_sh, kFbSub)) return rc;
+  if (int rc = make_attn_tmap(&tk64, K, a.B, a.Sk, a.Hkv, HD, a.k_sb, a.k_ss, a.k_sh, kFbSub)) return rc;
+  if (int rc = make_attn_tmap(&tv64, V, a.B, a.Sk, a.Hkv, HD, a.v_sb, a.v_ss, a.v_sh, kFbSub)) return rc;
+  if (int rc = make_attn_tmap(&tdo64, dO, a.B, a.Sq, a.H, HD, p.do_sb, p.do_ss, p.do_sh, kFbSub)) return rc;
   auto k1 = flash_attn_bwd_dkv_kernel<HD>;
   auto k2 = flash_attn_bwd_dq_kernel<HD>;
   static bool attr_set = false;
@@ -468,10 +504,10 @@ static int launch_fa_bwd(const void* Q, const void* K, const void* V, const void
     attr_set = true;
   }
   dim3 g1(ceil_div(a.Sk, kFbBlock), a.Hkv, a.B);
-  k1<<<g1, kFbThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, tdo, p);
+  k1<<<g1, kFbThreads, Cfg::kSmemBytes, stream>>>(tq64, tk, tv, tdo64, p);
   B200_LAUNCH_CHECK();
   dim3 g2(ceil_div(a.Sq, kFbBlock), a.H, a.B);
-  k2<<<g2, kFbThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, tdo, p);
+  k2<<<g2, kFbThreads, Cfg::kSmemBytes, stream>>>(tq, tk64, tv64, tdo, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -212,12 +212,13 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
           if (!(c + 96 < p.Sk && (!p.causal || c + 96 <= q_pos))) r3[i] = ninf;
         }
       }
-      float mx = -INFINITY;
+      float mx = -INFINITY, mx2 = -INFINITY;   // two chains of 3-input max (FMNMX3)
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
-        mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(r0[i]), __uint_as_float(r1[i])),
-                             fmaxf(__uint_as_float(r2[i]), __uint_as_float(r3[i]))));
+        mx = fmax3(mx, __uint_as_float(r0[i]), __uint_as_float(r1[i]));
+        mx2 = fmax3(mx2, __uint_as_float(r2[i]), __uint_as_float(r3[i]));
       }
+      mx = fmaxf(mx, mx2);
       // ---- lazy rescale decision ----
       float alpha = 1.f;
       bool rescale = false;
@@ -243,14 +244,16 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
       // ---- P = exp2((S - m) * scale), row sum, packed bf16 back into the S columns ----
       const float mneg = (m_used == -INFINITY) ? 0.f : -m_used * sl2;
-      float lsum = 0.f;
+      const uint64_t sl2_2 = f2_pack(sl2, sl2), mneg_2 = f2_pack(mneg, mneg);
+      uint64_t lsum2 = f2_pack(0.f, 0.f);
       auto do_chunk = [&](uint32_t (&r)[32], int c) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float p0 = exp2f(fmaf(__uint_as_float(r[i]), sl2, mneg));      // exp2(-inf) == 0 for masked keys
-          const float p1 = exp2f(fmaf(__uint_as_float(r[i + 1]), sl2, mneg));
-          lsum += p0 + p1;
+          float t0, t1;
+          f2_unpack(ffma2(f2_pack_u(r[i], r[i + 1]), sl2_2, mneg_2), t0, t1);   // one FFMA2 for two scores
+          const float p0 = ex2_approx(t0), p1 = ex2_approx(t1);                  // exp2(-inf) == 0 for masked keys
+          lsum2 = fadd2(lsum2, f2_pack(p0, p1));
           pk[i >> 1] = pack_bf16(p0, p1);
         }
         tmem_st_32x16(s_addr + c * 16, pk);
@@ -259,7 +262,9 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
       do_chunk(r1, 1);
       do_chunk(r2, 2);
       do_chunk(r3, 3);
-      l_run += lsum;
+      float ls0, ls1;
+      f2_unpack(lsum2, ls0, ls1);
+      l_run += ls0 + ls1;
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
