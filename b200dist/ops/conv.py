@@ -207,7 +207,7 @@ class _MaxPoolFn(Function):
 
 def max_pool2d(x, kernel_size: int, stride: Optional[int] = None, padding: int = 0):
     stride = kernel_size if stride is None else stride
-    if not x.is_cuda:
+    if not x.is_cuda or x.shape[1] % 8:
         return F.max_pool2d(x, kernel_size, stride, padding)
     return _MaxPoolFn.apply(x, kernel_size, stride, padding)
 

@@ -41,6 +41,8 @@ class _LinearFn(Function):
         y = N.gemm(xb, wb, bias=bias, residual=residual.reshape(-1, w.shape[0]) if residual is not None else None,
                    out_dtype=out_dtype)
         ctx.save_for_backward(xb, wb)
+        # a parallel wrapper (FSDP) may want the weight gradient written straight into its communication buffer
+        ctx.grad_sink = getattr(w, "_b200_grad_sink", None)
         ctx.x_shape, ctx.x_dtype, ctx.w_dtype = x.shape, x.dtype, w.dtype
         ctx.has_bias, ctx.has_res = bias is not None, residual is not None
         ctx.bias_dtype = bias.dtype if bias is not None else None
@@ -56,8 +58,11 @@ class _LinearFn(Function):
             dx = N.gemm(dyb, wb, b_mn=True,
                         out_dtype=torch.float32 if ctx.x_dtype == torch.float32 else _BF16).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dw = N.gemm(dyb, xb, a_mn=True, b_mn=True,
-                        out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else _BF16)
+            if ctx.grad_sink is not None and ctx.grad_sink(dyb, xb):
+                dw = None  # wgrad GEMM wrote into the sink (no autograd accumulation, no extra copy)
+            else:
+                dw = N.gemm(dyb, xb, a_mn=True, b_mn=True,
+                            out_dtype=torch.float32 if ctx.w_dtype == torch.float32 else _BF16)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy.reshape(-1, Nf).sum(0, dtype=torch.float32).to(ctx.bias_dtype)
         if ctx.has_res and ctx.needs_input_grad[3]:

@@ -60,6 +60,8 @@ class _Unit:
         self.grad_ready: List[bool] = []
         self.rs_event = None
         self.index = 0
+        self.stage_k = None            # staging buffer claimed for the current backward
+        self.sink_written: List[bool] = []
 
 
 def _default_units(module: nn.Module):
@@ -203,8 +205,11 @@ class FSDP(nn.Module):
             u.module.register_forward_hook(self._make_post_forward(u))
             u.module.register_full_backward_pre_hook(self._make_pre_backward(u))
         for u in self.exec_units:
+            u.sink_written = [False] * len(u.params)
             for i, p in enumerate(u.params):
                 p.register_post_accumulate_grad_hook(self._make_grad_hook(u, i))
+                if self.native and self.world > 1 and p.dim() == 2 and p.dtype == torch.bfloat16:
+                    p._b200_grad_sink = self._make_sink(u, i)
 
     def _next_unit(self, u: _Unit, step: int) -> Optional[_Unit]:
         j = u.index + step
@@ -248,6 +253,34 @@ class FSDP(nn.Module):
         return hook
 
     # ------------------------------------------------------------------ gradient path
+    def _claim_stage(self, u: _Unit):
+        """Pick one of the two symmetric staging buffers for this unit's gradients (first use in a backward)."""
+        if u.stage_k is None:
+            k = self._stage_idx
+            self._stage_idx ^= 1
+            if self._stage_events[k] is not None:  # the reduce-scatter that last read this buffer must be done
+                torch.cuda.current_stream(self.device).wait_event(self._stage_events[k])
+            u.stage_k = k
+        return self.grad_stage[u.stage_k]
+
+    def _make_sink(self, u: _Unit, slot: int):
+        """Weight-gradient sink: the wgrad GEMM writes dW directly into the unit's symmetric staging slot."""
+        def sink(dy2d, x2d) -> bool:
+            if not self.require_backward_grad_sync:
+                return False  # gradient accumulation: let autograd accumulate locally
+            self._begin_backward()
+            p, o = u.params[slot], u.offsets[slot]
+            view = self._claim_stage(u).tensor(self.dtype, 0, u.total)[o:o + p.numel()].view(p.shape)
+            N.gemm(dy2d, x2d, a_mn=True, b_mn=True, out=view, accumulate=u.sink_written[slot])
+            u.sink_written[slot] = True
+            if not u.grad_ready[slot]:
+                u.grad_ready[slot] = True
+                u.pending_grads -= 1
+            if u.pending_grads == 0:
+                self._reduce_unit(u)
+            return True
+        return sink
+
     def _reduce_unit(self, u: _Unit) -> None:
         u.pending_grads = -1  # launched
         if not self.require_backward_grad_sync:
@@ -258,14 +291,13 @@ class FSDP(nn.Module):
             self._local_update(u, hp, t)
             return
         if self.native:
-            k = self._stage_idx
-            self._stage_idx ^= 1
-            stage = self.grad_stage[k]
+            stage = self._claim_stage(u)
+            k = u.stage_k
             cur = torch.cuda.current_stream(self.device)
-            if self._stage_events[k] is not None:
-                cur.wait_event(self._stage_events[k])  # previous reduce-scatter out of this buffer is done
             st = stage.tensor(self.dtype, 0, u.total)
-            for p, o in zip(u.params, u.offsets):
+            for i, (p, o) in enumerate(zip(u.params, u.offsets)):
+                if u.sink_written[i]:
+                    continue  # the wgrad GEMM already wrote this slot
                 seg = st[o:o + p.numel()]
                 if p.grad is None:
                     seg.zero_()
@@ -335,6 +367,8 @@ class FSDP(nn.Module):
         for u in self.exec_units:
             u.grad_ready = [False] * len(u.params)
             u.pending_grads = len(u.params)
+            u.sink_written = [False] * len(u.params)
+            u.stage_k = None
         if self.root_unit is not None and self.world > 1:
             self._free(self.root_unit)
         self._in_backward = False

@@ -85,37 +85,60 @@ __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, in
 }
 
 // ------------------------------------------------------------------ per-channel reductions over rows
-// sums[0][c] += sum_r a[r][c] * (mask ? (y[r][c] > 0) : 1);  sums[1][c] += sum_r (same) * b-term
-//   mode 0: stats      -> sum x, sum x^2
-//   mode 1: bn backward-> sum dy_m, sum dy_m * (x - mean[c]) * rstd[c]   (dy_m = dy masked by relu(y))
+// sums[0][c] += sum_r f0(r, c);  sums[1][c] += sum_r f1(r, c)   (atomics: `sums` must be zeroed by the caller)
+//   mode 0: stats       -> sum x, sum x^2
+//   mode 1: bn backward -> sum dy_m, sum dy_m * (x - mean[c]) * rstd[c]   (dy_m = dy masked by relu(y))
+// Each thread owns 8 consecutive channels (one 128-bit load per row); a block covers `nvx` channel vectors x 256/nvx rows.
 template <typename T>
-__global__ void col_reduce_kernel(const T* __restrict__ a, const T* __restrict__ xin, const T* __restrict__ y,
-                                  const float* __restrict__ mean, const float* __restrict__ rstd,
-                                  float* __restrict__ sums, long long rows, int C, int mode, int relu_mask) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;  // blockDim.x channels, blockDim.y row lanes
-  if (c >= C) return;
+__global__ void __launch_bounds__(256) col_reduce_kernel(const T* __restrict__ a, const T* __restrict__ xin,
+                                                         const T* __restrict__ y, const float* __restrict__ mean,
+                                                         const float* __restrict__ rstd, float* __restrict__ sums,
+                                                         long long rows, int C, int mode, int relu_mask, int nvx) {
+  const int tx = threadIdx.x % nvx, ty = threadIdx.x / nvx, nty = 256 / nvx;
+  const int c = (blockIdx.x * nvx + tx) * 8;
+  const bool active = c < C;
   const long long rows_per = (rows + gridDim.y - 1) / gridDim.y;
   const long long r0 = blockIdx.y * rows_per;
   const long long r1 = r0 + rows_per < rows ? r0 + rows_per : rows;
-  float s0 = 0.f, s1 = 0.f;
-  const float mu = mode == 1 ? mean[c] : 0.f, rs = mode == 1 ? rstd[c] : 0.f;
-  for (long long r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-    const float v = to_f<T>(a[r * C + c]);
-    if (mode == 0) { s0 += v; s1 += v * v; }
-    else {
-      const float g = (relu_mask && !(to_f<T>(y[r * C + c]) > 0.f)) ? 0.f : v;
-      s0 += g;
-      s1 += g * (to_f<T>(xin[r * C + c]) - mu) * rs;
+  float s0[8], s1[8], mu[8], rs[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s0[j] = 0.f; s1[j] = 0.f; mu[j] = 0.f; rs[j] = 0.f; }
+  if (active && mode == 1) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mu[j] = mean[c + j]; rs[j] = rstd[c + j]; }
+  }
+  if (active) {
+#pragma unroll 2
+    for (long long r = r0 + ty; r < r1; r += nty) {
+      float v[8];
+      Vec8<T>::load(a + r * C + c, v);
+      if (mode == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0[j] += v[j]; s1[j] += v[j] * v[j]; }
+      } else {
+        float xv[8], yv[8];
+        Vec8<T>::load(xin + r * C + c, xv);
+        if (relu_mask) Vec8<T>::load(y + r * C + c, yv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float g = (relu_mask && !(yv[j] > 0.f)) ? 0.f : v[j];
+          s0[j] += g;
+          s1[j] += g * (xv[j] - mu[j]) * rs[j];
+        }
+      }
     }
   }
-  __shared__ float sh0[8][33], sh1[8][33];
-  sh0[threadIdx.y][threadIdx.x] = s0;
-  sh1[threadIdx.y][threadIdx.x] = s1;
+  __shared__ float sh[2][256][9];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sh[0][threadIdx.x][j] = s0[j]; sh[1][threadIdx.x][j] = s1[j]; }
   __syncthreads();
-  if (threadIdx.y == 0) {
-    for (int j = 1; j < blockDim.y; ++j) { s0 += sh0[j][threadIdx.x]; s1 += sh1[j][threadIdx.x]; }
-    atomicAdd(sums + c, s0);
-    atomicAdd(sums + C + c, s1);
+  if (ty == 0 && active) {
+    for (int t = 1; t < nty; ++t) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s0[j] += sh[0][t * nvx + tx][j]; s1[j] += sh[1][t * nvx + tx][j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { atomicAdd(sums + c + j, s0[j]); atomicAdd(sums + C + c + j, s1[j]); }
   }
 }
 
@@ -141,18 +164,31 @@ template <typename T>
 __global__ void bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
                                 const float* __restrict__ gamma, const float* __restrict__ beta,
                                 const T* __restrict__ residual, T* __restrict__ y, long long rows, int C, int relu) {
+  // Each thread keeps ONE channel vector (8 channels) for its whole grid-stride walk, so the per-channel
+  // scale / shift are computed once and the inner loop is load - fma - store.
   const int c8n = C >> 3;
-  const long long total = rows * c8n;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % c8n) * 8;
-    float v[8], r[8];
+  const long long nthreads = (long long)gridDim.x * blockDim.x;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long lanes_per_vec = nthreads / c8n;     // host guarantees nthreads % c8n == 0
+  if (lanes_per_vec == 0) return;
+  const int cv = (int)(tid % c8n);
+  const long long lane = tid / c8n;
+  if (lane >= lanes_per_vec) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = rstd[cv * 8 + j] * gamma[cv * 8 + j];
+    sh[j] = beta[cv * 8 + j] - mean[cv * 8 + j] * sc[j];
+  }
+  for (long long r = lane; r < rows; r += lanes_per_vec) {
+    const long long i = r * c8n + cv;
+    float v[8], rr[8];
     Vec8<T>::load(x + i * 8, v);
-    if (residual) Vec8<T>::load(residual + i * 8, r);
+    if (residual) Vec8<T>::load(residual + i * 8, rr);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float o = (v[j] - mean[c + j]) * rstd[c + j] * gamma[c + j] + beta[c + j];
-      if (residual) o += r[j];
+      float o = fmaf(v[j], sc[j], sh[j]);
+      if (residual) o += rr[j];
       v[j] = relu ? fmaxf(o, 0.f) : o;
     }
     Vec8<T>::store(y + i * 8, v);
@@ -165,12 +201,26 @@ __global__ void bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restric
                                     const float* __restrict__ mean, const float* __restrict__ rstd,
                                     const float* __restrict__ gamma, const float* __restrict__ sums,
                                     T* __restrict__ dx, T* __restrict__ dres, long long rows, int C, int relu_mask) {
+  // dx = A * g + B * x + K with per-channel A = gamma*rstd, B = -A*rstd*s1/M, K = -A*s0/M - B*mean
   const int c8n = C >> 3;
-  const long long total = rows * c8n;
   const float invM = 1.f / (float)rows;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % c8n) * 8;
+  const long long nthreads = (long long)gridDim.x * blockDim.x;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long lanes_per_vec = nthreads / c8n;
+  if (lanes_per_vec == 0) return;
+  const int cv = (int)(tid % c8n);
+  const long long lane = tid / c8n;
+  if (lane >= lanes_per_vec) return;
+  float ca[8], cb[8], ck[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = cv * 8 + j;
+    ca[j] = gamma[c] * rstd[c];
+    cb[j] = -ca[j] * rstd[c] * sums[C + c] * invM;
+    ck[j] = -ca[j] * sums[c] * invM - cb[j] * mean[c];
+  }
+  for (long long r = lane; r < rows; r += lanes_per_vec) {
+    const long long i = r * c8n + cv;
     float g[8], xv[8], yv[8], o[8];
     Vec8<T>::load(dy + i * 8, g);
     Vec8<T>::load(x + i * 8, xv);
@@ -178,8 +228,7 @@ __global__ void bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       if (relu_mask && !(yv[j] > 0.f)) g[j] = 0.f;
-      const float xh = (xv[j] - mean[c + j]) * rstd[c + j];
-      o[j] = gamma[c + j] * rstd[c + j] * (g[j] - sums[c + j] * invM - xh * sums[C + c + j] * invM);
+      o[j] = fmaf(ca[j], g[j], fmaf(cb[j], xv[j], ck[j]));
     }
     Vec8<T>::store(dx + i * 8, o);
     if (dres) Vec8<T>::store(dres + i * 8, g);
@@ -190,28 +239,38 @@ __global__ void bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restric
 template <typename T>
 __global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, unsigned char* __restrict__ idx, int N,
                                    int H, int W, int C, int K, int stride, int pad, int Ho, int Wo) {
-  const long long total = (long long)N * Ho * Wo * C;
+  const int c8n = C >> 3;   // host guarantees C % 8 == 0
+  const long long total = (long long)N * Ho * Wo * c8n;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     long long r = i;
-    const int c = (int)(r % C); r /= C;
+    const int c = (int)(r % c8n) * 8; r /= c8n;
     const int wo = (int)(r % Wo); r /= Wo;
     const int ho = (int)(r % Ho);
     const int n = (int)(r / Ho);
-    float m = -INFINITY;
-    int arg = 0;
+    float m[8];
+    int arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; arg[j] = 0; }
     for (int kh = 0; kh < K; ++kh) {
       const int h = ho * stride - pad + kh;
       if (h < 0 || h >= H) continue;
       for (int kw = 0; kw < K; ++kw) {
         const int w = wo * stride - pad + kw;
         if (w < 0 || w >= W) continue;
-        const float v = to_f<T>(x[(((long long)n * H + h) * W + w) * C + c]);
-        if (v > m) { m = v; arg = kh * K + kw; }  // first maximum wins, like torch
+        float v[8];
+        Vec8<T>::load(x + (((long long)n * H + h) * W + w) * C + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v[j] > m[j]) { m[j] = v[j]; arg[j] = kh * K + kw; }  // first maximum wins, like torch
       }
     }
-    y[i] = from_f<T>(m);
-    idx[i] = (unsigned char)arg;
+    const long long o = (((long long)n * Ho + ho) * Wo + wo) * C + c;
+    Vec8<T>::store(y + o, m);
+    uint2 packed;
+    packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+    packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+    *reinterpret_cast<uint2*>(idx + o) = packed;
   }
 }
 
@@ -220,15 +279,18 @@ template <typename T>
 __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ idx,
                                    T* __restrict__ dx, int N, int H, int W, int C, int K, int stride, int pad,
                                    int Ho, int Wo) {
-  const long long total = (long long)N * H * W * C;
+  const int c8n = C >> 3;
+  const long long total = (long long)N * H * W * c8n;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     long long r = i;
-    const int c = (int)(r % C); r /= C;
+    const int c = (int)(r % c8n) * 8; r /= c8n;
     const int w = (int)(r % W); r /= W;
     const int h = (int)(r % H);
     const int n = (int)(r / H);
-    float acc = 0.f;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     for (int kh = 0; kh < K; ++kh) {
       const int hs = h + pad - kh;
       if (hs < 0 || hs % stride) continue;
@@ -240,10 +302,18 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const unsigned char
         const int wo = ws / stride;
         if (wo >= Wo) continue;
         const long long o = (((long long)n * Ho + ho) * Wo + wo) * C + c;
-        if (idx[o] == kh * K + kw) acc += to_f<T>(dy[o]);
+        const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+        float g[8];
+        Vec8<T>::load(dy + o, g);
+        const unsigned tag = kh * K + kw;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const unsigned a = ((j < 4 ? pk.x : pk.y) >> ((j & 3) * 8)) & 0xffu;
+          if (a == tag) acc[j] += g[j];
+        }
       }
     }
-    dx[i] = from_f<T>(acc);
+    Vec8<T>::store(dx + (((long long)n * H + h) * W + w) * C + c, acc);
   }
 }
 
@@ -379,14 +449,19 @@ B200_API int b200_col_reduce(const void* a, const void* xin, const void* y, cons
                              float* sums, long long rows, int C, int mode, int relu_mask, int dtype,
                              cudaStream_t stream) {
   if (rows <= 0 || C <= 0) return B200_OK;
-  dim3 blk(32, 8);
-  int gy = (int)((rows + 255) / 256);
-  const int cap = b200_sm_count() * 8 / ((C + 31) / 32) + 1;
+  if (C & 7) { b200_set_error("col_reduce: C %% 8 != 0"); return B200_ERR_SHAPE; }
+  const int nvc = C >> 3;
+  int nvx = 1;
+  while (nvx * 2 <= nvc && nvx < 32) nvx <<= 1;        // channel vectors per block row (power of two <= 32)
+  const int gx = (nvc + nvx - 1) / nvx;
+  const int rows_per_iter = 256 / nvx;
+  long long gy = (rows + (long long)rows_per_iter * 8 - 1) / ((long long)rows_per_iter * 8);
+  const long long cap = (long long)b200_sm_count() * 2 / gx + 1;   // few blocks: the final atomics serialise per address
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
-  dim3 grd((C + 31) / 32, gy);
-  B200_DISPATCH_DTYPE(dtype, T, (col_reduce_kernel<T><<<grd, blk, 0, stream>>>(
-      (const T*)a, (const T*)xin, (const T*)y, mean, rstd, sums, rows, C, mode, relu_mask)));
+  dim3 grd(gx, (unsigned)gy);
+  B200_DISPATCH_DTYPE(dtype, T, (col_reduce_kernel<T><<<grd, 256, 0, stream>>>(
+      (const T*)a, (const T*)xin, (const T*)y, mean, rstd, sums, rows, C, mode, relu_mask, nvx)));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -404,7 +479,14 @@ B200_API int b200_bn_apply(const void* x, const float* mean, const float* rstd, 
   if (rows <= 0) return B200_OK;
   if (C & 7) { b200_set_error("bn_apply: C %% 8 != 0"); return B200_ERR_SHAPE; }
   const long long total = rows * (C >> 3);
-  B200_DISPATCH_DTYPE(dtype, T, (bn_apply_kernel<T><<<ew_grid(total, 256), 256, 0, stream>>>(
+  int grid_bn = ew_grid(total, 256);
+  {  // every thread keeps one channel vector: make (grid * 256) a multiple of C/8
+    const int c8n = C >> 3;
+    int unit = c8n;
+    while (unit % 2 == 0 && (unit / 2) * 256 % c8n == 0) unit /= 2;   // smallest block count whose threads tile c8n
+    grid_bn = (grid_bn + unit - 1) / unit * unit;
+  }
+  B200_DISPATCH_DTYPE(dtype, T, (bn_apply_kernel<T><<<grid_bn, 256, 0, stream>>>(
       (const T*)x, mean, rstd, gamma, beta, (const T*)residual, (T*)y, rows, C, relu)));
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -416,7 +498,14 @@ B200_API int b200_bn_bwd_apply(const void* dy, const void* x, const void* y, con
   if (rows <= 0) return B200_OK;
   if (C & 7) { b200_set_error("bn_bwd_apply: C %% 8 != 0"); return B200_ERR_SHAPE; }
   const long long total = rows * (C >> 3);
-  B200_DISPATCH_DTYPE(dtype, T, (bn_bwd_apply_kernel<T><<<ew_grid(total, 256), 256, 0, stream>>>(
+  int grid_bn = ew_grid(total, 256);
+  {
+    const int c8n = C >> 3;
+    int unit = c8n;
+    while (unit % 2 == 0 && (unit / 2) * 256 % c8n == 0) unit /= 2;
+    grid_bn = (grid_bn + unit - 1) / unit * unit;
+  }
+  B200_DISPATCH_DTYPE(dtype, T, (bn_bwd_apply_kernel<T><<<grid_bn, 256, 0, stream>>>(
       (const T*)dy, (const T*)x, (const T*)y, mean, rstd, gamma, sums, (T*)dx, (T*)dres, rows, C, relu_mask)));
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -425,7 +514,8 @@ B200_API int b200_bn_bwd_apply(const void* dy, const void* x, const void* y, con
 // forward: x -> out (+ idx, uint8 window offset of the max);  backward: a = dy, idx -> out = dx.  K <= 15.
 B200_API int b200_maxpool(const void* a, const void* x, void* idx, void* out, int N, int H, int W, int C, int K,
                           int stride, int pad, int Ho, int Wo, int backward, int dtype, cudaStream_t stream) {
-  const long long total = backward ? (long long)N * H * W * C : (long long)N * Ho * Wo * C;
+  if (C & 7) { b200_set_error("maxpool: C %% 8 != 0"); return B200_ERR_SHAPE; }
+  const long long total = (backward ? (long long)N * H * W : (long long)N * Ho * Wo) * (C >> 3);
   if (total <= 0) return B200_OK;
   B200_DISPATCH_DTYPE(dtype, T, {
     if (!backward)

@@ -28,6 +28,8 @@ struct GemmParams {
   int act;         // 0 none, 1 gelu(erf), 2 relu, 3 silu
   int accumulate;  // D += result (read-modify-write)
   int num_m_blocks, num_n_blocks, num_k_blocks, num_tiles;
+  int splits;      // split-K factor: tile index = mn_tile * splits + split; fp32 output accumulated with red.add
+  int kb_per_split;
 };
 
 // Extra state of the fused compute+collective variants (FUSED = true instantiations only).
@@ -253,7 +255,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const uint32_t full0 = (CG == 2) ? mapa(full_bar(0), 0) : full_bar(0);
       for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
         int m_blk, n_blk;
-        tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+        tile_coords(tile / p.splits, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+        const int kb0 = (tile % p.splits) * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.num_k_blocks);
         if constexpr (FUSED) m_blk = (m_blk + fp.m_rot) % p.num_m_blocks;
         const int m0 = (m_blk * CG + (int)cta_rank) * kBlockM;
         const int n0 = n_blk * BN + (int)cta_rank * kLoadN;
@@ -268,7 +272,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             fence_proxy_async_all();
           }
         }
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint32_t sb = sa + Cfg::kABytes;
@@ -311,7 +315,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(tempty_bar(as), aphase ^ 1u);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        const int kb0 = (tile % p.splits) * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.num_k_blocks);
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
@@ -322,7 +328,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                         : umma_smem_desc_sw128(sa + k * kUmmaK * 2, 16, 1024);
             const uint64_t bdesc = B_MN ? umma_smem_desc_sw128(sb + k * kUmmaK * 128, kBlockK * 128, 1024)
                                         : umma_smem_desc_sw128(sb + k * kUmmaK * 2, 16, 1024);
-            umma_f16_ss<CG>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_f16_ss<CG>(tmem_d, adesc, bdesc, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
           }
           // frees this smem stage (in both CTAs for cta_group::2) once the MMAs retire
           if constexpr (CG == 2) umma_commit_2sm(empty_bar(stage), 0x3);
@@ -342,7 +348,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const uint32_t tempty_remote = (CG == 2) ? mapa(tempty_bar(0), 0) : tempty_bar(0);
     for (int tile = cluster_id; tile < p.num_tiles; tile += num_clusters) {
       int m_blk, n_blk;
-      tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+      tile_coords(tile / p.splits, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
       if constexpr (FUSED) m_blk = (m_blk + fp.m_rot) % p.num_m_blocks;
       const int row = (m_blk * CG + (int)cta_rank) * kBlockM + quarter * 32 + lane;
       const int n_tile0 = n_blk * BN;
@@ -424,6 +430,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
               if (n0 + g * 4 < p.N) {
                 OutT* dst = drow + n0 + g * 4;
                 float4 o = make_float4(v[g * 4 + 0], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+                if (p.splits > 1) {   // split-K partial: accumulate into the (pre-zeroed or accumulating) fp32 output
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                               :: "l"(dst), "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w) : "memory");
+                  continue;
+                }
                 if (p.accumulate) {
                   const float4 b = *reinterpret_cast<const float4*>(dst);
                   o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
@@ -505,6 +516,27 @@ static int launch_gemm(const void* A, const void* B, const GemmParams& p0, long 
   p.num_n_blocks = ceil_div(p.N, BN);
   p.num_k_blocks = ceil_div(p.K, kBlockK);
   p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  // split-K: skinny outputs with a long reduction (weight gradients of convolutions / small layers) would leave most SMs
+  // idle; split the K loop over several CTAs and combine with fp32 atomics (plain fp32 output without other epilogue only)
+  p.splits = 1;
+  p.kb_per_split = p.num_k_blocks;
+  {
+    const int units = b200_sm_count() / CG;
+    const bool plain = sizeof(OutT) == 4 && p.bias == nullptr && p.residual == nullptr && p.act == 0 && p.alpha == 1.f;
+    if (plain && p.num_tiles * 2 <= units && p.num_k_blocks >= 16) {
+      int s = units / p.num_tiles;
+      const int max_by_k = p.num_k_blocks / 8;   // at least 8 k-blocks (512 reduction elements) per split
+      if (s > max_by_k) s = max_by_k;
+      if (s > 64) s = 64;
+      if (s > 1) {
+        p.kb_per_split = ceil_div(p.num_k_blocks, s);
+        p.splits = ceil_div(p.num_k_blocks, p.kb_per_split);
+        if (!p.accumulate)
+          B200_CUDA_CHECK(cudaMemset2DAsync(p.D, p.ldd * 4, 0, (size_t)p.N * 4, p.M, stream));
+        p.num_tiles *= p.splits;
+      }
+    }
+  }
 
   CUtensorMap ta, tb;
   int rc;
@@ -594,6 +626,8 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
   p.num_n_blocks = ceil_div(p.N, BN);
   p.num_k_blocks = ceil_div(p.K, kBlockK);
   p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  p.splits = 1;
+  p.kb_per_split = p.num_k_blocks;
   CUtensorMap ta, tb;
   {
     const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.M};

@@ -134,6 +134,22 @@ def group_simt(results):
     import torch
 
     dev = "cuda"
+    # split-K path: skinny fp32 outputs with a long reduction (conv / small-layer weight gradients)
+    torch.manual_seed(1)
+    for (M, N, K, amn, bmn) in [(64, 576, 50048, 1, 1), (128, 128, 16384, 0, 0), (256, 1152, 25088, 1, 1)]:
+        A = (torch.randn(M, K, device=dev) * 0.1).bfloat16()
+        B = (torch.randn(N, K, device=dev) * 0.1).bfloat16()
+        ref = A.float() @ B.float().t()
+        As = A.t().contiguous() if amn else A
+        Bs = B.t().contiguous() if bmn else B
+        D = torch.full((M, N), float("nan"), device=dev, dtype=torch.float32)
+        _gemm_raw(As, Bs, D, M, N, K, amn, bmn, 0)
+        _check(f"gemm split-K {M}x{N}x{K} a_mn={amn}", D, ref, 5e-2, 1e-2, results)
+        D2 = torch.ones((M, N), device=dev, dtype=torch.float32)
+        _gemm_raw(As, Bs, D2, M, N, K, amn, bmn, 0, accumulate=1)
+        _check(f"gemm split-K accumulate {M}x{N}x{K}", D2, ref + 1, 5e-2, 1e-2, results)
+        ms = _time(lambda: _gemm_raw(As, Bs, D, M, N, K, amn, bmn, 0))
+        print(f"[TIME] gemm split-K {M}x{N}x{K}: {ms*1e3:.1f} us {2.0*M*N*K/ms/1e9:.0f} TFLOP/s", flush=True)
     for (M, N, K) in [(32, 64, 10), (7, 2, 64), (50, 16, 20)]:
         A = torch.randn(M, K, device=dev).bfloat16()
         B = torch.randn(N, K, device=dev).bfloat16()
