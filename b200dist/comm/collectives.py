@@ -135,9 +135,22 @@ class Communicator:
         return self.all_gather_from(out, buf, 0, nbytes, channel)
 
     def all_gather_from(self, out: torch.Tensor, src: PeerBuffer, offset_bytes: int, nbytes: int,
-                        channel: int = 1) -> torch.Tensor:
-        """Zero-copy variant: every rank's shard already lives in the symmetric buffer ``src``."""
+                        channel: int = 1, copy_engine: bool = False) -> torch.Tensor:
+        """Zero-copy variant: every rank's shard already lives in the symmetric buffer ``src``.
+
+        ``copy_engine=True`` moves the payload with DMA peer copies (one per peer) behind a flag barrier instead
+        of an SM kernel: nothing competes with the compute kernels it overlaps.  The caller must guarantee that
+        nobody rewrites the shards before every rank has issued its next collective on this channel (true for FSDP:
+        the next writer is the fused reduce-scatter/AdamW of the same unit, which itself waits for all ranks)."""
         assert out.is_contiguous() and out.numel() * out.element_size() >= nbytes * self.world
+        if copy_engine:
+            L.call("comm_barrier", *self._ctx(self.flags, channel), self._s())   # all shards are final
+            base = out.data_ptr()
+            for d in range(self.world):
+                p = (self.rank + d) % self.world
+                L.check(L.load().b200_peer_memcpy(C.c_void_p(base + p * nbytes), C.c_void_p(src.ptrs[p] + offset_bytes),
+                                                  C.c_size_t(nbytes), self._s()), "peer_memcpy")
+            return out
         L.call("comm_allgather", *self._ctx(src, channel), L.ptr(out), LL(offset_bytes), LL(nbytes), I(self.max_ctas),
                self._s())
         return out

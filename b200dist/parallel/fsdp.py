@@ -77,7 +77,7 @@ def _default_units(module: nn.Module):
 class FSDP(nn.Module):
     def __init__(self, module: nn.Module, process_group=None, units: Optional[List] = None,
                  reshard_after_forward: bool = True, fused_optimizer: bool = True,
-                 comm_max_ctas: int = 64, sync_module_states: bool = True):
+                 comm_max_ctas: int = 64, sync_module_states: bool = True, copy_engine_gather: bool = True):
         super().__init__()
         self.module = module
         self.comm = get_communicator(process_group)
@@ -85,6 +85,7 @@ class FSDP(nn.Module):
         self.native = self.comm.native and next(module.parameters()).is_cuda
         self.reshard_after_forward = reshard_after_forward and self.world > 1
         self.fused_optimizer = fused_optimizer
+        self.copy_engine_gather = copy_engine_gather   # parameter all-gathers as DMA peer copies (no SMs)
         self.device = next(module.parameters()).device
         self.dtype = next(module.parameters()).dtype
         if self.native:
@@ -180,7 +181,8 @@ class FSDP(nn.Module):
             ev.record(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self.ag_stream):
                 self.ag_stream.wait_event(ev)
-                self.comm.all_gather_from(u.full, u.shard_buf, 0, u.shard_numel * u.full.element_size(), channel=1)
+                self.comm.all_gather_from(u.full, u.shard_buf, 0, u.shard_numel * u.full.element_size(), channel=1,
+                                          copy_engine=self.copy_engine_gather)
                 u.ag_event = torch.cuda.Event()
                 u.ag_event.record(self.ag_stream)
         else:
@@ -208,7 +210,9 @@ class FSDP(nn.Module):
             u.sink_written = [False] * len(u.params)
             for i, p in enumerate(u.params):
                 p.register_post_accumulate_grad_hook(self._make_grad_hook(u, i))
-                if self.native and self.world > 1 and p.dim() == 2 and p.dtype == torch.bfloat16:
+                # (not for the root unit: its first gradient (LM head) and last one (embedding) bracket the whole
+                # backward pass, so it would pin one of the two staging buffers while the blocks rotate through them)
+                if self.native and self.world > 1 and p.dim() == 2 and p.dtype == torch.bfloat16 and u is not self.root_unit:
                     p._b200_grad_sink = self._make_sink(u, i)
 
     def _next_unit(self, u: _Unit, step: int) -> Optional[_Unit]:

@@ -463,6 +463,13 @@ B200_API int b200_peer_close(void* p) {
   return B200_OK;
 }
 
+// Copy-engine transfer between (peer-mapped) device buffers: no SM is involved, so an all-gather built from
+// barrier + peer copies leaves every SM to the GEMMs it overlaps with.
+B200_API int b200_peer_memcpy(void* dst, const void* src, size_t bytes, cudaStream_t stream) {
+  B200_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, stream));
+  return B200_OK;
+}
+
 // ------------------------------------------------------------------ collectives
 // ctx layout passed from Python (all pointers are device addresses valid on this GPU):
 //   data_ptrs[world], flag_ptrs[world], counter, rank, world, channel, seq
