@@ -39,6 +39,10 @@ class Communicator:
         self.max_ctas = 0
         self.oneshot_threshold = 256 << 10
         self._seq = [0] * N_CHANNELS
+        self.push_threshold = 256 << 10   # all-reduce messages up to this size take the push (latency) path
+        self._push_slots = [None] * N_CHANNELS
+        self.broadcast2_min_world = 3     # two-stage broadcast pays off once the root would serve >= 2 readers
+        self._push_count = [0] * N_CHANNELS
         if self.native:
             self.flags = PeerBuffer(64 << 10, group, self.device)
             self.staging = [None] * N_CHANNELS
@@ -102,6 +106,10 @@ class Communicator:
         assert t.is_contiguous() and out.is_contiguous()
         n = t.numel()
         item = t.element_size()
+        if (algo in (0, 3) and n % 8 == 0 and n * item <= self.push_threshold and t.data_ptr() % 16 == 0
+                and out.data_ptr() % 16 == 0 and t.dtype in (torch.bfloat16, torch.float32)
+                and out.dtype in (torch.bfloat16, torch.float32)):
+            return self._all_reduce_push(t, out, scale, channel)
         pad_to = 8 * self.world
         n_pad = (n + pad_to - 1) // pad_to * pad_to
         buf = self._stage(channel, n_pad * item)
@@ -117,6 +125,18 @@ class Communicator:
                I(L.dtype_code(t.dtype)), I(L.dtype_code(out.dtype)), I(algo), L.ptr(self.gate), I(self.max_ctas), self._s())
         if not direct:
             out.reshape(-1).copy_(dst[:n])
+        return out
+
+    def _all_reduce_push(self, t, out, scale, channel):
+        """Latency path (<= push_threshold bytes): one kernel, no staging copy-in / copy-out, no depart handshake."""
+        slots = self._push_slots[channel]
+        if slots is None:   # collective allocation, same order on every rank
+            slots = self._push_slots[channel] = PeerBuffer(2 * self.world * self.push_threshold, self.group, self.device)
+        self._push_count[channel] += 1
+        slot_elems = self.push_threshold // t.element_size()
+        L.call("comm_allreduce_push", *self._ctx(slots, channel), L.ptr(t), L.ptr(out), LL(t.numel()), F(scale),
+               I(L.dtype_code(t.dtype)), I(L.dtype_code(out.dtype)), LL(slot_elems), I(self._push_count[channel] & 1),
+               self._s())
         return out
 
     # ------------------------------------------------------------------ all-gather
@@ -179,9 +199,37 @@ class Communicator:
         return out
 
     def rs_adamw_from(self, src: PeerBuffer, offset_elems: int, in_dtype: torch.dtype, n: int, grad_scale: float,
-                      master, lowp, m, v, *, lr, beta1, beta2, eps, wd, step, channel: int = 2):
-        """Fused gradient reduce-scatter + sharded AdamW update (FSDP)."""
+                      master, lowp, m, v, *, lr, beta1, beta2, eps, wd, step, channel: int = 2,
+                      copy_engine: bool = False):
+        """Fused gradient reduce-scatter + sharded AdamW update (FSDP).
+
+        ``copy_engine=True``: the peers' slices of this rank's chunk are first pulled into local scratch by DMA
+        peer copies (flag barrier before = every rank's gradients are final; flag barrier after = every rank has
+        finished reading, so the staging buffers may be rewritten), then ONE local kernel sums the ``world`` slabs
+        and applies AdamW at HBM speed.  NVLink traffic never occupies an SM, so the backward GEMMs this overlaps
+        keep the whole chip.  Slab order matches the pull kernel's summation order: results are bit-identical."""
         bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
+        if copy_engine and self.world > 1:
+            esz = torch.empty((), dtype=in_dtype).element_size()
+            nbytes = n * esz
+            need = nbytes * (self.world - 1)
+            if getattr(self, "_rs_scratch", None) is None or self._rs_scratch.numel() < need:
+                self._rs_scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            lib, s = L.load(), self._s()
+            L.call("comm_barrier", *self._ctx(self.flags, channel), s)
+            off = (offset_elems + self.rank * n) * esz
+            slabs = (C.c_void_p * self.world)()
+            slabs[0] = src.ptrs[self.rank] + off
+            for d in range(1, self.world):
+                dst = self._rs_scratch.data_ptr() + (d - 1) * nbytes
+                L.check(lib.b200_peer_memcpy(C.c_void_p(dst), C.c_void_p(src.ptrs[(self.rank + d) % self.world] + off),
+                                             C.c_size_t(nbytes), s), "peer_memcpy")
+                slabs[d] = dst
+            L.call("comm_barrier", *self._ctx(self.flags, channel), s)
+            L.call("comm_rs_adamw_local", slabs, I(self.world), LL(n), F(grad_scale), I(L.dtype_code(in_dtype)),
+                   L.ptr(master), L.ptr(lowp), L.ptr(m), L.ptr(v), F(lr), F(beta1), F(beta2), F(eps), F(wd), F(bc1),
+                   F(bc2), I(self.max_ctas), s)
+            return
         L.call("comm_rs_adamw", *self._ctx(src, channel), LL(offset_elems), LL(n), F(grad_scale),
                I(L.dtype_code(in_dtype)), L.ptr(master), L.ptr(lowp), L.ptr(m), L.ptr(v), F(lr), F(beta1), F(beta2),
                F(eps), F(wd), F(bc1), F(bc2), I(self.max_ctas), self._s())
@@ -199,7 +247,10 @@ class Communicator:
         buf = self._stage(channel, pad)
         if self.rank == src:
             buf.tensor(torch.uint8, 0, nbytes).copy_(t.reshape(-1).view(torch.uint8))
-        if pad == nbytes:
+        if pad == nbytes and self.world >= self.broadcast2_min_world and nbytes >= (1 << 20) and nbytes % (16 * self.world) == 0:
+            L.call("comm_broadcast2", *self._ctx(buf, channel), L.ptr(t), LL(0), LL(pad), I(src), L.ptr(self.gate),
+                   I(self.max_ctas), self._s())
+        elif pad == nbytes:
             L.call("comm_broadcast", *self._ctx(buf, channel), L.ptr(t), LL(0), LL(pad), I(src), I(self.max_ctas), self._s())
         else:
             tmp = torch.empty(pad, dtype=torch.uint8, device=t.device)

@@ -56,6 +56,19 @@ def model_args_for(name: str, **overrides) -> ModelArgs:
     return ModelArgs(**cfg)
 
 
+def _trunc_normal_(w: torch.Tensor, std: float, a: float = -2.0, b: float = 2.0) -> None:
+    """``nn.init.trunc_normal_`` evaluated in fp32.  The inverse-CDF sampling is not usable in bf16 (it yields std ~0.13
+    for a requested 0.02), so low-precision weights are drawn in fp32 and rounded once; fp32 weights are initialised in
+    place, which keeps the random stream identical to the reference model's (:185-188,269-272,414-426)."""
+    if w.dtype == torch.float32:
+        nn.init.trunc_normal_(w, mean=0.0, std=std, a=a, b=b)
+        return
+    tmp = torch.empty(w.shape, dtype=torch.float32, device=w.device)
+    nn.init.trunc_normal_(tmp, mean=0.0, std=std, a=a, b=b)
+    with torch.no_grad():
+        w.copy_(tmp)
+
+
 def ffn_hidden_dim(dim: int, multiple_of: int, ffn_dim_multiplier: Optional[float]) -> int:
     """int(2 * 4 * dim / 3) rounded up to ``multiple_of`` (reference :256-260): 11008 / 13824."""
     hidden = int(2 * (4 * dim) / 3)
@@ -114,8 +127,8 @@ class Attention(nn.Module):
 
     def init_weights(self, init_std: float):
         for lin in (self.wq, self.wk, self.wv):
-            nn.init.trunc_normal_(lin.weight, mean=0.0, std=0.02)
-        nn.init.trunc_normal_(self.wo.weight, mean=0.0, std=init_std)
+            _trunc_normal_(lin.weight, 0.02)
+        _trunc_normal_(self.wo.weight, init_std)
 
     def forward(self, x, freqs_cis, residual=None, pos_offset: int = 0):
         bsz, seqlen, _ = x.shape
@@ -142,9 +155,9 @@ class FeedForward(nn.Module):
         return self.w2(ops.swiglu(self.w1(x), self.w3(x)), residual=residual)
 
     def init_weights(self, init_std: float):
-        nn.init.trunc_normal_(self.w1.weight, mean=0.0, std=0.02)
+        _trunc_normal_(self.w1.weight, 0.02)
         for lin in (self.w2, self.w3):
-            nn.init.trunc_normal_(lin.weight, mean=0.0, std=init_std)
+            _trunc_normal_(lin.weight, init_std)
 
 
 class TransformerBlock(nn.Module):
@@ -211,7 +224,7 @@ class Transformer(nn.Module):
             layer.init_weights()
         self.norm.reset_parameters()
         std = self.model_args.dim ** -0.5
-        nn.init.trunc_normal_(self.output.weight, mean=0.0, std=std, a=-3 * std, b=3 * std)
+        _trunc_normal_(self.output.weight, std, a=-3 * std, b=3 * std)
 
     def embed(self, tokens):
         return self.tok_embeddings(tokens)
@@ -253,3 +266,67 @@ class Transformer(nn.Module):
         n_mm = sum(p.numel() for n, p in self.named_parameters() if p.dim() == 2 and "tok_embeddings" not in n)
         attn = a.n_layers * (4 * seq_len * a.dim / 2) * 3.5
         return 6.0 * n_mm + attn
+
+
+class TransformerStage(nn.Module):
+    """Contiguous slice of a ``Transformer`` for pipeline parallelism (BASELINE config 5a: Llama-2 7B, PP 4 x DP 2).
+
+    Only this stage's modules are built (a rank never materialises the other stages' weights).  Parameter names are
+    those of the full model (``layers.{global index}.…``, ``tok_embeddings``, ``norm``, ``output``), so the union of
+    the stage state dicts IS the full model's state dict.  The first stage maps tokens -> hidden states, middle stages
+    hidden -> hidden, the last stage hidden -> fp32 logits.  The reference has no Llama pipeline (its PP recipe trains
+    a 256-dim encoder, scripts/04_pipeline_parallel_pp/03_pipeline_training.py:51-120); the layer split follows its
+    "equal number of blocks per stage" rule (:92-103).
+    """
+
+    def __init__(self, model_args: ModelArgs, stage_index: int, num_stages: int, init: bool = True):
+        super().__init__()
+        self.model_args, self.stage_index, self.num_stages = model_args, stage_index, num_stages
+        per = (model_args.n_layers + num_stages - 1) // num_stages
+        self.layer_ids = list(range(stage_index * per, min(model_args.n_layers, (stage_index + 1) * per)))
+        self.is_first, self.is_last = stage_index == 0, stage_index == num_stages - 1
+        self.vocab_size = model_args.vocab_size
+        if self.is_first:
+            self.tok_embeddings = Embedding(model_args.vocab_size, model_args.dim)
+        self.layers = nn.ModuleDict({str(i): TransformerBlock(i, model_args) for i in self.layer_ids})
+        if self.is_last:
+            self.norm = RMSNorm(model_args.dim, eps=model_args.norm_eps)
+            self.output = Linear(model_args.dim, model_args.vocab_size)
+        self._freqs = None   # complex64 RoPE table, built lazily on the activation's device (never cast by .to(bf16))
+        if init:
+            self.init_weights()
+
+    def init_weights(self):
+        if self.is_first:
+            nn.init.normal_(self.tok_embeddings.weight)
+        for layer in self.layers.values():
+            layer.init_weights()
+        if self.is_last:
+            self.norm.reset_parameters()
+            std = self.model_args.dim ** -0.5
+            _trunc_normal_(self.output.weight, std, a=-3 * std, b=3 * std)
+
+    def forward(self, x: torch.Tensor, pos_offset: int = 0):
+        h = self.tok_embeddings(x) if self.is_first else x
+        if self._freqs is None or self._freqs.device != h.device:
+            a = self.model_args
+            self._freqs = ops.precompute_freqs_cis(a.dim // a.n_heads, a.max_seq_len * 2).to(h.device)
+        for layer in self.layers.values():
+            h = layer(h, self._freqs, pos_offset)
+        if self.is_last:
+            return self.output(self.norm(h)).float()
+        return h
+
+    @classmethod
+    def from_name(cls, name: str, stage_index: int, num_stages: int, device=None, dtype=None, **overrides):
+        args = model_args_for(name, **overrides)
+        prev = torch.get_default_dtype()
+        try:
+            if dtype is not None:
+                torch.set_default_dtype(dtype)
+            if device is not None:
+                with torch.device(device):
+                    return cls(args, stage_index, num_stages)
+            return cls(args, stage_index, num_stages)
+        finally:
+            torch.set_default_dtype(prev)

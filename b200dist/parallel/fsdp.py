@@ -77,7 +77,8 @@ def _default_units(module: nn.Module):
 class FSDP(nn.Module):
     def __init__(self, module: nn.Module, process_group=None, units: Optional[List] = None,
                  reshard_after_forward: bool = True, fused_optimizer: bool = True,
-                 comm_max_ctas: int = 64, sync_module_states: bool = True, copy_engine_gather: bool = True):
+                 comm_max_ctas: int = 64, sync_module_states: bool = True, copy_engine_gather: bool = True,
+                 copy_engine_reduce: bool = True):
         super().__init__()
         self.module = module
         self.comm = get_communicator(process_group)
@@ -86,6 +87,7 @@ class FSDP(nn.Module):
         self.reshard_after_forward = reshard_after_forward and self.world > 1
         self.fused_optimizer = fused_optimizer
         self.copy_engine_gather = copy_engine_gather   # parameter all-gathers as DMA peer copies (no SMs)
+        self.copy_engine_reduce = copy_engine_reduce   # gradient slices pulled by DMA, then a local reduce+AdamW kernel
         self.device = next(module.parameters()).device
         self.dtype = next(module.parameters()).dtype
         if self.native:
@@ -316,7 +318,8 @@ class FSDP(nn.Module):
                     self._ensure_state(u)
                     self.comm.rs_adamw_from(stage, 0, self.dtype, u.shard_numel, 1.0 / self.world, u.master, u.shard,
                                             u.m, u.v, lr=hp["lr"], beta1=hp["betas"][0], beta2=hp["betas"][1],
-                                            eps=hp["eps"], wd=hp["weight_decay"], step=t, channel=2)
+                                            eps=hp["eps"], wd=hp["weight_decay"], step=t, channel=2,
+                                            copy_engine=self.copy_engine_reduce)
                 else:
                     if u.grad_shard is None:
                         u.grad_shard = torch.zeros(u.shard_numel, dtype=torch.float32, device=self.device)

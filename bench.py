@@ -101,6 +101,7 @@ def parse():
     ap.add_argument("--lr", type=float, default=3e-4)
     ap.add_argument("--fsdp-ctas", type=int, default=64, help="CTAs per peer-memory collective kernel (FSDP)")
     ap.add_argument("--kernel-gather", action="store_true", help="FSDP all-gather with the SM pull kernel instead of DMA peer copies")
+    ap.add_argument("--kernel-reduce", action="store_true", help="FSDP reduce-scatter+AdamW pulling over NVLink from the SMs instead of DMA staging")
     ap.add_argument("--no-reshard", action="store_true", help="keep parameters gathered between forward and backward (ZeRO-2 style)")
     return ap.parse_args()
 
@@ -197,7 +198,7 @@ def run_b200dist(a, rank, world, local):
         from b200dist.parallel.fsdp import FSDP
 
         model = FSDP(model, comm_max_ctas=a.fsdp_ctas, reshard_after_forward=not a.no_reshard, sync_module_states=False,
-                     copy_engine_gather=not a.kernel_gather)
+                     copy_engine_gather=not a.kernel_gather, copy_engine_reduce=not a.kernel_reduce)
         opt = model.build_optimizer("adamw", lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1)
     else:
         opt = FusedAdamW(model.parameters(), lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1)

@@ -63,6 +63,7 @@ __device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t seq, cons
 
 // Steps 1+2.  Must be called by all threads of every block.
 __device__ __forceinline__ void comm_arrive_and_wait(const CommCtx& c) {
+  if (c.channel < 0) return;  // local variant: the payload was staged by copy engines, ranks already synchronised
   __syncthreads();
   if (blockIdx.x == 0 && threadIdx.x < c.world) {
     __threadfence_system();
@@ -75,6 +76,7 @@ __device__ __forceinline__ void comm_arrive_and_wait(const CommCtx& c) {
 // Step 4.  Must be called by all threads of every block after their last peer access.
 __device__ __forceinline__ void comm_depart(const CommCtx& c) {
   __shared__ int is_last;
+  if (c.channel < 0) return;
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
@@ -145,23 +147,73 @@ template <typename T> struct Acc8 {
   }
 };
 
-// Sum `world` peers' 8-element chunks at element offset `off` for kU consecutive grid-strided chunks:
+// fp32 vectors are 32 bytes per thread.  A lane-contiguous layout would make each 128-bit load instruction of a warp
+// touch 32 half-used 32-byte sectors, i.e. every sector would cross NVLink twice.  So whenever a full warp's worth of
+// vectors (32 x 8 floats = 1 KB) lies inside the range, lane l takes floats [4l, 4l+4) and [128 + 4l, 128 + 4l + 4) of that
+// 1 KB run: both load instructions are fully coalesced 512-byte reads.  bf16 vectors (16 bytes) are contiguous anyway.
+// Requires vector index i == lane (mod 32), true for every loop here (block size and strides are multiples of 32).
+template <typename T>
+__device__ __forceinline__ void vec_offsets(long long i, long long n8, long long& o0, long long& o1) {
+  if constexpr (sizeof(T) == 2) { o0 = i * 8; o1 = o0 + 4; }
+  else {
+    const long long w = i & ~31LL;
+    if (w + 32 <= n8) { o0 = w * 8 + (i & 31) * 4; o1 = o0 + 128; }
+    else { o0 = i * 8; o1 = o0 + 4; }
+  }
+}
+__device__ __forceinline__ void load4(const float* p, float* v) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void store4(float* p, const float* v) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, const float* v) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&a); u.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+// store / load the 8 values of vector i in the layout that input type TIn dictates (see vec_offsets)
+template <typename TIn, typename TOut>
+__device__ __forceinline__ void store_vec(TOut* out, long long i, long long n8, const float (&v)[8]) {
+  if constexpr (sizeof(TIn) == 2) Vec8<TOut>::store(out + i * 8, v);
+  else {
+    long long o0, o1;
+    vec_offsets<TIn>(i, n8, o0, o1);
+    store4(out + o0, v); store4(out + o1, v + 4);
+  }
+}
+template <typename TIn>
+__device__ __forceinline__ void load_vec_f32(const float* src, long long i, long long n8, float (&v)[8]) {
+  if constexpr (sizeof(TIn) == 2) Vec8<float>::load(src + i * 8, v);
+  else {
+    long long o0, o1;
+    vec_offsets<TIn>(i, n8, o0, o1);
+    load4(src + o0, v); load4(src + o1, v + 4);
+  }
+}
+
+// Sum `world` peers' 8-element vectors at element offset `off` for kU consecutive grid-strided vectors:
 // all kU * world 128-bit (bf16) / 2x128-bit (fp32) loads are issued before the first add, so one
 // thread keeps kU * world NVLink requests in flight (latency ~2 us needs ~1 MB in flight per GPU).
 template <typename T, int kU, int kW = kMaxRanks>
 __device__ __forceinline__ void peer_sum(const CommCtx& c, long long off, const long long (&idx)[kU],
-                                         const bool (&ok)[kU], float (&acc)[kU][8]) {
+                                         const bool (&ok)[kU], float (&acc)[kU][8], long long n8) {
   constexpr int kV = sizeof(T) == 2 ? 1 : 2;
   uint4 raw[kU][kW][kV];
 #pragma unroll
-  for (int u = 0; u < kU; ++u)
+  for (int u = 0; u < kU; ++u) {
+    long long o0 = 0, o1 = 0;
+    if (ok[u]) vec_offsets<T>(idx[u], n8, o0, o1);
 #pragma unroll
     for (int t = 0; t < kW; ++t)
       if (t < c.world && ok[u]) {
-        const T* p = reinterpret_cast<const T*>(c.data[(t + c.rank) % c.world]) + off + idx[u] * 8;
-#pragma unroll
-        for (int v = 0; v < kV; ++v) raw[u][t][v] = ld_peer_v4(reinterpret_cast<const uint4*>(p) + v);
+        const T* p = reinterpret_cast<const T*>(c.data[(t + c.rank) % c.world]) + off;
+        raw[u][t][0] = ld_peer_v4(p + o0);
+        if constexpr (kV == 2) raw[u][t][1] = ld_peer_v4(p + o1);
       }
+  }
 #pragma unroll
   for (int u = 0; u < kU; ++u) {
 #pragma unroll
@@ -236,13 +288,13 @@ __global__ void __launch_bounds__(512, 1) comm_reducescatter_kernel(CommCtx c, T
     float acc[kU][8];
 #pragma unroll
     for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < n8; }
-    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc, n8);
 #pragma unroll
     for (int u = 0; u < kU; ++u)
       if (ok[u]) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
-        Vec8<TOut>::store(out + idx[u] * 8, acc[u]);
+        store_vec<TIn, TOut>(out, idx[u], n8, acc[u]);
       }
   }
   comm_depart(c);
@@ -266,15 +318,15 @@ __global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long l
     float acc[kU][8];
 #pragma unroll
     for (int u = 0; u < kU; ++u) { idx[u] = i0 + u * stride; ok[u] = idx[u] < n8; }
-    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc);
+    peer_sum<TIn, kU, kW>(c, in_off + (long long)c.rank * n, idx, ok, acc, n8);
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       if (!ok[u]) continue;
       const long long i = idx[u];
       float pv[8], mv[8], vv[8];
-      Vec8<float>::load(master + i * 8, pv);
-      Vec8<float>::load(m + i * 8, mv);
-      Vec8<float>::load(v + i * 8, vv);
+      load_vec_f32<TIn>(master, i, n8, pv);
+      load_vec_f32<TIn>(m, i, n8, mv);
+      load_vec_f32<TIn>(v, i, n8, vv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float g = acc[u][j] * grad_scale;
@@ -282,10 +334,10 @@ __global__ void __launch_bounds__(512, 1) comm_rs_adamw_kernel(CommCtx c, long l
         vv[j] = beta2 * vv[j] + (1.f - beta2) * g * g;
         pv[j] = pv[j] * decay - step_size * (mv[j] / (sqrtf(vv[j]) / bc2_sqrt + eps));
       }
-      Vec8<float>::store(master + i * 8, pv);
-      Vec8<float>::store(m + i * 8, mv);
-      Vec8<float>::store(v + i * 8, vv);
-      if (lowp) Vec8<__nv_bfloat16>::store(lowp + i * 8, pv);
+      store_vec<TIn, float>(master, i, n8, pv);
+      store_vec<TIn, float>(m, i, n8, mv);
+      store_vec<TIn, float>(v, i, n8, vv);
+      if (lowp) store_vec<TIn, __nv_bfloat16>(lowp, i, n8, pv);
     }
   }
   comm_depart(c);
@@ -306,13 +358,13 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_oneshot_kernel(CommCtx 
     float acc[kU][8];
 #pragma unroll
     for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < n8; }
-    peer_sum<TIn, kU>(c, in_off, idx, ok, acc);
+    peer_sum<TIn, kU>(c, in_off, idx, ok, acc, n8);
 #pragma unroll
     for (int u = 0; u < kU; ++u)
       if (ok[u]) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
-        Vec8<TOut>::store(out + idx[u] * 8, acc[u]);
+        store_vec<TIn, TOut>(out, idx[u], n8, acc[u]);
       }
   }
   comm_depart(c);
@@ -337,13 +389,13 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx 
       float acc[kU][8];
 #pragma unroll
       for (int u = 0; u < kU; ++u) { idx[u] = i + u * stride; ok[u] = idx[u] < s8; }
-      peer_sum<T, kU>(c, in_off + (long long)c.rank * slice, idx, ok, acc);
+      peer_sum<T, kU>(c, in_off + (long long)c.rank * slice, idx, ok, acc, s8);
 #pragma unroll
       for (int u = 0; u < kU; ++u)
         if (ok[u]) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[u][j] *= scale;
-          Vec8<T>::store(mine + idx[u] * 8, acc[u]);
+          store_vec<T, T>(mine, idx[u], s8, acc[u]);
         }
     }
   }
@@ -356,20 +408,145 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx 
     const long long i = k - (long long)t * s8;
     float v8[8];
     // peers' reduced slices were written during this kernel: bypass the non-coherent path
-    const T* p = reinterpret_cast<const T*>(c.data[src]) + in_off + (long long)src * slice + i * 8;
+    const T* p = reinterpret_cast<const T*>(c.data[src]) + in_off + (long long)src * slice;
     if constexpr (sizeof(T) == 2) {
       uint4 u;
-      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "l"(p));
+      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "l"(p + i * 8));
       v8[0] = bf16lo(u.x); v8[1] = bf16hi(u.x); v8[2] = bf16lo(u.y); v8[3] = bf16hi(u.y);
       v8[4] = bf16lo(u.z); v8[5] = bf16hi(u.z); v8[6] = bf16lo(u.w); v8[7] = bf16hi(u.w);
     } else {
+      // s8 % 32 != 0 would break "i == lane (mod 32)" across slice boundaries: vec_offsets then stays on the safe path
+      long long o0, o1;
+      if ((s8 & 31) == 0) vec_offsets<T>(i, s8, o0, o1); else { o0 = i * 8; o1 = o0 + 4; }
       uint4 u0, u1;
-      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u0.x), "=r"(u0.y), "=r"(u0.z), "=r"(u0.w) : "l"(p));
-      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u1.x), "=r"(u1.y), "=r"(u1.z), "=r"(u1.w) : "l"(p + 4));
+      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u0.x), "=r"(u0.y), "=r"(u0.z), "=r"(u0.w) : "l"(p + o0));
+      asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(u1.x), "=r"(u1.y), "=r"(u1.z), "=r"(u1.w) : "l"(p + o1));
       v8[0] = __uint_as_float(u0.x); v8[1] = __uint_as_float(u0.y); v8[2] = __uint_as_float(u0.z); v8[3] = __uint_as_float(u0.w);
       v8[4] = __uint_as_float(u1.x); v8[5] = __uint_as_float(u1.y); v8[6] = __uint_as_float(u1.z); v8[7] = __uint_as_float(u1.w);
+      TOut* o = out + (long long)src * slice;
+      store4(o + o0, v8); store4(o + o1, v8 + 4);
+      continue;
     }
     Vec8<TOut>::store(out + (long long)src * slice + i * 8, v8);
+  }
+  comm_depart(c);
+}
+
+// push one-shot (latency path for small messages): no staging copy, no depart handshake.
+//   1. every rank stores its input straight from the user tensor into slot [parity][rank] of EVERY peer's slot buffer;
+//   2. the last block to finish raises this rank's arrive flag at every peer (release: the stores are visible first);
+//   3. each rank waits for all flags and sums the `world` slots out of its OWN memory in rank order, so the result is
+//      bitwise identical on every rank.
+// Two slot sets alternate (parity): a rank can run at most one collective ahead of the slowest peer (it needs that
+// peer's flag to pass step 3), so the set it overwrites was fully consumed two collectives ago.
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(512, 1) comm_allreduce_push_kernel(CommCtx c, const TIn* __restrict__ in,
+                                                                    TOut* __restrict__ out, long long n, float scale,
+                                                                    long long slot_elems, int parity) {
+  __shared__ int is_last_p;
+  constexpr int kV = sizeof(TIn) == 2 ? 1 : 2;    // 16-byte pieces per 8-element vector
+  const long long nv = (n >> 3) * kV;             // 16-byte pieces in the message
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const uint4* src = reinterpret_cast<const uint4*>(in);
+  const long long my_slot16 = ((long long)(parity * c.world + c.rank) * slot_elems * sizeof(TIn)) >> 4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv; i += stride) {
+    const uint4 v = src[i];
+#pragma unroll
+    for (int t = 0; t < kMaxRanks; ++t)
+      if (t < c.world) reinterpret_cast<uint4*>(c.data[(c.rank + t) % c.world])[my_slot16 + i] = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(c.counter + 128 + c.channel, 1u) + 1u;
+    is_last_p = (done == gridDim.x);
+    if (is_last_p) c.counter[128 + c.channel] = 0;
+  }
+  __syncthreads();
+  if (is_last_p && threadIdx.x < c.world) {
+    __threadfence_system();
+    st_release_sys(flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) spin_until(flag_row(c, c.rank, 0) + threadIdx.x, c.seq, "push");
+  __syncthreads();
+  const uint4* slots = reinterpret_cast<const uint4*>(c.data[c.rank]);
+  const long long set16 = ((long long)parity * c.world * slot_elems * sizeof(TIn)) >> 4;
+  const long long slot16 = (slot_elems * sizeof(TIn)) >> 4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv; i += stride) {
+    float acc[sizeof(TIn) == 2 ? 8 : 4];
+#pragma unroll
+    for (int j = 0; j < (int)(sizeof(acc) / sizeof(float)); ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int t = 0; t < kMaxRanks; ++t)
+      if (t < c.world) {
+        uint4 r;   // written by a peer during this kernel: coherent load
+        asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(slots + set16 + t * slot16 + i));
+        if constexpr (sizeof(TIn) == 2) {
+          acc[0] += bf16lo(r.x); acc[1] += bf16hi(r.x); acc[2] += bf16lo(r.y); acc[3] += bf16hi(r.y);
+          acc[4] += bf16lo(r.z); acc[5] += bf16hi(r.z); acc[6] += bf16lo(r.w); acc[7] += bf16hi(r.w);
+        } else {
+          acc[0] += __uint_as_float(r.x); acc[1] += __uint_as_float(r.y);
+          acc[2] += __uint_as_float(r.z); acc[3] += __uint_as_float(r.w);
+        }
+      }
+#pragma unroll
+    for (int j = 0; j < (int)(sizeof(acc) / sizeof(float)); ++j) acc[j] *= scale;
+    if constexpr (sizeof(TIn) == 2) Vec8<TOut>::store(out + i * 8, reinterpret_cast<const float(&)[8]>(acc));
+    else store4(out + i * 4, acc);
+  }
+}
+
+// two-stage broadcast for large messages: rank r first pulls slice r from the root into its own symmetric buffer
+// (root egress = one message), then after a rank+grid barrier every rank gathers the other slices from their new
+// owners, so the root's links stop being the bottleneck (a flat pull costs the root (W-1) messages of egress).
+// n16 must be a multiple of `world`; grid must be co-resident.
+__global__ void __launch_bounds__(512, 1) comm_broadcast2_kernel(CommCtx c, uint4* __restrict__ out, long long in_off16,
+                                                                long long n16, int root, uint32_t* local_gate) {
+  comm_arrive_and_wait(c);
+  const long long s16 = n16 / c.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kBU = 8;
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(c.data[root]) + in_off16 + (long long)c.rank * s16;
+    uint4* keep = reinterpret_cast<uint4*>(c.data[c.rank]) + in_off16 + (long long)c.rank * s16;
+    uint4* dst = out + (long long)c.rank * s16;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < s16; i += stride * kBU) {
+      uint4 v[kBU];
+#pragma unroll
+      for (int u = 0; u < kBU; ++u) if (i + u * stride < s16) v[u] = ld_peer_v4(src + i + u * stride);
+#pragma unroll
+      for (int u = 0; u < kBU; ++u)
+        if (i + u * stride < s16) {
+          if (c.rank != root) keep[i + u * stride] = v[u];
+          dst[i + u * stride] = v[u];
+        }
+    }
+  }
+  comm_grid_barrier(c, local_gate);
+  const long long rest = s16 * (c.world - 1);
+  for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < rest; k += stride * kBU) {
+    uint4 v[kBU];
+#pragma unroll
+    for (int u = 0; u < kBU; ++u) {
+      const long long kk = k + u * stride;
+      if (kk < rest) {
+        const int t = (int)(kk / s16) + 1;
+        const int owner = (c.rank + t) % c.world;
+        const uint4* p = reinterpret_cast<const uint4*>(c.data[owner]) + in_off16 + (long long)owner * s16 + (kk - (long long)(t - 1) * s16);
+        asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(p));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kBU; ++u) {
+      const long long kk = k + u * stride;
+      if (kk < rest) {
+        const int t = (int)(kk / s16) + 1;
+        const int owner = (c.rank + t) % c.world;
+        out[(long long)owner * s16 + (kk - (long long)(t - 1) * s16)] = v[u];
+      }
+    }
   }
   comm_depart(c);
 }
@@ -559,6 +736,29 @@ B200_API int b200_comm_rs_adamw(COMM_ARGS, long long in_off, long long n, float 
   return B200_OK;
 }
 
+// Same update, but the `world` gradient slabs are all LOCAL pointers (slab_ptrs[r] = n elements contributed by rank r):
+// the caller moved the peers' slices here with copy-engine transfers (b200_peer_memcpy) between two flag barriers, so
+// this kernel touches no peer memory, needs no rank synchronisation and runs at HBM speed instead of NVLink speed.
+B200_API int b200_comm_rs_adamw_local(const void* const* slab_ptrs, int world, long long n, float grad_scale, int in_dtype,
+                                      float* master, void* lowp, float* m, float* v, float lr, float beta1,
+                                      float beta2, float eps, float wd, float bc1, float bc2, int max_ctas,
+                                      cudaStream_t stream) {
+  using namespace b200;
+  if (world < 1 || world > kMaxRanks) { b200_set_error("rs_adamw_local: world %d out of range", world); return B200_ERR_LIMIT; }
+  if (n & 7) { b200_set_error("rs_adamw_local: shard elements must be a multiple of 8"); return B200_ERR_SHAPE; }
+  CommCtx c = {};
+  for (int r = 0; r < world; ++r) c.data[r] = const_cast<void*>(slab_ptrs[r]);
+  c.rank = 0; c.world = world; c.channel = -1;
+  const int grid = comm_grid(n >> 3, 512, max_ctas);
+#define RSA(TI, KW) comm_rs_adamw_kernel<TI, KW><<<grid, 512, 0, stream>>>(c, 0, n, grad_scale, master, \
+        (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, sqrtf(bc2))
+  if (in_dtype == 0) { if (world <= 2) RSA(__nv_bfloat16, 2); else if (world <= 4) RSA(__nv_bfloat16, 4); else RSA(__nv_bfloat16, 8); }
+  else { if (world <= 2) RSA(float, 2); else if (world <= 4) RSA(float, 4); else RSA(float, 8); }
+#undef RSA
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 // algo: 1 = one-shot, 2 = two-shot (n % (8*world) == 0; needs a co-resident grid, capped at the SM count)
 B200_API int b200_comm_allreduce(COMM_ARGS, void* out, long long in_off, long long n, float scale,
                                  int in_dtype, int out_dtype, int algo, void* local_gate, int max_ctas,
@@ -599,6 +799,47 @@ B200_API int b200_comm_slab_reduce(COMM_ARGS, void* out, const void* residual, l
   if (n & 7) { b200_set_error("slab_reduce: elements must be a multiple of 8"); return B200_ERR_SHAPE; }
   comm_slab_reduce_kernel<<<comm_grid(n >> 3, 512, max_ctas), 512, 0, stream>>>(
       COMM_CTX, (__nv_bfloat16*)out, (const __nv_bfloat16*)residual, n);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Small-message all-reduce without staging copies (see comm_allreduce_push_kernel).  data_ptrs = the symmetric SLOT
+// buffer [2][world][slot_elems] of in_dtype; `in` / `out` are ordinary device tensors (may alias); n % 8 == 0,
+// n <= slot_elems, `in` and `out` 16-byte aligned.  parity must alternate between consecutive calls on a channel.
+B200_API int b200_comm_allreduce_push(COMM_ARGS, const void* in, void* out, long long n, float scale, int in_dtype,
+                                      int out_dtype, long long slot_elems, int parity, cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if ((n & 7) || n > slot_elems || (slot_elems & 7) || ((uintptr_t)in & 15) || ((uintptr_t)out & 15)) {
+    b200_set_error("allreduce_push: n=%lld slot=%lld must be multiples of 8 with n <= slot, 16-byte aligned tensors", n, slot_elems);
+    return B200_ERR_SHAPE;
+  }
+  const long long nv = (n >> 3) * (in_dtype == 0 ? 1 : 2);
+  const int grid = comm_grid(nv, 512, 16);
+#define ARP(TI, TO) comm_allreduce_push_kernel<TI, TO><<<grid, 512, 0, stream>>>(COMM_CTX, (const TI*)in, (TO*)out, n, scale, \
+                                                                               slot_elems, parity & 1)
+  if (in_dtype == 0 && out_dtype == 0) ARP(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == 0 && out_dtype == 1) ARP(__nv_bfloat16, float);
+  else if (in_dtype == 1 && out_dtype == 1) ARP(float, float);
+  else if (in_dtype == 1 && out_dtype == 0) ARP(float, __nv_bfloat16);
+  else { b200_set_error("allreduce_push: bad dtype"); return B200_ERR_UNSUPPORTED; }
+#undef ARP
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Large-message broadcast in two stages (see comm_broadcast2_kernel): bytes % (16 * world) == 0.
+B200_API int b200_comm_broadcast2(COMM_ARGS, void* out, long long in_off_bytes, long long bytes, int root,
+                                  void* local_gate, int max_ctas, cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if (((bytes | in_off_bytes) & 15) || (bytes >> 4) % world) {
+    b200_set_error("broadcast2: bytes must be a multiple of 16 * world");
+    return B200_ERR_SHAPE;
+  }
+  int cap = b200_sm_count();
+  if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;
+  uint32_t* gate = reinterpret_cast<uint32_t*>(local_gate) + channel;
+  comm_broadcast2_kernel<<<comm_grid((bytes >> 4) / world, 512, cap), 512, 0, stream>>>(
+      COMM_CTX, (uint4*)out, in_off_bytes >> 4, bytes >> 4, root, gate);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -35,6 +35,23 @@ B200DIST_API int b200_gemm_bf16(const void* A, const void* B, void* D, int M, in
                             long long ldr, float alpha, int act, int accumulate, int config,
                             int max_ctas, cudaStream_t stream);
 
+/* ---- Fused GEMM + collective over peer memory (TP / SP hot ops) ----
+ * ag_gemm: D[M,N] = allgather_seq(A) . B^T.  a_ptrs[r] = rank r's [M/world, K] bf16 shard in symmetric memory; comm CTAs
+ *          inside the GEMM grid pull peer shards with TMA bulk copies and flag each `rows_per_flag` rows ready, the MMA
+ *          CTAs consume them tile by tile (replaces all_gather_into_tensor + cuBLAS behind ColwiseParallel,
+ *          scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:129-141).
+ * gemm_rs: partial = A . B^T is stored row-wise straight into the owning rank's staging slab (stage_ptrs[o] =
+ *          [world, M/world, N] bf16); b200_comm_slab_reduce then sums the slabs (+residual) on the owner
+ *          (replaces cuBLAS + reduce_scatter_tensor behind RowwiseParallel(output_layouts=Shard(1)), same file :136,143). */
+B200DIST_API int b200_ag_gemm_bf16(const void* const* a_ptrs, const void* B, void* D, int M, int N, int K, long long ldb,
+                               long long ldd, int b_mn_major, const void* bias, const void* residual, long long ldr,
+                               int act, void* flags, int rows_per_flag, unsigned epoch, int n_comm_clusters,
+                               const void* const* sig_ptrs, void* counter, int channel, unsigned seq, int world,
+                               int rank, cudaStream_t stream);
+B200DIST_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* stage_ptrs, int M, int N, int K,
+                               long long lda, long long ldb, int b_mn_major, const void* residual, long long ldr,
+                               int world, int rank, cudaStream_t stream);
+
 /* ---- Attention (tcgen05 flash attention) ----
  * replaces F.scaled_dot_product_attention: fsdp_tp/llama2_model.py:218-223; explicit softmax attention: scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122 */
 B200DIST_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, void* O, float* LSE,
@@ -147,6 +164,8 @@ B200DIST_API int b200_peer_free(void* p);
 B200DIST_API int b200_peer_export(void* p, unsigned char* handle64);
 B200DIST_API int b200_peer_import(const unsigned char* handle64, void** out);
 B200DIST_API int b200_peer_close(void* p);
+/* copy-engine (DMA) transfer between local and imported peer memory: the FSDP parameter all-gather path, no SMs used */
+B200DIST_API int b200_peer_memcpy(void* dst, const void* src, size_t bytes, cudaStream_t stream);
 
 /* ---- Collectives over NVLink peer memory ----
  * replace c10d/NCCL: tests/torch_comm_bench.py:49,79; DDP / FSDP / DTensor implicit collectives */
@@ -167,11 +186,27 @@ B200DIST_API int b200_comm_rs_adamw(const void* const* data_ptrs, const void* co
                                 float* master, void* lowp, float* m, float* v, float lr, float beta1,
                                 float beta2, float eps, float wd, float bc1, float bc2, int max_ctas,
                                 cudaStream_t stream);
+/* local variant: slab_ptrs[r] are `world` LOCAL n-element gradient slabs (peers' slices staged by b200_peer_memcpy) */
+B200DIST_API int b200_comm_rs_adamw_local(const void* const* slab_ptrs, int world, long long n, float grad_scale, int in_dtype,
+                                      float* master, void* lowp, float* m, float* v, float lr, float beta1,
+                                      float beta2, float eps, float wd, float bc1, float bc2, int max_ctas,
+                                      cudaStream_t stream);
+/* latency path: input pushed straight from the user tensor into every peer's slot buffer, no staging copy, no depart */
+B200DIST_API int b200_comm_allreduce_push(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, const void* in, void* out, long long n, float scale, int in_dtype,
+                                      int out_dtype, long long slot_elems, int parity, cudaStream_t stream);
+/* large-message broadcast: scatter from the root, then all-gather among the ranks */
+B200DIST_API int b200_comm_broadcast2(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes, int root,
+                                  void* local_gate, int max_ctas, cudaStream_t stream);
 B200DIST_API int b200_comm_broadcast(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes, int root,
                                  int max_ctas, cudaStream_t stream);
 B200DIST_API int b200_comm_alltoall(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes_per_peer,
                                 int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_slab_reduce(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, void* out, const void* residual, long long n, int max_ctas,
+                                   cudaStream_t stream);
 
 #endif  /* B200DIST_H_ */

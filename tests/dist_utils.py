@@ -19,7 +19,7 @@ def free_port() -> int:
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, backend, fn, args, errq):
+def _worker(rank, world, port, backend, fn, args, errq, init_pg=True):
     os.environ.update({"RANK": str(rank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(rank),
                        "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port), "B200DIST_DISABLE_MPI4PY": "1"})
     if str(ROOT) not in sys.path:
@@ -28,13 +28,16 @@ def _worker(rank, world, port, backend, fn, args, errq):
     import torch.distributed as dist
 
     try:
-        if backend == "nccl":
+        if not init_pg:
+            pass  # the test exercises its own process-group initialisation
+        elif backend == "nccl":
             torch.cuda.set_device(rank)
             dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
         else:
             dist.init_process_group("gloo", rank=rank, world_size=world)
         fn(rank, world, *args)
-        dist.barrier()
+        if dist.is_initialized():
+            dist.barrier()
     except Exception:  # noqa: BLE001
         errq.put((rank, traceback.format_exc()))
     finally:
@@ -42,12 +45,12 @@ def _worker(rank, world, port, backend, fn, args, errq):
             dist.destroy_process_group()
 
 
-def run_distributed(fn, world: int = 2, backend: str = "gloo", args=(), timeout: float = 180.0):
+def run_distributed(fn, world: int = 2, backend: str = "gloo", args=(), timeout: float = 180.0, init_pg: bool = True):
     """Run ``fn(rank, world, *args)`` in ``world`` processes; raise if any rank failed."""
     ctx = mp.get_context("spawn")
     errq = ctx.Queue()
     port = free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, fn, args, errq)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, backend, fn, args, errq, init_pg)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:

@@ -62,6 +62,29 @@ def main():
             y32 = torch.empty(n, device=dev, dtype=torch.float32)
             comm.all_reduce(x, scale=0.5, out=y32)
             check(f"all_reduce scale+cast {dt} n={n}", y32, ref.float() * 0.5)
+        # push (latency) path: default algo for small messages; back-to-back calls alternate the slot set
+        for it in range(5):
+            n = 8 * (it + 1) * 37
+            x = torch.randint(-8, 8, (n,), device=dev).to(dt)
+            ref = x.clone(); dist.all_reduce(ref)
+            y = x.clone(); comm.all_reduce(y)
+            check(f"all_reduce push {dt} n={n} call {it}", y, ref)
+            yo = torch.empty(n, device=dev, dtype=torch.float32 if dt == torch.bfloat16 else torch.bfloat16)
+            comm.all_reduce(x, scale=0.25, out=yo)
+            check(f"all_reduce push cast {dt} n={n}", yo, (ref.float() * 0.25).to(yo.dtype))
+        for n in (8 * 33, 8 * 32 * 5 + 8 * 7, 1 << 18):      # reduce-scatter tails around the 32-vector fp32 layout
+            xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+            o = torch.empty(n, device=dev, dtype=dt); r = torch.empty(n, device=dev, dtype=dt)
+            dist.reduce_scatter_tensor(r, xin)
+            comm.reduce_scatter(o, xin)
+            check(f"reduce_scatter {dt} n={n}", o, r)
+        bb = torch.randint(-8, 8, ((4 << 20) // (2 if dt == torch.bfloat16 else 4) * world // world,), device=dev).to(dt)
+        bb = bb[: bb.numel() // (8 * world) * (8 * world)].contiguous(); rbb = bb.clone()
+        dist.broadcast(rbb, src=0)
+        comm.broadcast2_min_world = 2
+        comm.broadcast(bb, src=0)
+        comm.broadcast2_min_world = 3
+        check(f"broadcast two-stage {dt} {bb.numel()} elems", bb, rbb)
         n = 1 << 18
         x = torch.randint(-8, 8, (n,), device=dev).to(dt)
         out = torch.empty(n * world, device=dev, dtype=dt); ref = torch.empty_like(out)
@@ -100,6 +123,20 @@ def main():
                        eps=1e-8, wd=0.1, step=1)
     check("rs_adamw master", master, pr.detach(), 2e-3)
     check("rs_adamw lowp", lowp, pr.detach(), 3e-2)
+    # copy-engine staged variant and fp32 gradients must give bit-identical results to the pull kernel
+    for in_dt, src_t in ((torch.bfloat16, g), (torch.float32, g.float())):
+        b2 = comm.symmetric_buffer(src_t.numel() * src_t.element_size())
+        b2.tensor(in_dt).copy_(src_t)
+        outs = []
+        for ce in (False, True):
+            ms, mm, vv = p0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+            lp = torch.empty(n, device=dev, dtype=torch.bfloat16)
+            comm.rs_adamw_from(b2, 0, in_dt, n, 1.0 / world, ms, lp, mm, vv, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8,
+                               wd=0.1, step=1, copy_engine=ce)
+            outs.append((ms, lp))
+        check(f"rs_adamw {in_dt} vs reference", outs[0][0], pr.detach(), 2e-3)
+        check(f"rs_adamw {in_dt} copy-engine == pull kernel", outs[1][0], outs[0][0])
+        check(f"rs_adamw {in_dt} copy-engine lowp", outs[1][1], outs[0][1])
     torch.cuda.synchronize()
     # bandwidth
     for mb in (1, 16, 256):
@@ -118,6 +155,11 @@ def main():
         if rank == 0:
             print(f"[TIME] all_gather {mb} MiB/rank: own {t_own*1e3:.1f} us busbw {busg(t_own):.0f} GB/s | NCCL {t_nccl*1e3:.1f} us "
                   f"busbw {busg(t_nccl):.0f} GB/s", flush=True)
+    x32 = torch.randn(64 << 20, device=dev)
+    t_own = ev_time(lambda: comm.all_reduce(x32, algo=2)); t_nccl = ev_time(lambda: dist.all_reduce(x32))
+    if rank == 0:
+        print(f"[TIME] all_reduce 256 MiB fp32 x{world}: own {t_own*1e3:.1f} us | NCCL {t_nccl*1e3:.1f} us", flush=True)
+    del x32
     x = torch.zeros(8, device=dev)
     t_own = ev_time(lambda: comm.barrier(), iters=50)
     t_small = ev_time(lambda: comm.all_reduce(x), iters=50)

