@@ -12,12 +12,14 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import sys
 from typing import Optional
 
 import torch
 import torch.distributed as dist
 
 from ..ops import _lib as L
+from ..utils import debug as _debug
 from .peer_mem import PeerBuffer
 
 I, LL, F, U = C.c_int, C.c_longlong, C.c_float, C.c_uint
@@ -39,6 +41,7 @@ class Communicator:
         self.max_ctas = 0
         self.oneshot_threshold = 256 << 10
         self._seq = [0] * N_CHANNELS
+        self._order = _debug.CollectiveOrderChecker() if _debug.collectives_debug_enabled() else None
         self.push_threshold = 256 << 10   # all-reduce messages up to this size take the push (latency) path
         self._push_slots = [None] * N_CHANNELS
         self.broadcast2_min_world = 3     # two-stage broadcast pays off once the root would serve >= 2 readers
@@ -65,6 +68,8 @@ class Communicator:
 
     def _ctx(self, data: PeerBuffer, channel: int):
         self._seq[channel] += 1
+        if self._order is not None:   # B200DIST_DEBUG_COLLECTIVES=1: fold (caller, bytes) into the channel's order digest
+            self._order.record(channel, sys._getframe(1).f_code.co_name, data.nbytes)
         return (data.ptr_array, self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
                 U(self._seq[channel] & 0xFFFFFFFF))
 
@@ -83,6 +88,8 @@ class Communicator:
         if not self.native:
             dist.barrier(group=self.group)
             return
+        if self._order is not None:
+            self._order.verify(self.group)   # host-side: raises CollectiveOrderError before the device barrier can hang
         L.call("comm_barrier", *self._ctx(self.flags, channel), self._s())
 
     # ------------------------------------------------------------------ all-reduce

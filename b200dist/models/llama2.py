@@ -231,6 +231,9 @@ class Transformer(nn.Module):
 
     def forward(self, tokens: torch.Tensor, pos_offset: int = 0):
         h = self.embed(tokens)
+        if tokens.shape[1] + pos_offset > self.freqs_cis.shape[0]:
+            raise ValueError(f"sequence of {tokens.shape[1]} tokens at offset {pos_offset} exceeds the RoPE table "
+                             f"({self.freqs_cis.shape[0]} positions = 2 x max_seq_len); build the model with a larger max_seq_len")
         if self.freqs_cis.device != h.device:
             self.freqs_cis = self.freqs_cis.to(h.device)
         for layer in self.layers:
@@ -311,6 +314,9 @@ class TransformerStage(nn.Module):
         if self._freqs is None or self._freqs.device != h.device:
             a = self.model_args
             self._freqs = ops.precompute_freqs_cis(a.dim // a.n_heads, a.max_seq_len * 2).to(h.device)
+        if h.shape[1] + pos_offset > self._freqs.shape[0]:
+            raise ValueError(f"sequence of {h.shape[1]} tokens at offset {pos_offset} exceeds the RoPE table "
+                             f"({self._freqs.shape[0]} positions = 2 x max_seq_len)")
         for layer in self.layers.values():
             h = layer(h, self._freqs, pos_offset)
         if self.is_last:

@@ -15,6 +15,8 @@ from pathlib import Path
 
 import torch
 
+from ..utils import debug as _debug
+
 _LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libb200dist.so"
 _lock = threading.Lock()
 _lib = None
@@ -94,3 +96,5 @@ def call(name: str, *args) -> None:
     fn = getattr(load(), "b200_" + name)
     launch_count += _KERNELS_PER_CALL.get(name, 1)
     check(fn(*args), name)
+    if _debug.sync_debug_enabled():
+        _debug.after_native_call(name)

@@ -10,9 +10,14 @@ ranks ``step()``.  Differences by design:
   Llama model by layer ranges (each rank only ever builds ITS stage, the reference builds the whole
   model on every rank, 03_pipeline_training.py:166-171);
 * the schedule object is built once and reused every step (the reference rebuilds it per step, :236-240);
-* activations/gradients travel as asynchronous NCCL p2p (``isend``/``irecv``) — by the north-star
-  this path stays on NCCL — with the next receive posted before the current microbatch computes,
-  so transfers overlap compute; gloo on CPU;
+* stage boundaries are PEER-MEMORY mailboxes on CUDA (``transport="peer"``, the default when the native library and
+  peer access are available): the sender's copy engines write the tensor into slot ``mb`` of the receiver's symmetric
+  buffer from a side stream and raise a flag, the receiver's compute stream waits on the flag and uses the slot in
+  place (zero-copy, nothing is ever posted, both directions of a middle stage are independent).  NCCL p2p
+  (``isend``/``irecv``, next receive posted one microbatch ahead) is the fallback, used for the first step (shape
+  discovery), forward-only steps and ``transport="nccl"``; gloo on CPU.  NCCL orders all unbatched p2p ops of a
+  communicator on one stream, which serialises the two directions of a middle stage: 4 stages x 8 microbatches of a
+  16-layer Llama-7B slice ran 371 ms/step over NCCL p2p vs 306 ms for torch.distributed.pipelining;
 * PP x DP: pass ``dp_group`` and the stage's gradients are bucket-all-reduced across replicas
   (``b200dist.parallel.DDP``), synchronised only on each step's last backward.
 
@@ -54,7 +59,7 @@ def bubble_fraction(n_stages: int, n_microbatches: int) -> float:
 
 class PipelineStage:
     def __init__(self, module: nn.Module, stage_index: int, num_stages: int, device=None, group=None,
-                 dp_group=None):
+                 dp_group=None, transport: str = "auto"):
         self.stage_index, self.num_stages = stage_index, num_stages
         self.group = group
         self.device = device if device is not None else next(module.parameters()).device
@@ -71,7 +76,15 @@ class PipelineStage:
             module = DDP(module, process_group=dp_group)
         self.submod = module
         self._recv_meta = None   # (shape, dtype) of incoming activations
-        self._out_meta = None
+        self._out_meta = None    # (shape, dtype) of outgoing activations
+        if transport == "auto":
+            from ..ops import _lib as L
+
+            transport = "peer" if (torch.device(self.device).type == "cuda" and L.available() and num_stages > 1) else "nccl"
+        assert transport in ("peer", "nccl")
+        self.transport = transport
+        self._peer: Optional[_PeerTransport] = None
+        self._train_steps = 0
 
     def parameters(self):
         return self.submod.parameters()
@@ -94,6 +107,150 @@ class PipelineStage:
         return self._recv_meta
 
 
+class _NcclTransport:
+    """isend / irecv on the pp group (gloo on CPU).  Receives are posted explicitly, one microbatch ahead."""
+
+    def __init__(self, stage: "PipelineStage", M: int):
+        self.st, self.M = stage, M
+        self.recv_act: dict = {}
+        self.recv_grad: dict = {}
+        self.pending: list = []
+
+    def post_recv_act(self, i: int) -> None:
+        st = self.st
+        if st.is_first or i >= self.M or i in self.recv_act:
+            return
+        shape, dt = st._recv_meta_once()
+        buf = torch.empty(shape, dtype=dt, device=st.device)
+        self.recv_act[i] = (buf, dist.irecv(buf, st.prev_rank, group=st.group))
+
+    def wait_act(self, i: int) -> torch.Tensor:
+        self.post_recv_act(i)
+        buf, work = self.recv_act.pop(i)
+        work.wait()
+        return buf
+
+    def send_act(self, i: int, out: torch.Tensor) -> None:
+        st = self.st
+        if st._out_meta is None:
+            st._send_meta(out)
+            st._out_meta = (tuple(out.shape), out.dtype)
+        self.pending.append(dist.isend(out.detach(), st.next_rank, group=st.group))
+
+    def post_recv_grad(self, i: int, like: Optional[torch.Tensor]) -> None:
+        st = self.st
+        if st.is_last or i >= self.M or i in self.recv_grad or like is None:
+            return
+        buf = torch.empty_like(like)
+        self.recv_grad[i] = (buf, dist.irecv(buf, st.next_rank, group=st.group))
+
+    def wait_grad(self, i: int, like: torch.Tensor) -> torch.Tensor:
+        self.post_recv_grad(i, like)
+        g, work = self.recv_grad.pop(i)
+        work.wait()
+        return g
+
+    def send_grad(self, i: int, g: torch.Tensor) -> None:
+        self.pending.append(dist.isend(g, self.st.prev_rank, group=self.st.group))
+
+    def flush(self) -> None:
+        for w in self.pending:
+            w.wait()
+        self.pending = []
+
+
+class _PeerTransport:
+    """Mailboxes in the receiver's symmetric memory + flag words (see the module docstring).
+
+    Slot ``i`` of a mailbox is rewritten once per step.  Reuse is safe in TRAINING steps without acknowledgements: a
+    sender reaches microbatch i of step t+1 only after its own backward of step t, which depends (through the gradient
+    it received) on the receiver having finished both its forward and backward of microbatch i of step t.
+    """
+
+    ACT, GRAD, MAX_MB = 0, 1, 1024
+
+    def __init__(self, stage: "PipelineStage", M: int):
+        from ..comm.peer_mem import PeerBuffer
+        from ..ops import _lib as L
+
+        self.st, self.M, self.L = stage, M, L
+        st = stage
+        in_shape, in_dt = st._recv_meta if st._recv_meta is not None else ((0,), torch.bfloat16)
+        out_shape, out_dt = st._out_meta if st._out_meta is not None else ((0,), torch.bfloat16)
+        nbytes = lambda sh, dt: int(torch.Size(sh).numel()) * torch.empty((), dtype=dt).element_size()  # noqa: E731
+        need = torch.tensor([max(nbytes(in_shape, in_dt), nbytes(out_shape, out_dt))], device=st.device, dtype=torch.int64)
+        dist.all_reduce(need, op=dist.ReduceOp.MAX, group=st.group)
+        self.slot = (int(need.item()) + 255) // 256 * 256
+        assert M <= self.MAX_MB
+        self.act_box = PeerBuffer(M * self.slot, st.group, st.device)    # written by the previous stage
+        self.grad_box = PeerBuffer(M * self.slot, st.group, st.device)   # written by the next stage
+        self.flags = PeerBuffer(2 * self.MAX_MB * 4, st.group, st.device)
+        self.me = st.stage_index
+        self.in_meta, self.out_meta = (in_shape, in_dt), (out_shape, out_dt)
+        self.tx_act, self.tx_grad = torch.cuda.Stream(st.device), torch.cuda.Stream(st.device)
+        self.seq = 0
+        torch.cuda.synchronize(st.device)
+        dist.barrier(group=st.group, device_ids=[st.device.index]) if dist.get_backend(st.group) == "nccl" \
+            else dist.barrier(group=st.group)
+
+    def begin_step(self) -> None:
+        self.seq += 1
+
+    def _flag(self, owner: int, kind: int, i: int) -> int:
+        return self.flags.ptrs[owner] + (kind * self.MAX_MB + i) * 4
+
+    def _view(self, box, i: int, meta) -> torch.Tensor:
+        shape, dt = meta
+        n = int(torch.Size(shape).numel())
+        return box.tensor(dt, i * self.slot, n).view(shape)
+
+    def _send(self, box, owner: int, kind: int, i: int, t: torch.Tensor, tx) -> None:
+        import ctypes as C
+
+        L = self.L
+        t = t.contiguous()
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.st.device))
+        t.record_stream(tx)
+        with torch.cuda.stream(tx):
+            tx.wait_event(ev)
+            L.check(L.load().b200_peer_memcpy(C.c_void_p(box.ptrs[owner] + i * self.slot), C.c_void_p(t.data_ptr()),
+                                              C.c_size_t(t.numel() * t.element_size()), L.stream_ptr(self.st.device)),
+                    "peer_memcpy")
+            L.call("p2p_signal", C.c_void_p(self._flag(owner, kind, i)), C.c_uint(self.seq), L.stream_ptr(self.st.device))
+
+    def _wait(self, kind: int, i: int) -> None:
+        import ctypes as C
+
+        self.L.call("p2p_wait", C.c_void_p(self._flag(self.me, kind, i)), C.c_uint(self.seq),
+                    self.L.stream_ptr(self.st.device))
+
+    def post_recv_act(self, i: int) -> None:      # nothing to post: the sender writes into our mailbox unasked
+        pass
+
+    def post_recv_grad(self, i: int, like) -> None:
+        pass
+
+    def wait_act(self, i: int) -> torch.Tensor:
+        self._wait(self.ACT, i)
+        return self._view(self.act_box, i, self.in_meta)
+
+    def send_act(self, i: int, out: torch.Tensor) -> None:
+        self._send(self.act_box, self.me + 1, self.ACT, i, out.detach(), self.tx_act)
+
+    def wait_grad(self, i: int, like: torch.Tensor) -> torch.Tensor:
+        self._wait(self.GRAD, i)
+        return self._view(self.grad_box, i, (tuple(like.shape), like.dtype))
+
+    def send_grad(self, i: int, g: torch.Tensor) -> None:
+        self._send(self.grad_box, self.me - 1, self.GRAD, i, g, self.tx_grad)
+
+    def flush(self) -> None:
+        cur = torch.cuda.current_stream(self.st.device)
+        cur.wait_stream(self.tx_act)
+        cur.wait_stream(self.tx_grad)
+
+
 class _Schedule:
     kind = "gpipe"
 
@@ -113,23 +270,14 @@ class _Schedule:
         saved_in: List[Optional[torch.Tensor]] = [None] * M
         saved_out: List[Optional[torch.Tensor]] = [None] * M
         outputs: List[Optional[torch.Tensor]] = [None] * M
-        recv_act: dict = {}
-        recv_grad: dict = {}
-        pending_sends: list = []
-
-        def post_recv_act(i):
-            if st.is_first or i >= M or i in recv_act:
-                return
-            shape, dt = st._recv_meta_once()
-            buf = torch.empty(shape, dtype=dt, device=st.device)
-            recv_act[i] = (buf, dist.irecv(buf, st.prev_rank, group=st.group))
-
-        def post_recv_grad(i):
-            if st.is_last or i >= M or i in recv_grad or not training:
-                return
-            o = saved_out[i]
-            buf = torch.empty_like(o)
-            recv_grad[i] = (buf, dist.irecv(buf, st.next_rank, group=st.group))
+        # shapes are discovered over NCCL during the first training step; every stage switches to mailboxes together
+        if st.transport == "peer" and training and st._train_steps >= 1:
+            if st._peer is None or st._peer.M < M:
+                st._peer = _PeerTransport(st, M)
+            tr = st._peer
+            tr.begin_step()
+        else:
+            tr = _NcclTransport(st, M)
 
         ddp = st.submod if hasattr(st.submod, "no_sync") else None
         n_back = sum(1 for a in self.actions if a[0] == "B")
@@ -140,12 +288,10 @@ class _Schedule:
                 if st.is_first:
                     x = mb_in[i]
                 else:
-                    post_recv_act(i)
-                    buf, work = recv_act.pop(i)
-                    work.wait()
-                    post_recv_act(i + 1)  # prefetch the next activation while this microbatch computes
+                    buf = tr.wait_act(i)
+                    tr.post_recv_act(i + 1)  # NCCL: prefetch the next activation while this microbatch computes
                     if training and buf.is_floating_point():
-                        buf.requires_grad_(True)
+                        buf = buf.detach().requires_grad_(True)
                     saved_in[i] = buf
                     x = (buf,)
                 if ddp is not None and training:
@@ -154,18 +300,15 @@ class _Schedule:
                 else:
                     out = st.submod(*x)
                 if st.is_last:
-                    outputs[i] = out
+                    outputs[i] = out.detach()
                     if training:
                         loss = self.loss_fn(out, tgt[i])
                         saved_out[i] = loss
                         if losses is not None:
                             losses.append(loss.detach())
                 else:
-                    if st._out_meta is None:
-                        st._send_meta(out)
-                        st._out_meta = True
                     saved_out[i] = out
-                    pending_sends.append(dist.isend(out.detach(), st.next_rank, group=st.group))
+                    tr.send_act(i, out)
             else:  # backward
                 last_b = b_done == n_back - 1
                 ctx = ddp.no_sync() if (ddp is not None and not last_b) else _null()
@@ -173,22 +316,20 @@ class _Schedule:
                     if st.is_last:
                         (saved_out[i] / M).backward()
                     else:
-                        post_recv_grad(i)
-                        g, work = recv_grad.pop(i)
-                        work.wait()
+                        g = tr.wait_grad(i, saved_out[i])
                         torch.autograd.backward(saved_out[i], g)
                 b_done += 1
                 saved_out[i] = None
                 if not st.is_first:
-                    gin = saved_in[i].grad
-                    pending_sends.append(dist.isend(gin, st.prev_rank, group=st.group))
+                    tr.send_grad(i, saved_in[i].grad)
                     saved_in[i] = None
-        for w in pending_sends:
-            w.wait()
+        tr.flush()
+        if training:
+            st._train_steps += 1
         if ddp is not None and training:
             ddp.finish_backward()
         if st.is_last:
-            return torch.cat([o.detach() for o in outputs]) if all(o is not None for o in outputs) else None
+            return torch.cat(outputs) if all(o is not None for o in outputs) else None
         return None
 
 

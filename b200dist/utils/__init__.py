@@ -1,5 +1,6 @@
 """Shared runtime utilities (same public names as the reference ``utils`` package,
 /root/reference/utils/__init__.py:9-16)."""
+from . import debug
 from .checkpointing import (consolidate_sharded_checkpoint, load_checkpoint, load_sharded_checkpoint, load_snapshot,
                             save_checkpoint, save_sharded_checkpoint, save_snapshot)
 from .config import TrainingConfig
@@ -12,4 +13,4 @@ from .sampler import DistributedSampler
 __all__ = ["get_rank_info", "init_distributed", "cleanup_distributed", "is_main_rank", "print_rank0", "get_logger",
            "rank_log", "verify_min_gpu_count", "save_checkpoint", "load_checkpoint", "save_sharded_checkpoint",
            "load_sharded_checkpoint", "consolidate_sharded_checkpoint", "save_snapshot", "load_snapshot",
-           "TrainingConfig", "training_profiler", "print_profiler_summary", "redirect", "DistributedSampler"]
+           "debug", "TrainingConfig", "training_profiler", "print_profiler_summary", "redirect", "DistributedSampler"]

@@ -803,6 +803,30 @@ B200_API int b200_comm_slab_reduce(COMM_ARGS, void* out, const void* residual, l
   return B200_OK;
 }
 
+// ------------------------------ point-to-point signalling (pipeline stage boundaries) ------------------------------
+// A stage boundary is a producer/consumer copy: the sender moves the tensor into a mailbox slot in the RECEIVER's
+// symmetric memory (b200_peer_memcpy on a side stream, copy engines) and then raises the slot's flag; the receiver's
+// compute stream waits on the flag and uses the slot in place.  Replaces dist.isend/irecv of
+// scripts/04_pipeline_parallel_pp/*.py (torch.distributed.pipelining's batch_isend_irecv) without NCCL's per-communicator
+// stream ordering, which serialises the two directions of a middle stage.
+__global__ void p2p_signal_kernel(uint32_t* remote_flag, uint32_t value) {
+  __threadfence_system();
+  b200::st_release_sys(remote_flag, value);
+}
+__global__ void p2p_wait_kernel(const uint32_t* local_flag, uint32_t value) {
+  b200::spin_until(local_flag, value, "p2p");
+}
+B200_API int b200_p2p_signal(void* remote_flag, unsigned value, cudaStream_t stream) {
+  p2p_signal_kernel<<<1, 1, 0, stream>>>(reinterpret_cast<uint32_t*>(remote_flag), value);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+B200_API int b200_p2p_wait(const void* local_flag, unsigned value, cudaStream_t stream) {
+  p2p_wait_kernel<<<1, 1, 0, stream>>>(reinterpret_cast<const uint32_t*>(local_flag), value);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 // Small-message all-reduce without staging copies (see comm_allreduce_push_kernel).  data_ptrs = the symmetric SLOT
 // buffer [2][world][slot_elems] of in_dtype; `in` / `out` are ordinary device tensors (may alias); n % 8 == 0,
 // n <= slot_elems, `in` and `out` 16-byte aligned.  parity must alternate between consecutive calls on a channel.

@@ -167,6 +167,12 @@ B200DIST_API int b200_peer_close(void* p);
 /* copy-engine (DMA) transfer between local and imported peer memory: the FSDP parameter all-gather path, no SMs used */
 B200DIST_API int b200_peer_memcpy(void* dst, const void* src, size_t bytes, cudaStream_t stream);
 
+/* ---- Point-to-point signalling for pipeline stage boundaries (replaces dist.isend/irecv,
+ * scripts/04_pipeline_parallel_pp/01_manual_model_split.py:108-125): copy with b200_peer_memcpy, then signal; the
+ * receiver's stream waits on its own flag word.  Flags are 32-bit sequence numbers that only grow. */
+B200DIST_API int b200_p2p_signal(void* remote_flag, unsigned value, cudaStream_t stream);
+B200DIST_API int b200_p2p_wait(const void* local_flag, unsigned value, cudaStream_t stream);
+
 /* ---- Collectives over NVLink peer memory ----
  * replace c10d/NCCL: tests/torch_comm_bench.py:49,79; DDP / FSDP / DTensor implicit collectives */
 B200DIST_API int b200_comm_barrier(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,

@@ -194,3 +194,66 @@ def test_llama_state_dict_compat_with_reference():
         assert torch.allclose(p.grad, q.grad, atol=1e-4, rtol=1e-3), n
     assert ffn_hidden_dim(4096, 256, None) == 11008 and ffn_hidden_dim(5120, 256, None) == 13824
     assert m.to(torch.bfloat16).freqs_cis.dtype == torch.complex64
+
+
+def _order_worker(rank, world):
+    from b200dist.utils.debug import CollectiveOrderChecker, CollectiveOrderError, assert_replicas_equal
+
+    c = CollectiveOrderChecker()
+    for i in range(5):
+        c.record(0, "all_reduce", 1024)
+        c.record(2, "rs_adamw_from", 4096 + i)
+    c.verify()                                   # identical sequences on both ranks: passes
+    if rank == 1:
+        c.record(2, "all_gather_from", 64)       # rank 1 issues one extra collective on channel 2
+    try:
+        c.verify()
+    except CollectiveOrderError as e:
+        assert "channel 2" in str(e) and "rank 1" in str(e)
+    else:
+        raise AssertionError("diverging collective order was not detected")
+    t = torch.arange(16, dtype=torch.float32)
+    assert_replicas_equal(t, name="same")
+    try:
+        assert_replicas_equal(t + (rank == 1) * 1e-3, name="diverged")
+    except AssertionError as e:
+        assert "diverged" in str(e)
+    else:
+        raise AssertionError("replica divergence was not detected")
+
+
+def test_collective_order_hash_and_replica_check_gloo_world2():
+    run_distributed(_order_worker, 2)
+
+
+def test_stream_hazard_tracker():
+    import pytest
+
+    from b200dist.utils.debug import StreamHazardError, StreamHazardTracker
+
+    t = StreamHazardTracker()
+    t.write("stage0", "main")                    # backward writes gradients into the staging buffer
+    t.record("grads_ready", "main")
+    t.wait("grads_ready", "comm")
+    t.read("stage0", "comm")                     # reduce-scatter reads it after the event: fine
+    with pytest.raises(StreamHazardError, match="write-after-read"):
+        t.write("stage0", "main")                # next backward overwrites while comm may still be reading
+    t2 = StreamHazardTracker()
+    t2.write("flat", "prefetch")
+    with pytest.raises(StreamHazardError, match="read-after-write"):
+        t2.read("flat", "main")                  # compute consumes the gathered weights without waiting for the gather
+    t2.record("gathered", "prefetch"); t2.wait("gathered", "main")
+    t2.read("flat", "main")
+    t2.record("consumed", "main"); t2.wait("consumed", "prefetch")
+    t2.write("flat", "prefetch")                 # properly ordered reuse
+    with pytest.raises(StreamHazardError, match="never recorded"):
+        t2.wait("missing", "main")
+
+
+def test_sync_debug_toggle():
+    from b200dist.utils import debug
+
+    assert not debug.sync_debug_enabled()
+    with debug.sync_debug():
+        assert debug.sync_debug_enabled()
+    assert not debug.sync_debug_enabled()

@@ -114,12 +114,12 @@ def main():
 
     big2 = batches(2, B=1, S=256 * world * 2)
     big = [big2[i % 2] for i in range(steps)]
-    mref = toy().to(dev).to(torch.bfloat16)
+    mref = toy(max_seq_len=256 * world * 2).to(dev).to(torch.bfloat16)   # RoPE table must cover the long sequence
     oref = FusedAdamW(mref.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
     ref_l = []
     for t in big:
         t = t.to(dev); oref.zero_grad(); l = ops.cross_entropy(mref(t[:, :-1]), t[:, 1:]); l.backward(); oref.step(); ref_l.append(float(l))
-    m = toy().to(dev).to(torch.bfloat16)
+    m = toy(max_seq_len=256 * world * 2).to(dev).to(torch.bfloat16)
     llama_tp_plan(m, mesh["tp"], sequence_parallel=True)
     enable_fused_tp(m, mesh["tp"])
     opt = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
@@ -200,6 +200,49 @@ def main():
     ok &= good
     if rank == 0:
         print(f"[{'PASS' if good else 'FAIL'}] halo conv vs full conv: max err {err:.3g}", flush=True)
+    # ---------------- pipeline parallel: 1F1B over peer-memory mailboxes vs one GPU ----------------
+    from b200dist.models.llama2 import ModelArgs, TransformerStage
+    from b200dist.parallel.pp import PipelineStage, Schedule1F1B, ScheduleGPipe
+
+    pcfg = dict(dim=256, n_layers=2 * world, n_heads=4, vocab_size=512, max_seq_len=256)
+    torch.manual_seed(3)
+    full = toy(n_layers=2 * world).to(dev).to(torch.bfloat16)
+    sd = {k: v.clone() for k, v in full.state_dict().items()}   # snapshot before the reference run trains `full`
+    ofull = FusedAdamW(full.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    Mb = 2 * world
+    pdata = [two[i % 2][: Mb] if two[0].shape[0] >= Mb else two[i % 2].repeat(Mb, 1)[:Mb] for i in range(steps)]
+    ref_pp = []
+    for t_ in pdata:
+        t_ = t_.to(dev); ofull.zero_grad()
+        tot = 0.0
+        for mb in t_.chunk(Mb):     # same microbatch split as the schedule: mean of per-microbatch losses
+            l = ops.cross_entropy(full(mb[:, :-1]), mb[:, 1:]) / Mb; l.backward(); tot += float(l)
+        ofull.step(); ref_pp.append(tot)
+    for kind in ("1f1b", "gpipe"):
+        stage_mod = TransformerStage(ModelArgs(**pcfg), rank, world, init=False).to(dev).to(torch.bfloat16)
+        stage_mod.load_state_dict({k: sd[k] for k in stage_mod.state_dict()})
+        stage = PipelineStage(stage_mod, rank, world, device=dev)
+        sched = (Schedule1F1B if kind == "1f1b" else ScheduleGPipe)(
+            stage, Mb, loss_fn=lambda o, y: ops.cross_entropy(o, y))
+        opt = FusedAdamW(stage.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+        got = []
+        for t_ in pdata:
+            t_ = t_.to(dev); opt.zero_grad(); ls = []
+            if stage.is_first and stage.is_last:
+                sched.step(t_[:, :-1], target=t_[:, 1:], losses=ls)
+            elif stage.is_first:
+                sched.step(t_[:, :-1])
+            elif stage.is_last:
+                sched.step(target=t_[:, 1:], losses=ls)
+            else:
+                sched.step()
+            opt.step()
+            lt = torch.zeros(1, device=dev)
+            if stage.is_last:
+                lt += torch.stack([x.float() for x in ls]).mean()
+            dist.all_reduce(lt); got.append(float(lt))
+        used = "peer mailboxes" if stage._peer is not None else "nccl p2p"
+        report(f"PP{world} {kind} ({used} after step 1) loss curve", got, ref_pp, 0.02)
     t = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(t)
     if rank == 0:
