@@ -16,31 +16,40 @@ namespace b200 {
 
 // ------------------------------------------------------------------ im2col / col2im
 // col[(n, ho, wo), (kh, kw, c)] = x[n, ho*s - p + kh, wo*s - p + kw, c]  (zero outside); c padded to Cp
+// A warp owns one output pixel at a time and sweeps that pixel's row of the patch matrix 32 vectors (512 bytes) per
+// step, so the (n, ho, wo) decode is done once per row and the per-vector work is two 32-bit divisions, one 128-bit
+// load and one fully coalesced 128-bit store (the first version decoded every vector with six 64-bit div/mods and was
+// instruction-bound at ~1.4 TB/s).
 template <typename T>
-__global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int N, int H, int W, int C, int Cp,
-                              int KH, int KW, int stride, int pad, int Ho, int Wo) {
-  const int c8n = Cp >> 3;
-  const long long total = (long long)N * Ho * Wo * KH * KW * c8n;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long r = i;
-    const int c8 = (int)(r % c8n); r /= c8n;
-    const int kw = (int)(r % KW); r /= KW;
-    const int kh = (int)(r % KH); r /= KH;
-    const int wo = (int)(r % Wo); r /= Wo;
-    const int ho = (int)(r % Ho);
-    const int n = (int)(r / Ho);
-    const int h = ho * stride - pad + kh, w = wo * stride - pad + kw;
-    float v[8];
+__global__ void __launch_bounds__(256) im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int N, int H, int W,
+                                                     int C, int Cp, int KH, int KW, int stride, int pad, int Ho, int Wo) {
+  const unsigned c8n = Cp >> 3;
+  const unsigned L = (unsigned)(KH * KW) * c8n;           // vectors per patch-matrix row
+  const long long pixels = (long long)N * Ho * Wo;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool vec_ok = (C & 7) == 0;
+  for (long long p = (long long)blockIdx.x * 8 + warp; p < pixels; p += (long long)gridDim.x * 8) {
+    const unsigned pw = (unsigned)(p % ((long long)Ho * Wo));
+    const int n = (int)(p / ((long long)Ho * Wo));
+    const int ho = pw / Wo, wo = pw % Wo;
+    const int h0 = ho * stride - pad, w0 = wo * stride - pad;
+    const T* img = x + (long long)n * H * W * C;
+    T* dst = col + p * (long long)L * 8;
+    for (unsigned q = lane; q < L; q += 32) {
+      const unsigned tap = q / c8n, c8 = q - tap * c8n;
+      const int kh = tap / KW, kw = tap - kh * KW;
+      const int h = h0 + kh, w = w0 + kw;
+      float v[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = 0.f;
-    if (h >= 0 && h < H && w >= 0 && w < W) {
-      const T* src = x + (((long long)n * H + h) * W + w) * C + c8 * 8;
-      if ((C & 7) == 0) Vec8<T>::load(src, v);
-      else
-        for (int j = 0; j < 8; ++j) if (c8 * 8 + j < C) v[j] = to_f<T>(src[j]);
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+      if (h >= 0 && h < H && w >= 0 && w < W) {
+        const T* src = img + ((long long)h * W + w) * C + c8 * 8;
+        if (vec_ok) Vec8<T>::load(src, v);
+        else
+          for (int j = 0; j < 8; ++j) if ((int)(c8 * 8 + j) < C) v[j] = to_f<T>(src[j]);
+      }
+      Vec8<T>::store(dst + (long long)q * 8, v);
     }
-    Vec8<T>::store(col + i * 8, v);
   }
 }
 
@@ -61,6 +70,29 @@ __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, in
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (KH == 3 && KW == 3 && stride == 1) {
+      // the common case (no divisions): one filter row = three independent 128-bit loads in flight at a time
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh) {
+        const int ho = h + pad - kh;
+        if (ho < 0 || ho >= Ho) continue;
+        float v[3][8];
+        bool ok[3];
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+          const int wo = w + pad - kw;
+          ok[kw] = wo >= 0 && wo < Wo;
+          if (ok[kw])
+            Vec8<T>::load(dcol + (((long long)n * Ho + ho) * Wo + wo) * row_len + (long long)(kh * 3 + kw) * Cp + c8 * 8, v[kw]);
+        }
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw)
+          if (ok[kw]) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += v[kw][j];
+          }
+      }
+    } else
     for (int kh = 0; kh < KH; ++kh) {
       const int hs = h + pad - kh;
       if (hs < 0 || hs % stride) continue;
@@ -89,11 +121,11 @@ __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, in
 //   mode 0: stats       -> sum x, sum x^2
 //   mode 1: bn backward -> sum dy_m, sum dy_m * (x - mean[c]) * rstd[c]   (dy_m = dy masked by relu(y))
 // Each thread owns 8 consecutive channels (one 128-bit load per row); a block covers `nvx` channel vectors x 256/nvx rows.
-template <typename T>
+template <typename T, int mode>
 __global__ void __launch_bounds__(256) col_reduce_kernel(const T* __restrict__ a, const T* __restrict__ xin,
                                                          const T* __restrict__ y, const float* __restrict__ mean,
                                                          const float* __restrict__ rstd, float* __restrict__ sums,
-                                                         long long rows, int C, int mode, int relu_mask, int nvx) {
+                                                         long long rows, int C, int relu_mask, int nvx) {
   const int tx = threadIdx.x % nvx, ty = threadIdx.x / nvx, nty = 256 / nvx;
   const int c = (blockIdx.x * nvx + tx) * 8;
   const bool active = c < C;
@@ -108,8 +140,37 @@ __global__ void __launch_bounds__(256) col_reduce_kernel(const T* __restrict__ a
     for (int j = 0; j < 8; ++j) { mu[j] = mean[c + j]; rs[j] = rstd[c + j]; }
   }
   if (active) {
-#pragma unroll 2
-    for (long long r = r0 + ty; r < r1; r += nty) {
+    // kB independent rows per iteration: all their 128-bit loads are issued before the first add, so a thread keeps
+    // kB (stats) or 2-3 x kB (backward) requests in flight - the kernel is a pure HBM stream and needs ~6 MB in flight.
+    constexpr int kB = mode == 0 ? 8 : 4;
+    long long r = r0 + ty;
+    for (; r + (long long)(kB - 1) * nty < r1; r += (long long)kB * nty) {
+      float v[kB][8], xv[mode == 1 ? kB : 1][8], yv[mode == 1 ? kB : 1][8];
+#pragma unroll
+      for (int b = 0; b < kB; ++b) {
+        const long long off = (r + (long long)b * nty) * C + c;
+        Vec8<T>::load(a + off, v[b]);
+        if constexpr (mode == 1) {
+          Vec8<T>::load(xin + off, xv[b]);
+          if (relu_mask) Vec8<T>::load(y + off, yv[b]);
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kB; ++b) {
+        if constexpr (mode == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { s0[j] += v[b][j]; s1[j] += v[b][j] * v[b][j]; }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float g = (relu_mask && !(yv[b][j] > 0.f)) ? 0.f : v[b][j];
+            s0[j] += g;
+            s1[j] += g * (xv[b][j] - mu[j]) * rs[j];
+          }
+        }
+      }
+    }
+    for (; r < r1; r += nty) {
       float v[8];
       Vec8<T>::load(a + r * C + c, v);
       if (mode == 0) {
@@ -429,7 +490,8 @@ using namespace b200;
 B200_API int b200_im2col(const void* x, void* col, CONV_ARGS, int dtype, cudaStream_t stream) {
   const long long total = (long long)N * Ho * Wo * KH * KW * (Cp >> 3);
   if (total <= 0) return B200_OK;
-  B200_DISPATCH_DTYPE(dtype, T, (im2col_kernel<T><<<ew_grid(total, 256), 256, 0, stream>>>(
+  const long long pixels = (long long)N * Ho * Wo;
+  B200_DISPATCH_DTYPE(dtype, T, (im2col_kernel<T><<<ew_grid(pixels * 32, 256, 16), 256, 0, stream>>>(
       (const T*)x, (T*)col, N, H, W, C, Cp, KH, KW, stride, pad, Ho, Wo)));
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -456,12 +518,17 @@ B200_API int b200_col_reduce(const void* a, const void* xin, const void* y, cons
   const int gx = (nvc + nvx - 1) / nvx;
   const int rows_per_iter = 256 / nvx;
   long long gy = (rows + (long long)rows_per_iter * 8 - 1) / ((long long)rows_per_iter * 8);
-  const long long cap = (long long)b200_sm_count() * 2 / gx + 1;   // few blocks: the final atomics serialise per address
+  const long long cap = (long long)b200_sm_count() * 4 / gx + 1;   // few blocks: the final atomics serialise per address
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
   dim3 grd(gx, (unsigned)gy);
-  B200_DISPATCH_DTYPE(dtype, T, (col_reduce_kernel<T><<<grd, 256, 0, stream>>>(
-      (const T*)a, (const T*)xin, (const T*)y, mean, rstd, sums, rows, C, mode, relu_mask, nvx)));
+  if (mode == 0) {
+    B200_DISPATCH_DTYPE(dtype, T, (col_reduce_kernel<T, 0><<<grd, 256, 0, stream>>>(
+        (const T*)a, (const T*)xin, (const T*)y, mean, rstd, sums, rows, C, relu_mask, nvx)));
+  } else {
+    B200_DISPATCH_DTYPE(dtype, T, (col_reduce_kernel<T, 1><<<grd, 256, 0, stream>>>(
+        (const T*)a, (const T*)xin, (const T*)y, mean, rstd, sums, rows, C, relu_mask, nvx)));
+  }
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
