@@ -200,6 +200,30 @@ def xent_fwd(logits, target, ignore_index=-100):
     return loss, lse
 
 
+def xent_fwd_vp(logits, target, ignore_index, vocab_start):
+    """Local-shard forward: (lse_local - logit[target] where the target column is local else 0, lse_local)."""
+    V = logits.shape[-1]
+    l2 = logits.reshape(-1, V)
+    assert l2.stride(1) == 1
+    t = target.reshape(-1).contiguous().to(torch.int64)
+    loss = torch.empty(l2.shape[0], device=logits.device, dtype=torch.float32)
+    lse = torch.empty_like(loss)
+    L.call("xent_fwd_vp", L.ptr(l2), L.ptr(t), L.ptr(loss), L.ptr(lse), I(l2.shape[0]), I(V), LL(l2.stride(0)),
+           LL(ignore_index), LL(vocab_start), I(L.dtype_code(logits.dtype)), _s())
+    return loss, lse
+
+
+def xent_bwd_vp(logits, target, lse_global, gscale, ignore_index, vocab_start, v_total):
+    V = logits.shape[-1]
+    l2 = logits.reshape(-1, V)
+    t = target.reshape(-1).contiguous().to(torch.int64)
+    out = torch.empty_like(l2)
+    L.call("xent_bwd_vp", L.ptr(l2), L.ptr(t), L.ptr(lse_global), L.ptr(gscale), L.ptr(out), I(l2.shape[0]), I(V),
+           LL(l2.stride(0)), LL(out.stride(0)), LL(ignore_index), LL(vocab_start), LL(v_total),
+           I(L.dtype_code(logits.dtype)), _s())
+    return out.view(logits.shape)
+
+
 def xent_bwd(logits, target, lse, gscale, ignore_index=-100, out=None):
     V = logits.shape[-1]
     l2 = logits.reshape(-1, V)

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--fused", action="store_true")
     ap.add_argument("--no-sp", action="store_true")
+    ap.add_argument("--vocab-parallel-loss", action="store_true", help="keep the logits vocabulary-sharded (no [M, V] all-gather)")
     ap.add_argument("--impl", default="b200dist", choices=["b200dist", "reference"])
     ap.add_argument("--verbose", action="store_true", help="print the loss of every step (adds a sync per step)")
     a = ap.parse_args()
@@ -54,7 +55,7 @@ def main():
         from b200dist import ops
         from b200dist.models import ModelArgs, Transformer
         from b200dist.parallel import FSDP, init_device_mesh
-        from b200dist.parallel.tp import enable_fused_tp, llama_tp_plan
+        from b200dist.parallel.tp import enable_fused_tp, llama_tp_plan, vocab_parallel_cross_entropy
 
         mesh = init_device_mesh("cuda", (dp, tp), ("dp", "tp"))
         dp_rank = mesh.get_local_rank("dp")
@@ -62,7 +63,8 @@ def main():
         with torch.device(dev):
             model = Transformer(ModelArgs(**cfg))
         torch.set_default_dtype(prev)
-        llama_tp_plan(model, mesh["tp"], sequence_parallel=not a.no_sp)
+        llama_tp_plan(model, mesh["tp"], sequence_parallel=not a.no_sp, gather_logits=not a.vocab_parallel_loss)
+        tp_comm = mesh["tp"].communicator()
         if a.fused:
             enable_fused_tp(model, mesh["tp"])
         torch.cuda.empty_cache()
@@ -71,7 +73,10 @@ def main():
 
         def step(x, y):
             opt.zero_grad()
-            loss = ops.cross_entropy(model(x).view(-1, vocab), y.reshape(-1))
+            if a.vocab_parallel_loss:
+                loss = vocab_parallel_cross_entropy(model(x), y, tp_comm)
+            else:
+                loss = ops.cross_entropy(model(x).view(-1, vocab), y.reshape(-1))
             loss.backward()
             opt.step()
             return loss
@@ -156,7 +161,7 @@ def main():
                           "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
                           "dtype": "bf16", "data": "synthetic tokens, random-init weights", "impl": a.impl,
                           "config": {"model": a.model, "n_layers": cfg["n_layers"], "seq_len": S, "global_batch": dp * B,
-                                     "parallelism": f"tp{tp}{'' if a.no_sp else '+sp'} x fsdp{dp}", "fused_tp": bool(a.fused)},
+                                     "parallelism": f"tp{tp}{'' if a.no_sp else '+sp'} x fsdp{dp}", "fused_tp": bool(a.fused), "vocab_parallel_loss": bool(a.vocab_parallel_loss)},
                           "peak_mem_gib": round(peak, 1), "loss_last": round(float(loss.detach()), 4)}), flush=True)
     dist.destroy_process_group()
 

@@ -214,7 +214,7 @@ __global__ void embedding_bwd_kernel(const long long* __restrict__ idx, const T*
 template <typename T>
 __global__ void xent_fwd_kernel(const T* __restrict__ logits, const long long* __restrict__ target,
                                 float* __restrict__ loss, float* __restrict__ lse_out, int rows, int V,
-                                long long ld, long long ignore_index) {
+                                long long ld, long long ignore_index, long long vocab_start) {
   __shared__ float red[33];
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     const T* lr = logits + (long long)row * ld;
@@ -226,9 +226,10 @@ __global__ void xent_fwd_kernel(const T* __restrict__ logits, const long long* _
     s = block_sum(s, red);
     if (threadIdx.x == 0) {
       const float lse = mx + __logf(s);
-      const long long t = target[row];
+      // vocabulary-parallel use: this rank holds columns [vocab_start, vocab_start + V); a target outside contributes 0
+      const long long tg = target[row], t = tg - vocab_start;
       lse_out[row] = lse;
-      loss[row] = (t == ignore_index || t < 0 || t >= V) ? 0.f : lse - to_f<T>(lr[t]);
+      loss[row] = (tg == ignore_index || t < 0 || t >= V) ? 0.f : lse - to_f<T>(lr[t]);
     }
   }
 }
@@ -238,13 +239,13 @@ template <typename T>
 __global__ void xent_bwd_kernel(const T* __restrict__ logits, const long long* __restrict__ target,
                                 const float* __restrict__ lse, const float* __restrict__ gscale,
                                 T* __restrict__ dlogits, int rows, int V, long long ld, long long ldd,
-                                long long ignore_index) {
+                                long long ignore_index, long long vocab_start, long long v_total) {
   const float gs = *gscale;
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     const T* lr = logits + (long long)row * ld;
     T* dr = dlogits + (long long)row * ldd;
-    const long long t = target[row];
-    const bool ignored = (t == ignore_index || t < 0 || t >= V);
+    const long long tg = target[row], t = tg - vocab_start;   // softmax term for every kept row, one-hot only if local
+    const bool ignored = (tg == ignore_index || tg < 0 || tg >= v_total);
     const float l = lse[row];
     for (int i = threadIdx.x; i < V; i += blockDim.x) {
       float g = 0.f;
@@ -363,7 +364,36 @@ B200_API int b200_xent_fwd(const void* logits, const long long* target, float* l
   const int threads = V >= 4096 ? 1024 : 256;
   const int grid = rows < b200_sm_count() * 4 ? rows : b200_sm_count() * 4;
   B200_DISPATCH_DTYPE(dtype, T, (xent_fwd_kernel<T><<<grid, threads, 0, stream>>>(
-      (const T*)logits, target, loss, lse, rows, V, ld, ignore_index)));
+      (const T*)logits, target, loss, lse, rows, V, ld, ignore_index, 0LL)));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Vocabulary-parallel pieces (avoids the all-gather of [M, V] logits behind
+// ColwiseParallel(output_layouts=Replicate()), 01_fsdp_tp_hybrid.py:119-122).  Forward: per-row log-sum-exp over the
+// LOCAL columns [vocab_start, vocab_start + V) and `lse_local - logit[target]` where the target is local, else 0; the
+// caller combines the per-rank pairs (log-sum-exp of the lse, sum of the target terms).  Backward: given the GLOBAL
+// lse, dlogits_local = (exp(x - lse) - onehot_local) * gscale.
+B200_API int b200_xent_fwd_vp(const void* logits, const long long* target, float* loss, float* lse, int rows, int V,
+                              long long ld, long long ignore_index, long long vocab_start, int dtype,
+                              cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  const int threads = V >= 4096 ? 1024 : 256;
+  const int grid = rows < b200_sm_count() * 4 ? rows : b200_sm_count() * 4;
+  B200_DISPATCH_DTYPE(dtype, T, (xent_fwd_kernel<T><<<grid, threads, 0, stream>>>(
+      (const T*)logits, target, loss, lse, rows, V, ld, ignore_index, vocab_start)));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+B200_API int b200_xent_bwd_vp(const void* logits, const long long* target, const float* lse, const float* gscale,
+                              void* dlogits, int rows, int V, long long ld, long long ldd, long long ignore_index,
+                              long long vocab_start, long long v_total, int dtype, cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  const int threads = V >= 4096 ? 1024 : 256;
+  const int grid = rows < b200_sm_count() * 4 ? rows : b200_sm_count() * 4;
+  B200_DISPATCH_DTYPE(dtype, T, (xent_bwd_kernel<T><<<grid, threads, 0, stream>>>(
+      (const T*)logits, target, lse, gscale, (T*)dlogits, rows, V, ld, ldd, ignore_index, vocab_start, v_total)));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -375,7 +405,7 @@ B200_API int b200_xent_bwd(const void* logits, const long long* target, const fl
   const int threads = V >= 4096 ? 1024 : 256;
   const int grid = rows < b200_sm_count() * 4 ? rows : b200_sm_count() * 4;
   B200_DISPATCH_DTYPE(dtype, T, (xent_bwd_kernel<T><<<grid, threads, 0, stream>>>(
-      (const T*)logits, target, lse, gscale, (T*)dlogits, rows, V, ld, ldd, ignore_index)));
+      (const T*)logits, target, lse, gscale, (T*)dlogits, rows, V, ld, ldd, ignore_index, 0LL, (long long)V)));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -119,6 +119,14 @@ B200DIST_API int b200_xent_fwd(const void* logits, const long long* target, floa
 B200DIST_API int b200_xent_bwd(const void* logits, const long long* target, const float* lse,
                            const float* gscale, void* dlogits, int rows, int V, long long ld,
                            long long ldd, long long ignore_index, int dtype, cudaStream_t stream);
+/* vocabulary-parallel pieces: local columns [vocab_start, vocab_start + V) of a [rows, v_total] logits matrix sharded
+ * over tensor-parallel ranks (no counterpart in the reference, whose hybrid recipe gathers the full logits) */
+B200DIST_API int b200_xent_fwd_vp(const void* logits, const long long* target, float* loss, float* lse, int rows, int V,
+                              long long ld, long long ignore_index, long long vocab_start, int dtype,
+                              cudaStream_t stream);
+B200DIST_API int b200_xent_bwd_vp(const void* logits, const long long* target, const float* lse, const float* gscale,
+                              void* dlogits, int rows, int V, long long ld, long long ldd, long long ignore_index,
+                              long long vocab_start, long long v_total, int dtype, cudaStream_t stream);
 B200DIST_API int b200_sum_scale(const float* x, float* out, int n, float scale, cudaStream_t stream);
 
 /* ---- Optimizers ----

@@ -190,3 +190,33 @@ def test_pipeline_1f1b_grads_match():
 
 def test_pipeline_gpipe_grads_match():
     run_distributed(_pp_worker, 3, args=("gpipe",))
+
+
+def _vp_xent_worker(rank, world):
+    from b200dist import ops
+    from b200dist.parallel import init_device_mesh
+    from b200dist.parallel.tp import llama_tp_plan, vocab_parallel_cross_entropy
+
+    ref = _toy_llama()
+    model = _toy_llama()
+    mesh = init_device_mesh("cpu", (world,), ("tp",))
+    llama_tp_plan(model, mesh["tp"], sequence_parallel=True, gather_logits=False)
+    tok = torch.randint(0, 64, (2, 9), generator=torch.Generator().manual_seed(5))
+    x, y = tok[:, :-1], tok[:, 1:].clone()
+    y[0, 2] = -100                                     # an ignored position
+    out = model(x)
+    assert out.shape == (2, 8, 64 // world)            # logits stay vocabulary-sharded: nothing is gathered
+    loss = vocab_parallel_cross_entropy(out, y, mesh["tp"].communicator())
+    loss_ref = ops.cross_entropy(ref(x), y)
+    assert torch.allclose(loss, loss_ref, atol=1e-5), (float(loss), float(loss_ref))
+    loss.backward(); loss_ref.backward()
+    g = model.output.weight.grad
+    gr = ref.output.weight.grad.chunk(world, 0)[rank]
+    assert torch.allclose(g, gr, atol=1e-5, rtol=1e-3), (g - gr).abs().max()
+    g = model.layers[0].attention.wq.weight.grad
+    gr = ref.layers[0].attention.wq.weight.grad.chunk(world, 0)[rank]
+    assert torch.allclose(g, gr, atol=1e-5, rtol=1e-3), (g - gr).abs().max()
+
+
+def test_vocab_parallel_cross_entropy_matches_gathered_logits():
+    run_distributed(_vp_xent_worker, 2)

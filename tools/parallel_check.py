@@ -108,6 +108,20 @@ def main():
             l = ops.cross_entropy(m(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
             losses.append(float(l))
         report(f"TP{world} sp={sp} loss curve", losses, ref_losses, 0.02)
+    # ---------------- vocabulary-parallel cross-entropy (logits never gathered) ----------------
+    from b200dist.parallel.tp import vocab_parallel_cross_entropy
+
+    m = toy().to(dev).to(torch.bfloat16)
+    llama_tp_plan(m, mesh["tp"], sequence_parallel=True, gather_logits=False)
+    opt = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    losses = []
+    for t in data:
+        t = t.to(dev)
+        opt.zero_grad()
+        out = m(t[:, :-1])
+        l = vocab_parallel_cross_entropy(out, t[:, 1:], mesh["tp"].communicator()); l.backward(); opt.step()
+        losses.append(float(l))
+    report(f"TP{world} vocab-parallel loss (local logits {tuple(out.shape)}) loss curve", losses, ref_losses, 0.02)
     # ---------------- fused all-gather->GEMM / GEMM->reduce-scatter TP path ----------------
     from b200dist.parallel.tp import enable_fused_tp
     from b200dist.parallel import tp_fused
