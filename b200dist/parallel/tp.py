@@ -213,10 +213,14 @@ class ColwiseParallel(ParallelStyle):
 
 
 class RowwiseParallel(ParallelStyle):
+    """``fused=True`` (replicated output only) runs GEMM -> all-reduce as ONE fused reduce-scatter GEMM plus a pull
+    all-gather (``tp_fused.linear_ar``) when the input qualifies (CUDA bf16, rows divisible by the TP degree)."""
+
     def __init__(self, *, input_layouts: Optional[Layout] = None, output_layouts: Optional[Layout] = None,
-                 use_local_output: bool = True):
+                 use_local_output: bool = True, fused: bool = False):
         self.input_layouts = input_layouts or Shard(-1)
         self.output_layouts = output_layouts or Replicate()
+        self.fused = fused
 
     def apply(self, module, mesh, name):
         comm, T, r = mesh.communicator(), mesh.size(), mesh.get_local_rank()
@@ -240,7 +244,15 @@ class RowwiseParallel(ParallelStyle):
             module.in_features //= T
         module._tp_info = {"style": "rowwise", "dim": 1, "world": T, "rank": r}
 
+        fused = self.fused and not seq_out
+
         def forward(x, residual=None):
+            if (fused and comm.native and comm.world > 1 and x.is_cuda and x.dtype == torch.bfloat16
+                    and (x.numel() // x.shape[-1]) % comm.world == 0 and module.weight.shape[0] % 8 == 0):
+                from . import tp_fused
+
+                y = tp_fused.linear_ar(comm, x, module.weight, getattr(module, "bias", None))
+                return y + residual if residual is not None else y
             y = ops.linear(x, module.weight, None)  # partial sums; bias is added once, after the reduction
             y = reduce_scatter_seq(y, comm) if seq_out else all_reduce(y, comm)
             b = getattr(module, "bias", None)

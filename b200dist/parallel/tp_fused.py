@@ -159,6 +159,42 @@ class _LinearRS(Function):
         return None, dx.view(1, dx.shape[0], dx.shape[1]), dw, (dy if ctx.has_res else None)
 
 
+class _LinearAR(Function):
+    """all_reduce(x @ w^T) for a row-parallel weight with a REPLICATED output (plain Megatron TP without sequence
+    parallelism: RowwiseParallel(), scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:357-359).
+    Two-shot all-reduce whose first half is fused into the GEMM: the epilogue scatters row blocks to their owners'
+    slabs (GEMM -> reduce-scatter), the owners sum them, and a pull all-gather replicates the reduced blocks - the
+    partial [M, N] product is never written locally."""
+
+    @staticmethod
+    def forward(ctx, comm, x, w, bias):
+        x2 = x.reshape(-1, x.shape[-1])
+        x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        chunk = _gemm_rs(comm, x2, w)
+        if bias is not None:
+            chunk = chunk + bias
+        out = torch.empty((x2.shape[0], chunk.shape[1]), dtype=chunk.dtype, device=chunk.device)
+        comm.all_gather(out, chunk)
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = bias is not None
+        return out.view(*x.shape[:-1], out.shape[-1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w = ctx.saved_tensors
+        d2 = dy.reshape(-1, dy.shape[-1])
+        d2 = d2 if d2.is_contiguous() else d2.contiguous()
+        dx = N.gemm(d2, w, b_mn=True)                      # dY is replicated: the input gradient is purely local
+        dw = N.gemm(d2, x2, a_mn=True, b_mn=True, out_dtype=w.dtype)
+        db = d2.float().sum(0).to(dy.dtype) if ctx.has_bias else None
+        return None, dx.view(*dy.shape[:-1], dx.shape[-1]), dw, db
+
+
+def linear_ar(comm, x, w, bias: Optional[torch.Tensor] = None):
+    """Row-parallel linear with an all-reduced (replicated) output; rows of ``x`` must be divisible by the TP degree."""
+    return _LinearAR.apply(comm, x, w, bias)
+
+
 def ag_linear(comm, x, weights: List[torch.Tensor]):
     return _AGLinear.apply(comm, x, *weights)
 

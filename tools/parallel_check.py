@@ -153,6 +153,12 @@ def main():
     e1 = float((y.float() - yref).abs().max())
     a_full = torch.randn(world * Mloc, K, generator=g2).to(dev).to(torch.bfloat16)
     out = tp_fused._gemm_rs(comm_tp, a_full, wgt)
+    yar = tp_fused.linear_ar(comm_tp, a_full, wgt)         # GEMM -> all-reduce (reduce-scatter fused + all-gather)
+    ar_ref = a_full.float() @ wgt.float().t(); dist.all_reduce(ar_ref)
+    e_ar = float((yar.float() - ar_ref).abs().max())
+    ok &= e_ar < 0.25
+    if rank == 0:
+        print(f"[{'PASS' if e_ar < 0.25 else 'FAIL'}] fused gemm_ar vs GEMM + NCCL all-reduce: max err {e_ar:.3g} (|ref| max {float(ar_ref.abs().max()):.3g})", flush=True)
     pref = (a_full.float() @ wgt.float().t())
     dist.all_reduce(pref)
     e2 = float((out.float() - pref[rank * Mloc:(rank + 1) * Mloc]).abs().max())
