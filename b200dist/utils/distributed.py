@@ -124,6 +124,7 @@ def init_distributed(backend: str = "nccl", verbose: bool = True,
     use_cuda = torch.cuda.is_available()
     if use_cuda:
         torch.cuda.set_device(local_rank % max(1, torch.cuda.device_count()))
+    backend = os.environ.get("B200DIST_BACKEND", backend)   # lets test drivers repeat a script per backend
     if backend == "nccl" and not use_cuda:
         backend = "gloo"
     if world_size > 1 and not dist.is_initialized():
