@@ -266,7 +266,7 @@ using namespace b200;
 // Number of per-CTA partial rows the backward kernels write into `scratch`
 // ([b200_norm_bwd_partials(rows), D] fp32 for RMSNorm, twice that for LayerNorm).
 B200_API int b200_norm_bwd_partials(int rows) {
-  int n = b200_sm_count() * 2;
+  int n = b200_sm_count() * 3;   // = the CTAs resident at once (3 per SM at ~155 registers x 128-256 threads)
   return rows < n ? (rows < 1 ? 1 : rows) : n;
 }
 
@@ -275,7 +275,7 @@ B200_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd
   if (rows <= 0) return B200_OK;
   int threads;
   if (int rc = norm_threads(D, &threads)) return rc;
-  const int grid = rows < b200_sm_count() * 8 ? rows : b200_sm_count() * 8;
+  const int grid = rows;   // one CTA per row: a capped persistent grid ran two unequal waves (7 CTAs/SM resident, 8/SM launched)
   B200_DISPATCH_DTYPE(dtype, T, (rmsnorm_fwd_kernel<T><<<grid, threads, 0, stream>>>(
       (const T*)x, (const T*)w, (T*)y, rstd, rows, D, eps)));
   B200_LAUNCH_CHECK();
@@ -306,7 +306,7 @@ B200_API int b200_layernorm_fwd(const void* x, const void* w, const void* b, voi
   if (rows <= 0) return B200_OK;
   int threads;
   if (int rc = norm_threads(D, &threads)) return rc;
-  const int grid = rows < b200_sm_count() * 8 ? rows : b200_sm_count() * 8;
+  const int grid = rows;   // one CTA per row: a capped persistent grid ran two unequal waves (7 CTAs/SM resident, 8/SM launched)
   B200_DISPATCH_DTYPE(dtype, T, (layernorm_fwd_kernel<T><<<grid, threads, 0, stream>>>(
       (const T*)x, (const T*)w, (const T*)b, (T*)y, mean, rstd, rows, D, eps)));
   B200_LAUNCH_CHECK();
