@@ -20,7 +20,7 @@ import torch.distributed as dist
 
 from ..ops import _lib as L
 from ..utils import debug as _debug
-from .peer_mem import PeerBuffer
+from .peer_mem import MulticastBuffer, PeerBuffer, multicast_supported
 
 I, LL, F, U = C.c_int, C.c_longlong, C.c_float, C.c_uint
 
@@ -45,6 +45,13 @@ class Communicator:
         self.push_threshold = 256 << 10   # all-reduce messages up to this size take the push (latency) path
         self._push_slots = [None] * N_CHANNELS
         self.broadcast2_min_world = 3     # two-stage broadcast pays off once the root would serve >= 2 readers
+        # NVLS (switch-side reduction): tried lazily on the first large all-reduce; None = not tried, False = unavailable
+        self.nvls_threshold = int(os.environ.get("B200DIST_NVLS_MIN_BYTES", str(1 << 20)))
+        self._nvls = None if os.environ.get("B200DIST_NVLS", "1") != "0" else False
+        self._nvls_buf = [None] * N_CHANNELS
+        # through the switch a GPU moves (1 + 1/W) x bytes per direction, the pull two-shot 2 (W-1)/W x bytes: NVLS wins
+        # from W = 4 (1.25 vs 1.5), loses at W = 2 (1.5 vs 1.0)
+        self.nvls_min_world = 4
         self._push_count = [0] * N_CHANNELS
         if self.native:
             self.flags = PeerBuffer(64 << 10, group, self.device)
@@ -117,6 +124,12 @@ class Communicator:
                 and out.data_ptr() % 16 == 0 and t.dtype in (torch.bfloat16, torch.float32)
                 and out.dtype in (torch.bfloat16, torch.float32)):
             return self._all_reduce_push(t, out, scale, channel)
+        if ((algo == 4 or (algo == 0 and self.world >= self.nvls_min_world)) and n * item >= self.nvls_threshold
+                and t.dtype == out.dtype
+                and t.dtype in (torch.bfloat16, torch.float32) and self._nvls_ready()):
+            return self._all_reduce_nvls(t, out, scale, channel)
+        if algo == 4:
+            algo = 2
         pad_to = 8 * self.world
         n_pad = (n + pad_to - 1) // pad_to * pad_to
         buf = self._stage(channel, n_pad * item)
@@ -133,6 +146,77 @@ class Communicator:
         if not direct:
             out.reshape(-1).copy_(dst[:n])
         return out
+
+    def _nvls_ready(self) -> bool:
+        """Collective decision (every rank takes the same branch): all ranks must support NVSwitch multicast."""
+        if self._nvls is None:
+            ok = torch.tensor([1 if multicast_supported() else 0], device=self.device, dtype=torch.int32)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            self._nvls = bool(ok.item())
+        return bool(self._nvls)
+
+    def _all_reduce_nvls(self, t, out, scale, channel):
+        """Large all-reduce through the switch: copy into the multicast buffer, ONE kernel in which every rank
+        ``multimem.ld_reduce``s its 1/world slice (summed by the NVSwitch) and ``multimem.st``s it back to every copy,
+        copy out.  Falls back to the pull kernels for good if the platform refuses to build the multicast object."""
+        n, item = t.numel(), t.element_size()
+        unit = self.world * (16 // item)
+        n_pad = (n + unit - 1) // unit * unit
+        buf = self._nvls_buf[channel]
+        # zero-copy: the tensor already lives in the multicast buffer (Communicator.nvls_tensor), reduce it where it is
+        if (buf is not None and out is t and n_pad == n and buf.local_ptr <= t.data_ptr()
+                and t.data_ptr() + n * item <= buf.local_ptr + buf.nbytes and (t.data_ptr() - buf.local_ptr) % 16 == 0):
+            self._launch_nvls(buf, t.data_ptr() - buf.local_ptr, n, t.dtype, scale, channel)
+            return out
+        if buf is None or buf.nbytes < n_pad * item:
+            buf = self._nvls_alloc(channel, n_pad * item)
+            if buf is None:
+                return self.all_reduce(t, scale=scale, out=out, channel=channel, algo=2)
+        st = buf.tensor(t.dtype, 0, n_pad)
+        st[:n].copy_(t.reshape(-1))
+        if n_pad != n:
+            st[n:].zero_()
+        self._launch_nvls(buf, 0, n_pad, t.dtype, scale, channel)
+        out.reshape(-1).copy_(st[:n])
+        return out
+
+    def _nvls_alloc(self, channel: int, nbytes: int):
+        """Collective (re)allocation of the channel's multicast buffer; None (and NVLS off for good) if refused."""
+        try:
+            buf = MulticastBuffer(max(nbytes, self.staging_bytes), self.group, self.device)
+            okf = 1
+        except Exception as e:  # noqa: BLE001  (driver refused: not permitted / system not ready)
+            self._nvls_error = str(e)
+            buf, okf = None, 0
+        flag = torch.tensor([okf], device=self.device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if not flag.item():
+            self._nvls = False
+            return None
+        self._nvls_buf[channel] = buf
+        return buf
+
+    def _launch_nvls(self, buf, offset_bytes: int, n: int, dtype, scale: float, channel: int) -> None:
+        self._seq[channel] += 1
+        if self._order is not None:
+            self._order.record(channel, "all_reduce_nvls", n)
+        L.call("comm_allreduce_nvls", self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
+               U(self._seq[channel] & 0xFFFFFFFF), C.c_void_p(buf.mc_ptr + offset_bytes), LL(n), F(scale),
+               I(L.dtype_code(dtype)), I(self.max_ctas), self._s())
+
+    def nvls_tensor(self, numel: int, dtype: torch.dtype, channel: int = 0) -> Optional[torch.Tensor]:
+        """Collective: a tensor of ``numel`` elements inside the channel's NVSwitch multicast buffer ("registered"
+        memory).  ``all_reduce`` on it (in place, numel % (world * 16 / itemsize) == 0) runs zero-copy through the
+        switch.  None when NVLS is unavailable.  The tensor is valid until a larger request reallocates the buffer."""
+        if self.world == 1 or not self.native or not self._nvls_ready():
+            return None
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        buf = self._nvls_buf[channel]
+        if buf is None or buf.nbytes < nbytes:
+            buf = self._nvls_alloc(channel, nbytes)
+            if buf is None:
+                return None
+        return buf.tensor(dtype, 0, numel)
 
     def _all_reduce_push(self, t, out, scale, channel):
         """Latency path (<= push_threshold bytes): one kernel, no staging copy-in / copy-out, no depart handshake."""

@@ -77,3 +77,92 @@ class PeerBuffer:
             self._local = None
             lib.b200_peer_free(C.c_void_p(self.local_ptr))
             self.local_ptr = 0
+
+
+def multicast_supported() -> bool:
+    """True when this GPU can join NVSwitch multicast teams (NVLS) and the library exposes the entry points."""
+    if not (torch.cuda.is_available() and L.available()):
+        return False
+    v = C.c_int(0)
+    try:
+        return L.load().b200_mc_supported(C.byref(v)) == 0 and v.value == 1
+    except AttributeError:
+        return False
+
+
+class MulticastBuffer:
+    """Symmetric buffer behind an NVSwitch multicast object: ``tensor()`` views the local copy, ``mc_ptr`` is the
+    multicast address that ``multimem.ld_reduce`` / ``multimem.st`` kernels use (csrc/multicast.cu).
+
+    Collective over ``group``.  Rank 0 creates the object and exports it as a POSIX file descriptor; the descriptor
+    travels to the other processes over an AF_UNIX socket (SCM_RIGHTS), the socket path over torch.distributed.
+    Raises RuntimeError when the platform refuses any step (callers fall back to the pull kernels)."""
+
+    def __init__(self, nbytes: int, group=None, device: Optional[torch.device] = None):
+        import os
+        import socket
+        import tempfile
+        import time
+
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        lib = L.load()
+        self._state = None
+        with torch.cuda.device(self.device):
+            rounded = C.c_size_t(0)
+            L.check(lib.b200_mc_granularity(C.c_size_t(int(nbytes)), C.c_int(self.world), C.byref(rounded)), "mc_granularity")
+            self.nbytes = int(rounded.value)
+            handle = C.c_ulonglong(0)
+            path = [None]
+            if self.rank == 0:
+                fd = C.c_int(-1)
+                L.check(lib.b200_mc_create(C.c_size_t(self.nbytes), C.c_int(self.world), C.byref(handle), C.byref(fd)), "mc_create")
+                path[0] = os.path.join(tempfile.gettempdir(), f"b200dist_mc_{os.getpid()}_{int(time.time() * 1e6) & 0xffffff}.sock")
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path[0])
+                srv.listen(self.world)
+            dist.broadcast_object_list(path, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            if self.rank == 0:
+                for _ in range(self.world - 1):
+                    conn, _a = srv.accept()
+                    socket.send_fds(conn, [b"mc"], [fd.value])
+                    conn.close()
+                srv.close()
+                os.unlink(path[0])
+                os.close(fd.value)
+            else:
+                cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                cli.connect(path[0])
+                _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
+                cli.close()
+                L.check(lib.b200_mc_import(C.c_int(fds[0]), C.byref(handle)), "mc_import")
+                os.close(fds[0])
+            L.check(lib.b200_mc_add_device(handle), "mc_add_device")
+            # binding blocks until every device has been added; the barrier keeps failures from turning into hangs
+            if dist.get_backend(group) == "nccl":
+                dist.barrier(group=group, device_ids=[self.device.index])
+            else:
+                dist.barrier(group=group)
+            lp, mp, st = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            L.check(lib.b200_mc_bind_map(handle, C.c_size_t(self.nbytes), C.byref(lp), C.byref(mp), C.byref(st)), "mc_bind_map")
+        self.local_ptr, self.mc_ptr, self._state = lp.value, mp.value, st
+        self._local = _wrap(self.local_ptr, self.nbytes, self.device)
+        torch.cuda.synchronize(self.device)
+        if dist.get_backend(group) == "nccl":
+            dist.barrier(group=group, device_ids=[self.device.index])
+        else:
+            dist.barrier(group=group)
+
+    def tensor(self, dtype: torch.dtype = torch.uint8, offset_bytes: int = 0, numel: Optional[int] = None):
+        item = torch.empty((), dtype=dtype).element_size()
+        if numel is None:
+            numel = (self.nbytes - offset_bytes) // item
+        return self._local[offset_bytes:offset_bytes + numel * item].view(dtype)
+
+    def close(self):
+        if self._state is not None:
+            self._local = None
+            L.load().b200_mc_release(self._state)
+            self._state = None

@@ -72,6 +72,8 @@ def main():
     ap.add_argument("--benchmark_runs", type=int, default=20)
     ap.add_argument("--output_file", default="results/benchmark_results.log")
     ap.add_argument("--impl", default="both", choices=["b200dist", "nccl", "both"])
+    ap.add_argument("--no-registered", dest="registered", action="store_false",
+                    help="b200dist all-reduce on an ordinary tensor (staging copies) instead of one inside the multicast buffer")
     ap.add_argument("--ops", nargs="+", default=["broadcast", "all_reduce", "all_gather", "reduce_scatter", "send_recv"])
     ap.add_argument("--max_bytes", type=int, default=1 << 30)
     a = ap.parse_args()
@@ -105,7 +107,18 @@ def main():
                     fn = (lambda: comm.broadcast(x, 0)) if impl == "b200dist" else (lambda: dist.broadcast(x, 0))
                     size = nbytes
                 elif op == "all_reduce":
-                    fn = (lambda: comm.all_reduce(x)) if impl == "b200dist" else (lambda: dist.all_reduce(x))
+                    if impl == "b200dist":
+                        # large messages: place the tensor in the NVSwitch multicast buffer ("registered" user buffer, what
+                        # ncclMemAlloc + buffer registration is to NCCL) so the all-reduce runs in place through the switch
+                        xr = comm.nvls_tensor(n_pad, torch.float32) if (a.registered and device.type == "cuda" and world >= comm.nvls_min_world
+                                                                        and nbytes >= comm.nvls_threshold and n_pad % (4 * world) == 0) else None
+                        if xr is not None:
+                            xr.fill_(1.0)
+                            fn = (lambda xr=xr: comm.all_reduce(xr, algo=4))
+                        else:
+                            fn = (lambda: comm.all_reduce(x))
+                    else:
+                        fn = (lambda: dist.all_reduce(x))
                     size = nbytes
                 elif op == "all_gather":
                     if gathered is None:

@@ -1,0 +1,317 @@
+// NVLS data plane: NVSwitch multicast objects (cuMulticast*) + multimem.ld_reduce / multimem.st kernels.
+//
+// A multicast object groups one physical allocation per GPU behind ONE virtual address.  A load with
+// `multimem.ld_reduce` from that address is answered by the SWITCH with the element-wise sum of all GPUs' copies; a
+// `multimem.st` is replicated by the switch into all copies.  An all-reduce therefore costs each GPU one read of its
+// 1/world slice (reduced in the fabric) and one write of that slice (broadcast by the fabric): the SMs never see the
+// peers' partial values.  Per GPU and direction the links carry (1 + 1/world) x bytes (every copy is read once by the
+// switch, own slice included, and written once), against 2 (world-1)/world x bytes for the pull two-shot: NVLS wins
+// from world = 4 and approaches 2x at world = 8 - the algorithm NCCL uses on this box.
+// The pull kernels in comm_kernels.cu stay as the general path and the default below 4 ranks.
+//
+// Host side (all driver entry points are resolved with cudaGetDriverEntryPoint; the library does not link libcuda):
+//   rank 0 : b200_mc_create  -> multicast handle + POSIX fd (the fd is passed to the peers over an AF_UNIX socket by
+//            the Python layer, SCM_RIGHTS)
+//   others : b200_mc_import(fd)
+//   all    : b200_mc_add_device, [barrier], b200_mc_bind_map -> local unicast pointer + multicast pointer
+// Replaces what NCCL does internally for the reference's dist.all_reduce call sites (tests/torch_comm_bench.py:79, DDP).
+#include "vec.cuh"
+#include <cuda.h>
+#include <string.h>
+
+namespace b200 {
+
+template <typename F>
+static F drv(const char* name) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  return reinterpret_cast<F>(fn);
+}
+
+#define MC_DRV(var, name, ...)                                                                   \
+  auto var = drv<CUresult (*)(__VA_ARGS__)>(name);                                               \
+  if (!var) { b200_set_error("multicast: driver entry point %s unavailable", name); return B200_ERR_UNSUPPORTED; }
+#define MC_CHECK(call, what)                                                                     \
+  do {                                                                                           \
+    CUresult _r = (call);                                                                        \
+    if (_r != CUDA_SUCCESS) { b200_set_error("multicast: %s failed with CUresult %d", what, (int)_r); return B200_ERR_CUDA; } \
+  } while (0)
+
+static CUmulticastObjectProp mc_prop(int world, size_t bytes) {
+  CUmulticastObjectProp p;
+  memset(&p, 0, sizeof(p));
+  p.numDevices = (unsigned)world;
+  p.size = bytes;
+  p.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  p.flags = 0;
+  return p;
+}
+
+struct McState {   // one per b200_mc_bind_map, returned to the caller as an opaque handle for b200_mc_release
+  CUmemGenericAllocationHandle mc, mem;
+  CUdeviceptr local_va, mc_va;
+  size_t bytes;
+};
+
+// ---------------------------------------------------------------- kernels
+__device__ __forceinline__ void mm_ldred_f32(const void* p, float (&v)[4]) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void mm_st_f32(void* p, const float (&v)[4]) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+}
+__device__ __forceinline__ uint4 mm_ldred_bf16(const void* p) {   // 8 bf16, accumulated in fp32 inside the switch
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mm_st_bf16(void* p, uint4 r) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
+}
+
+__device__ __forceinline__ void mc_st_release(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t mc_ld_acquire(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// flags: the Communicator's flag pads (same layout as comm_kernels.cu: [channel][2][32] uint32 per rank)
+struct McCtx {
+  uint32_t* flags[8];
+  uint32_t* counter;
+  int rank, world, channel;
+  uint32_t seq;
+};
+__device__ __forceinline__ uint32_t* mc_flag_row(const McCtx& c, int owner, int which) {
+  return c.flags[owner] + ((size_t)c.channel * 2 + which) * 32;
+}
+__device__ __forceinline__ void mc_spin(const uint32_t* p, uint32_t seq) {
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while ((int32_t)(mc_ld_acquire(p) - seq) < 0) {
+    if ((++spins & 0xfffu) == 0) {
+      const uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 5 * B200_WATCHDOG_NS) { printf("b200dist watchdog: nvls flag stuck (want %u have %u)\n", seq, *p); __trap(); }
+    }
+  }
+}
+
+// In-place all-reduce of the multicast buffer: rank r reduces and re-broadcasts elements [r * slice, (r+1) * slice).
+//   arrive : every rank's input is final (flag row 0)
+//   body   : ld_reduce own slice through the switch, scale, multimem.st it back to every copy
+//   depart : every rank's stores have landed everywhere (flag row 1) -> the whole buffer is valid locally
+template <typename T>
+__global__ void __launch_bounds__(512, 1) nvls_allreduce_kernel(McCtx c, T* __restrict__ mc, long long n, float scale) {
+  __shared__ int is_last;
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
+  __syncthreads();
+  constexpr int kPer = 16 / sizeof(T);               // elements per 16-byte access
+  const long long slice = n / c.world;               // n % (world * kPer) == 0 (host-checked)
+  const long long nv = slice / kPer;
+  T* base = mc + (long long)c.rank * slice;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kU = 8;   // 128 bytes of switch requests in flight per thread
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv; i += stride * kU) {
+    if constexpr (sizeof(T) == 4) {
+      float v[kU][4];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) if (i + u * stride < nv) mm_ldred_f32(base + (i + u * stride) * 4, v[u]);
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (i + u * stride < nv) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) v[u][j] *= scale;
+          mm_st_f32(base + (i + u * stride) * 4, v[u]);
+        }
+    } else {
+      uint4 r[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) if (i + u * stride < nv) r[u] = mm_ldred_bf16(base + (i + u * stride) * 8);
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (i + u * stride < nv) {
+          if (scale != 1.f) {
+            r[u].x = pack_bf16(bf16lo(r[u].x) * scale, bf16hi(r[u].x) * scale);
+            r[u].y = pack_bf16(bf16lo(r[u].y) * scale, bf16hi(r[u].y) * scale);
+            r[u].z = pack_bf16(bf16lo(r[u].z) * scale, bf16hi(r[u].z) * scale);
+            r[u].w = pack_bf16(bf16lo(r[u].w) * scale, bf16hi(r[u].w) * scale);
+          }
+          mm_st_bf16(base + (i + u * stride) * 8, r[u]);
+        }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
+    is_last = (done == gridDim.x);
+    if (is_last) c.counter[192 + c.channel] = 0;
+  }
+  __syncthreads();
+  if (is_last) {
+    if (threadIdx.x < c.world) {
+      __threadfence_system();
+      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + c.rank, c.seq);
+      mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// *supported = 1 when the current device can join NVSwitch multicast teams
+B200_API int b200_mc_supported(int* supported) {
+  int dev = 0, v = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  MC_DRV(getattr, "cuDeviceGetAttribute", int*, CUdevice_attribute, CUdevice);
+  MC_CHECK(getattr(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, (CUdevice)dev), "cuDeviceGetAttribute");
+  *supported = v;
+  return B200_OK;
+}
+
+// bytes is rounded up to the recommended multicast granularity; *rounded returns the size every rank must use
+B200_API int b200_mc_granularity(size_t bytes, int world, size_t* rounded) {
+  MC_DRV(getgran, "cuMulticastGetGranularity", size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  CUmulticastObjectProp p = mc_prop(world, bytes);
+  size_t g = 0;
+  MC_CHECK(getgran(&g, &p, CU_MULTICAST_GRANULARITY_RECOMMENDED), "cuMulticastGetGranularity");
+  if (g == 0) g = 2u << 20;
+  *rounded = (bytes + g - 1) / g * g;
+  return B200_OK;
+}
+
+// rank 0: create the multicast object (bytes must come from b200_mc_granularity) and export it as a POSIX fd
+B200_API int b200_mc_create(size_t bytes, int world, unsigned long long* handle, int* fd) {
+  MC_DRV(create, "cuMulticastCreate", CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+  MC_DRV(exportfd, "cuMemExportToShareableHandle", void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long);
+  CUmulticastObjectProp p = mc_prop(world, bytes);
+  CUmemGenericAllocationHandle h;
+  MC_CHECK(create(&h, &p), "cuMulticastCreate");
+  int f = -1;
+  MC_CHECK(exportfd(&f, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0), "cuMemExportToShareableHandle");
+  *handle = (unsigned long long)h;
+  *fd = f;
+  return B200_OK;
+}
+
+B200_API int b200_mc_import(int fd, unsigned long long* handle) {
+  MC_DRV(importfd, "cuMemImportFromShareableHandle", CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType);
+  CUmemGenericAllocationHandle h;
+  MC_CHECK(importfd(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR), "cuMemImportFromShareableHandle");
+  *handle = (unsigned long long)h;
+  return B200_OK;
+}
+
+B200_API int b200_mc_add_device(unsigned long long handle) {
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  MC_DRV(adddev, "cuMulticastAddDevice", CUmemGenericAllocationHandle, CUdevice);
+  MC_CHECK(adddev((CUmemGenericAllocationHandle)handle, (CUdevice)dev), "cuMulticastAddDevice");
+  return B200_OK;
+}
+
+// After EVERY rank has added its device: allocate this GPU's physical backing, map it (local_ptr), bind it to the
+// multicast object and map the multicast object (mc_ptr).  *state is an opaque handle for b200_mc_release.
+B200_API int b200_mc_bind_map(unsigned long long handle, size_t bytes, void** local_ptr, void** mc_ptr, void** state) {
+  int dev = 0;
+  B200_CUDA_CHECK(cudaGetDevice(&dev));
+  MC_DRV(memcreate, "cuMemCreate", CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
+  MC_DRV(reserve, "cuMemAddressReserve", CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long);
+  MC_DRV(map, "cuMemMap", CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long);
+  MC_DRV(setaccess, "cuMemSetAccess", CUdeviceptr, size_t, const CUmemAccessDesc*, size_t);
+  MC_DRV(bind, "cuMulticastBindMem", CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long);
+  MC_DRV(allocgran, "cuMemGetAllocationGranularity", size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
+  CUmemAllocationProp ap;
+  memset(&ap, 0, sizeof(ap));
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = dev;
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t ag = 0;
+  MC_CHECK(allocgran(&ag, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED), "cuMemGetAllocationGranularity");
+  if (ag && bytes % ag) { b200_set_error("multicast: size %zu is not a multiple of the allocation granularity %zu", bytes, ag); return B200_ERR_SHAPE; }
+  McState* st = new McState();
+  st->mc = (CUmemGenericAllocationHandle)handle;
+  st->bytes = bytes;
+  MC_CHECK(memcreate(&st->mem, bytes, &ap, 0), "cuMemCreate");
+  CUmemAccessDesc ad;
+  memset(&ad, 0, sizeof(ad));
+  ad.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ad.location.id = dev;
+  ad.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  MC_CHECK(reserve(&st->local_va, bytes, 0, 0, 0), "cuMemAddressReserve(local)");
+  MC_CHECK(map(st->local_va, bytes, 0, st->mem, 0), "cuMemMap(local)");
+  MC_CHECK(setaccess(st->local_va, bytes, &ad, 1), "cuMemSetAccess(local)");
+  MC_CHECK(bind(st->mc, 0, st->mem, 0, bytes, 0), "cuMulticastBindMem");
+  MC_CHECK(reserve(&st->mc_va, bytes, 0, 0, 0), "cuMemAddressReserve(multicast)");
+  MC_CHECK(map(st->mc_va, bytes, 0, st->mc, 0), "cuMemMap(multicast)");
+  MC_CHECK(setaccess(st->mc_va, bytes, &ad, 1), "cuMemSetAccess(multicast)");
+  B200_CUDA_CHECK(cudaMemset((void*)st->local_va, 0, bytes));
+  B200_CUDA_CHECK(cudaDeviceSynchronize());
+  *local_ptr = (void*)st->local_va;
+  *mc_ptr = (void*)st->mc_va;
+  *state = st;
+  return B200_OK;
+}
+
+B200_API int b200_mc_release(void* state) {
+  McState* st = reinterpret_cast<McState*>(state);
+  if (!st) return B200_OK;
+  auto unmap = drv<CUresult (*)(CUdeviceptr, size_t)>("cuMemUnmap");
+  auto afree = drv<CUresult (*)(CUdeviceptr, size_t)>("cuMemAddressFree");
+  auto release = drv<CUresult (*)(CUmemGenericAllocationHandle)>("cuMemRelease");
+  auto unbind = drv<CUresult (*)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t)>("cuMulticastUnbind");
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceSynchronize();
+  if (unmap && afree && release) {
+    unmap(st->mc_va, st->bytes); afree(st->mc_va, st->bytes);
+    if (unbind) unbind(st->mc, (CUdevice)dev, 0, st->bytes);
+    unmap(st->local_va, st->bytes); afree(st->local_va, st->bytes);
+    release(st->mem); release(st->mc);
+  }
+  delete st;
+  return B200_OK;
+}
+
+// In-place all-reduce (sum, then * scale) of the first n elements of the multicast buffer.  flag_ptrs / counter are the
+// Communicator's signal pads; n must be a multiple of world * (16 / element size).
+B200_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                      unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas,
+                                      cudaStream_t stream) {
+  if (world < 2 || world > 8) { b200_set_error("allreduce_nvls: world %d out of range", world); return B200_ERR_LIMIT; }
+  const int per = dtype == 0 ? 8 : 4;
+  if (n % ((long long)world * per)) { b200_set_error("allreduce_nvls: n must be a multiple of world * %d", per); return B200_ERR_SHAPE; }
+  McCtx c;
+  memset(&c, 0, sizeof(c));
+  for (int r = 0; r < world; ++r) c.flags[r] = reinterpret_cast<uint32_t*>(const_cast<void*>(flag_ptrs[r]));
+  c.counter = reinterpret_cast<uint32_t*>(counter);
+  c.rank = rank; c.world = world; c.channel = channel; c.seq = seq;
+  const long long nv = n / world / per;
+  long long g = (nv + 512 * 8 - 1) / (512 * 8);
+  int cap = max_ctas > 0 ? max_ctas : b200_sm_count();
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  if (dtype == 0) nvls_allreduce_kernel<__nv_bfloat16><<<(int)g, 512, 0, stream>>>(c, (__nv_bfloat16*)mc_ptr, n, scale);
+  else if (dtype == 1) nvls_allreduce_kernel<float><<<(int)g, 512, 0, stream>>>(c, (float*)mc_ptr, n, scale);
+  else { b200_set_error("allreduce_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}

@@ -55,10 +55,13 @@ def main():
         for n in (8 * world, 1024, 100003, 1 << 20, 5 * (1 << 20) + 8 * world):
             x = torch.randint(-8, 8, (n,), device=dev).to(dt)   # integer payload: sums are exact
             ref = x.clone(); dist.all_reduce(ref)
-            for algo in (1, 2):
+            for algo in (1, 2, 4):   # 4 = NVLS (multimem through the switch) when the platform offers it, else two-shot
                 y = x.clone()
                 comm.all_reduce(y, algo=algo)
                 check(f"all_reduce {dt} n={n} algo={algo}", y, ref)
+            ys = x.clone()
+            comm.all_reduce(ys, scale=0.5, algo=4)     # the scale inside the NVLS kernel (DDP averages this way)
+            check(f"all_reduce scaled in place {dt} n={n} algo=4", ys, ref * 0.5)
             y32 = torch.empty(n, device=dev, dtype=torch.float32)
             comm.all_reduce(x, scale=0.5, out=y32)
             check(f"all_reduce scale+cast {dt} n={n}", y32, ref.float() * 0.5)
@@ -105,6 +108,14 @@ def main():
         dist.all_to_all_single(ra, a2)
         comm.all_to_all(oa, a2)
         check(f"all_to_all {dt}", oa, ra)
+    if rank == 0:
+        print(f"[INFO] NVLS multicast path active: {comm._nvls}  {getattr(comm, '_nvls_error', '')}", flush=True)
+    xr = comm.nvls_tensor(1 << 20, torch.bfloat16)          # zero-copy path: tensor inside the multicast buffer
+    if xr is not None:
+        src = torch.randint(-8, 8, (1 << 20,), device=dev).to(torch.bfloat16)
+        ref = src.clone(); dist.all_reduce(ref)
+        xr.copy_(src); comm.all_reduce(xr, algo=4)
+        check("all_reduce NVLS registered tensor (in place, zero copy)", xr, ref)
     # fused reduce-scatter + AdamW vs (NCCL reduce-scatter, torch AdamW)
     n = 1 << 16
     g = torch.randn(n * world, device=dev).bfloat16()
@@ -143,11 +154,12 @@ def main():
         n = mb * (1 << 20) // 2
         x = torch.randn(n, device=dev).bfloat16()
         t_own = ev_time(lambda: comm.all_reduce(x, algo=2))
+        t_nvls = ev_time(lambda: comm.all_reduce(x, algo=4))
         t_nccl = ev_time(lambda: dist.all_reduce(x))
         bus = lambda t: 2 * (world - 1) / world * n * 2 / t / 1e6
         if rank == 0:
-            print(f"[TIME] all_reduce {mb} MiB bf16 x{world}: own {t_own*1e3:.1f} us busbw {bus(t_own):.0f} GB/s | "
-                  f"NCCL {t_nccl*1e3:.1f} us busbw {bus(t_nccl):.0f} GB/s", flush=True)
+            print(f"[TIME] all_reduce {mb} MiB bf16 x{world}: two-shot {t_own*1e3:.1f} us busbw {bus(t_own):.0f} GB/s | "
+                  f"nvls {t_nvls*1e3:.1f} us busbw {bus(t_nvls):.0f} GB/s | NCCL {t_nccl*1e3:.1f} us busbw {bus(t_nccl):.0f} GB/s", flush=True)
         out = torch.empty(n * world, device=dev, dtype=torch.bfloat16)
         t_own = ev_time(lambda: comm.all_gather(out, x))
         t_nccl = ev_time(lambda: dist.all_gather_into_tensor(out, x))
@@ -156,9 +168,10 @@ def main():
             print(f"[TIME] all_gather {mb} MiB/rank: own {t_own*1e3:.1f} us busbw {busg(t_own):.0f} GB/s | NCCL {t_nccl*1e3:.1f} us "
                   f"busbw {busg(t_nccl):.0f} GB/s", flush=True)
     x32 = torch.randn(64 << 20, device=dev)
-    t_own = ev_time(lambda: comm.all_reduce(x32, algo=2)); t_nccl = ev_time(lambda: dist.all_reduce(x32))
+    t_own = ev_time(lambda: comm.all_reduce(x32, algo=2)); t_nvls = ev_time(lambda: comm.all_reduce(x32, algo=4))
+    t_nccl = ev_time(lambda: dist.all_reduce(x32))
     if rank == 0:
-        print(f"[TIME] all_reduce 256 MiB fp32 x{world}: own {t_own*1e3:.1f} us | NCCL {t_nccl*1e3:.1f} us", flush=True)
+        print(f"[TIME] all_reduce 256 MiB fp32 x{world}: two-shot {t_own*1e3:.1f} us | nvls {t_nvls*1e3:.1f} us | NCCL {t_nccl*1e3:.1f} us", flush=True)
     del x32
     x = torch.zeros(8, device=dev)
     t_own = ev_time(lambda: comm.barrier(), iters=50)
