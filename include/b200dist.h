@@ -223,4 +223,20 @@ B200DIST_API int b200_comm_slab_reduce(const void* const* data_ptrs, const void*
                   int world, int channel, unsigned seq, void* out, const void* residual, long long n, int max_ctas,
                                    cudaStream_t stream);
 
+/* ---- NVLS: NVSwitch multicast objects + in-switch reduction (csrc/multicast.cu) ----
+ * rank 0: b200_mc_create (handle + POSIX fd to pass to the peers); others: b200_mc_import(fd); all: b200_mc_add_device,
+ * barrier, b200_mc_bind_map -> local unicast pointer + multicast pointer.  b200_comm_allreduce_nvls reduces the first n
+ * elements of the multicast buffer in place (sum * scale); n % (world * 16 / element size) == 0.  Plays the role of
+ * NCCL's NVLS algorithm behind dist.all_reduce (tests/torch_comm_bench.py:79, DDP buckets). */
+B200DIST_API int b200_mc_supported(int* supported);
+B200DIST_API int b200_mc_granularity(size_t bytes, int world, size_t* rounded);
+B200DIST_API int b200_mc_create(size_t bytes, int world, unsigned long long* handle, int* fd);
+B200DIST_API int b200_mc_import(int fd, unsigned long long* handle);
+B200DIST_API int b200_mc_add_device(unsigned long long handle);
+B200DIST_API int b200_mc_bind_map(unsigned long long handle, size_t bytes, void** local_ptr, void** mc_ptr, void** state);
+B200DIST_API int b200_mc_release(void* state);
+B200DIST_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                      unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas,
+                                      cudaStream_t stream);
+
 #endif  /* B200DIST_H_ */
