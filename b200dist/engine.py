@@ -10,11 +10,27 @@ scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:171-180) has exactly this sha
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Optional
 
 import torch
 
 from . import ops
+
+
+class InjectedFault(RuntimeError):
+    """Raised by the fault-injection hook (``B200DIST_INJECT_FAULT=rank:step``)."""
+
+
+def _fault_spec():
+    """``B200DIST_INJECT_FAULT="rank:step"`` makes that rank fail right before that (0-based) optimizer step - a test
+    hook for restart-from-checkpoint drills (the reference has no fault injection; its only recovery
+    path is resuming from snapshot.pt, scripts/01_data_parallel_ddp/multinode_ddp_basic.py:144-155)."""
+    spec = os.environ.get("B200DIST_INJECT_FAULT", "")
+    if not spec:
+        return None
+    r, s = spec.split(":")
+    return int(r), int(s)
 
 
 def lm_loss(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
@@ -30,9 +46,13 @@ class Trainer:
         self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._staged = None
         self.steps_done = 0
+        self._fault = _fault_spec()
+        self._rank = int(os.environ.get("RANK", "0"))
 
     # ---------------------------------------------------------------- device-resident step
     def train_step(self, inputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        if self._fault is not None and self._fault == (self._rank, self.steps_done):
+            raise InjectedFault(f"injected fault on rank {self._rank} before step {self.steps_done}")
         self.optimizer.zero_grad(set_to_none=True)
         out = self.model(inputs)
         loss = self.loss_fn(out, targets)

@@ -86,6 +86,8 @@ def dtype_code(dt: torch.dtype) -> int:
     raise NativeError(f"b200dist kernels support bf16 and fp32 tensors, got {dt}")
 
 
+_NVTX = os.environ.get("B200DIST_NVTX", "0") not in ("", "0")
+
 # entry points that launch more than one kernel
 _KERNELS_PER_CALL = {"rmsnorm_bwd": 2, "layernorm_bwd": 3, "flash_attn_bwd": 3}
 
@@ -95,6 +97,13 @@ def call(name: str, *args) -> None:
     global launch_count
     fn = getattr(load(), "b200_" + name)
     launch_count += _KERNELS_PER_CALL.get(name, 1)
-    check(fn(*args), name)
+    if _NVTX:   # B200DIST_NVTX=1: one NVTX range per native call (kernels and collectives) for nsys / torch.profiler
+        torch.cuda.nvtx.range_push("b200_" + name)
+        try:
+            check(fn(*args), name)
+        finally:
+            torch.cuda.nvtx.range_pop()
+    else:
+        check(fn(*args), name)
     if _debug.sync_debug_enabled():
         _debug.after_native_call(name)

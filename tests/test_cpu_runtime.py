@@ -257,3 +257,59 @@ def test_sync_debug_toggle():
     with debug.sync_debug():
         assert debug.sync_debug_enabled()
     assert not debug.sync_debug_enabled()
+
+
+def test_fault_injection_and_resume_from_checkpoint(tmp_path, monkeypatch):
+    """Restart-from-checkpoint drill: a fault injected before step 2 kills the run, a fresh Trainer resumes from the
+    last checkpoint and ends with exactly the weights of an uninterrupted run."""
+    import pytest
+
+    from b200dist.engine import InjectedFault, Trainer
+    from b200dist.utils import load_checkpoint, save_checkpoint
+
+    def make():
+        torch.manual_seed(0)
+        m = torch.nn.Linear(8, 4)
+        return m, torch.optim.SGD(m.parameters(), lr=0.1, momentum=0.9)
+
+    data = [(torch.randn(5, 8, generator=torch.Generator().manual_seed(i)), torch.randint(0, 4, (5,), generator=torch.Generator().manual_seed(i)))
+            for i in range(4)]
+    loss = torch.nn.functional.cross_entropy
+    m_ref, o_ref = make()
+    t = Trainer(m_ref, o_ref, loss_fn=loss)
+    for x, y in data:
+        t.train_step(x, y)
+    ck = str(tmp_path / "ck.pt")
+    monkeypatch.setenv("B200DIST_INJECT_FAULT", "0:2")
+    m, o = make()
+    t = Trainer(m, o, loss_fn=loss)
+    with pytest.raises(InjectedFault):
+        for i, (x, y) in enumerate(data):
+            t.train_step(x, y)
+            save_checkpoint(m, o, i + 1, ck)
+    monkeypatch.delenv("B200DIST_INJECT_FAULT")
+    m2, o2 = make()
+    done = load_checkpoint(m2, o2, ck)
+    assert done == 2
+    t2 = Trainer(m2, o2, loss_fn=loss)
+    for x, y in data[done:]:
+        t2.train_step(x, y)
+    assert torch.allclose(m2.weight, m_ref.weight) and torch.allclose(m2.bias, m_ref.bias)
+
+
+def test_public_header_declares_every_exported_symbol():
+    """include/b200dist.h is the C ABI contract: every b200_* symbol the library exports must be declared there."""
+    import re
+    import subprocess
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    so = root / "b200dist" / "_native" / "libb200dist.so"
+    if not so.exists():
+        import pytest
+
+        pytest.skip("native library not built")
+    out = subprocess.run(["nm", "-D", "--defined-only", str(so)], capture_output=True, text=True, check=True).stdout
+    exported = {l.split()[-1] for l in out.splitlines() if " T b200_" in l}
+    declared = set(re.findall(r"\bb200_[a-z0-9_]+", (root / "include" / "b200dist.h").read_text()))
+    assert exported and not (exported - declared), sorted(exported - declared)
