@@ -51,7 +51,7 @@ class Communicator:
         self._nvls_buf = [None] * N_CHANNELS
         # through the switch a GPU moves (1 + 1/W) x bytes per direction, the pull two-shot 2 (W-1)/W x bytes: NVLS wins
         # from W = 4 (1.25 vs 1.5), loses at W = 2 (1.5 vs 1.0)
-        self.nvls_min_world = 4
+        self.nvls_min_world = int(os.environ.get("B200DIST_NVLS_MIN_WORLD", "4"))
         self._push_count = [0] * N_CHANNELS
         if self.native:
             self.flags = PeerBuffer(64 << 10, group, self.device)
@@ -203,6 +203,33 @@ class Communicator:
         L.call("comm_allreduce_nvls", self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
                U(self._seq[channel] & 0xFFFFFFFF), C.c_void_p(buf.mc_ptr + offset_bytes), LL(n), F(scale),
                I(L.dtype_code(dtype)), I(self.max_ctas), self._s())
+
+    def nvls_buffer(self, nbytes: int):
+        """Collective: a dedicated NVSwitch multicast buffer (e.g. all DDP buckets of a model); None if unavailable."""
+        if self.world == 1 or not self.native or not self._nvls_ready():
+            return None
+        try:
+            buf = MulticastBuffer(nbytes, self.group, self.device)
+            okf = 1
+        except Exception as e:  # noqa: BLE001
+            self._nvls_error = str(e)
+            buf, okf = None, 0
+        flag = torch.tensor([okf], device=self.device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if not flag.item():
+            if buf is not None:
+                buf.close()
+            self._nvls = False
+            return None
+        return buf
+
+    def all_reduce_nvls_inplace(self, buf, offset_bytes: int, numel: int, dtype: torch.dtype, scale: float = 1.0,
+                                channel: int = 0) -> None:
+        """Reduce ``numel`` elements at ``offset_bytes`` of multicast buffer ``buf`` in place on every rank
+        (numel % (world * 16 / itemsize) == 0, offset 16-byte aligned)."""
+        item = torch.empty((), dtype=dtype).element_size()
+        assert offset_bytes % 16 == 0 and numel % (self.world * (16 // item)) == 0
+        self._launch_nvls(buf, offset_bytes, numel, dtype, scale, channel)
 
     def nvls_tensor(self, numel: int, dtype: torch.dtype, channel: int = 0) -> Optional[torch.Tensor]:
         """Collective: a tensor of ``numel`` elements inside the channel's NVSwitch multicast buffer ("registered"

@@ -95,65 +95,89 @@ class MulticastBuffer:
     multicast address that ``multimem.ld_reduce`` / ``multimem.st`` kernels use (csrc/multicast.cu).
 
     Collective over ``group``.  Rank 0 creates the object and exports it as a POSIX file descriptor; the descriptor
-    travels to the other processes over an AF_UNIX socket (SCM_RIGHTS), the socket path over torch.distributed.
-    Raises RuntimeError when the platform refuses any step (callers fall back to the pull kernels)."""
+    travels to the other processes over an AF_UNIX socket (SCM_RIGHTS), the socket path over torch.distributed.  After
+    every phase the ranks agree on success, so a refusal on ANY rank (not permitted, system not ready, ...) raises
+    RuntimeError on ALL ranks instead of leaving the others blocked; callers then fall back to the pull kernels."""
 
     def __init__(self, nbytes: int, group=None, device: Optional[torch.device] = None):
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self._state = None
+        self._lib = L.load()
+        with torch.cuda.device(self.device):
+            handle = C.c_ulonglong(0)
+            self._agree(self._phase_create(int(nbytes), handle), "create / share the multicast object")
+            self._agree(self._try(lambda: L.check(self._lib.b200_mc_add_device(handle), "mc_add_device")), "add the device")
+            lp, mp, st = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            # binding blocks until every device has been added: the agreement above doubles as that barrier
+            self._agree(self._try(lambda: L.check(self._lib.b200_mc_bind_map(
+                handle, C.c_size_t(self.nbytes), C.byref(lp), C.byref(mp), C.byref(st)), "mc_bind_map")), "bind and map memory")
+        self.local_ptr, self.mc_ptr, self._state = lp.value, mp.value, st
+        self._local = _wrap(self.local_ptr, self.nbytes, self.device)
+        torch.cuda.synchronize(self.device)
+        self._agree(None, "finish")
+
+    @staticmethod
+    def _try(fn) -> Optional[str]:
+        try:
+            fn()
+            return None
+        except Exception as e:  # noqa: BLE001
+            return str(e)
+
+    def _agree(self, err: Optional[str], what: str) -> None:
+        flag = torch.tensor([0 if err is None else 1], device=self.device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.group)
+        if flag.item():
+            raise RuntimeError(f"NVSwitch multicast unavailable (could not {what}): {err or 'refused on another rank'}")
+
+    def _phase_create(self, nbytes: int, handle) -> Optional[str]:
         import os
         import socket
         import tempfile
         import time
 
-        self.group = group
-        self.rank = dist.get_rank(group)
-        self.world = dist.get_world_size(group)
-        self.device = device or torch.device("cuda", torch.cuda.current_device())
-        lib = L.load()
-        self._state = None
-        with torch.cuda.device(self.device):
-            rounded = C.c_size_t(0)
-            L.check(lib.b200_mc_granularity(C.c_size_t(int(nbytes)), C.c_int(self.world), C.byref(rounded)), "mc_granularity")
-            self.nbytes = int(rounded.value)
-            handle = C.c_ulonglong(0)
-            path = [None]
-            if self.rank == 0:
-                fd = C.c_int(-1)
-                L.check(lib.b200_mc_create(C.c_size_t(self.nbytes), C.c_int(self.world), C.byref(handle), C.byref(fd)), "mc_create")
-                path[0] = os.path.join(tempfile.gettempdir(), f"b200dist_mc_{os.getpid()}_{int(time.time() * 1e6) & 0xffffff}.sock")
+        lib = self._lib
+        path, err, fd = [None], None, C.c_int(-1)
+        rounded = C.c_size_t(0)
+        err = self._try(lambda: L.check(lib.b200_mc_granularity(C.c_size_t(nbytes), C.c_int(self.world), C.byref(rounded)),
+                                        "mc_granularity"))
+        self.nbytes = int(rounded.value) if err is None else nbytes
+        srv = None
+        if self.rank == 0 and err is None:
+            err = self._try(lambda: L.check(lib.b200_mc_create(C.c_size_t(self.nbytes), C.c_int(self.world), C.byref(handle),
+                                                               C.byref(fd)), "mc_create"))
+            if err is None:
+                path[0] = os.path.join(tempfile.gettempdir(),
+                                       f"b200dist_mc_{os.getpid()}_{int(time.time() * 1e6) & 0xffffff}.sock")
                 srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
                 srv.bind(path[0])
                 srv.listen(self.world)
-            dist.broadcast_object_list(path, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-            if self.rank == 0:
-                for _ in range(self.world - 1):
-                    conn, _a = srv.accept()
-                    socket.send_fds(conn, [b"mc"], [fd.value])
-                    conn.close()
-                srv.close()
-                os.unlink(path[0])
-                os.close(fd.value)
-            else:
-                cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                cli.connect(path[0])
-                _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
-                cli.close()
-                L.check(lib.b200_mc_import(C.c_int(fds[0]), C.byref(handle)), "mc_import")
-                os.close(fds[0])
-            L.check(lib.b200_mc_add_device(handle), "mc_add_device")
-            # binding blocks until every device has been added; the barrier keeps failures from turning into hangs
-            if dist.get_backend(group) == "nccl":
-                dist.barrier(group=group, device_ids=[self.device.index])
-            else:
-                dist.barrier(group=group)
-            lp, mp, st = C.c_void_p(), C.c_void_p(), C.c_void_p()
-            L.check(lib.b200_mc_bind_map(handle, C.c_size_t(self.nbytes), C.byref(lp), C.byref(mp), C.byref(st)), "mc_bind_map")
-        self.local_ptr, self.mc_ptr, self._state = lp.value, mp.value, st
-        self._local = _wrap(self.local_ptr, self.nbytes, self.device)
-        torch.cuda.synchronize(self.device)
-        if dist.get_backend(group) == "nccl":
-            dist.barrier(group=group, device_ids=[self.device.index])
-        else:
-            dist.barrier(group=group)
+        src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+        dist.broadcast_object_list(path, src=src, group=self.group)   # None = rank 0 could not create the object
+        if path[0] is None:
+            return err or "rank 0 could not create the multicast object"
+        if self.rank == 0:
+            for _ in range(self.world - 1):
+                conn, _a = srv.accept()
+                socket.send_fds(conn, [b"mc"], [fd.value])
+                conn.close()
+            srv.close()
+            os.unlink(path[0])
+            os.close(fd.value)
+            return None
+        if err is not None:   # still drain the connection so rank 0 does not block in accept()
+            pass
+        cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        cli.connect(path[0])
+        _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
+        cli.close()
+        if err is None:
+            err = self._try(lambda: L.check(lib.b200_mc_import(C.c_int(fds[0]), C.byref(handle)), "mc_import"))
+        os.close(fds[0])
+        return err
 
     def tensor(self, dtype: torch.dtype = torch.uint8, offset_bytes: int = 0, numel: Optional[int] = None):
         item = torch.empty((), dtype=dtype).element_size()

@@ -40,13 +40,20 @@ class _Bucket:
         for p in params:
             self.offsets.append(n)
             n += (p.numel() + 7) // 8 * 8  # keep every slot 16/32-byte aligned
-        self.numel = n
+        self.numel = n = (n + 63) // 64 * 64   # whole 16-byte vectors per rank for any world <= 8 (NVLS slices)
+        self.dtype = dtype
+        self.mc_offset = None                  # byte offset inside the DDP multicast buffer when NVLS is in use
         self.flat = torch.zeros(n, dtype=dtype, device=device)
         self.views = [self.flat[o:o + p.numel()].view(p.shape) for o, p in zip(self.offsets, params)]
         self.pending = len(params)
         self.ready = [False] * len(params)
         self.event = None
         self.launched = False
+
+    def rebase(self, flat: torch.Tensor, mc_offset: int) -> None:
+        """Move the bucket into ``flat`` (a view of the multicast buffer's local copy)."""
+        self.flat, self.mc_offset = flat, mc_offset
+        self.views = [flat[o:o + p.numel()].view(p.shape) for o, p in zip(self.offsets, self.params)]
 
     def reset(self):
         self.pending = len(self.params)
@@ -73,6 +80,8 @@ class DistributedDataParallel(nn.Module):
         self._stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._sync_module_states()
         self._build_buckets(params, bucket_cap_mb, first_bucket_mb)
+        self._mc = None
+        self._place_buckets_in_multicast_memory()
         self._hooks = []
         for b in self.buckets:
             for i, p in enumerate(b.params):
@@ -114,6 +123,32 @@ class DistributedDataParallel(nn.Module):
         if cur:
             self.buckets.append(_Bucket(cur, cur_dtype, self.device, len(self.buckets)))
 
+    def _place_buckets_in_multicast_memory(self) -> None:
+        """From ``nvls_min_world`` ranks up the buckets live inside ONE NVSwitch multicast buffer, so a bucket all-reduce
+        is a single zero-copy NVLS kernel: ``multimem.ld_reduce`` of the rank's slice (summed in the switch), x 1/world,
+        ``multimem.st`` to every replica.  Otherwise (fewer ranks, no multicast support, CPU)
+        buckets are ordinary tensors reduced through the staging buffer by the two-shot pull kernel."""
+        comm = self.comm
+        if not (comm.native and self.device.type == "cuda" and comm.world >= comm.nvls_min_world and self.buckets):
+            return
+        if not comm._nvls_ready():
+            return
+        offs, total = [], 0
+        for b in self.buckets:
+            offs.append(total)
+            total += (b.numel * b.flat.element_size() + 255) // 256 * 256
+        self._mc = comm.nvls_buffer(total)
+        if self._mc is None:
+            return
+        for b, o in zip(self.buckets, offs):
+            b.rebase(self._mc.tensor(b.dtype, o, b.numel), o)
+
+    def _reduce(self, bucket: _Bucket, scale: float) -> None:
+        if bucket.mc_offset is not None:
+            self.comm.all_reduce_nvls_inplace(self._mc, bucket.mc_offset, bucket.numel, bucket.dtype, scale, self._channel)
+        else:
+            self.comm.all_reduce(bucket.flat, scale=scale, channel=self._channel)
+
     # ------------------------------------------------------------------ backward hooks
     def _make_hook(self, bucket: _Bucket, slot: int):
         def hook(p: torch.Tensor):
@@ -139,13 +174,13 @@ class DistributedDataParallel(nn.Module):
         bucket.launched = True
         scale = 1.0 / self.world
         if self._stream is None:
-            self.comm.all_reduce(bucket.flat, scale=scale, channel=self._channel)
+            self._reduce(bucket, scale)
             return
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(self._stream):
             self._stream.wait_event(ev)
-            self.comm.all_reduce(bucket.flat, scale=scale, channel=self._channel)
+            self._reduce(bucket, scale)
             bucket.event = torch.cuda.Event()
             bucket.event.record(self._stream)
 

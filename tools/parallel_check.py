@@ -95,6 +95,21 @@ def main():
         l = ops.cross_entropy(d(t[:, :-1]), t[:, 1:]); l.backward(); d.finish_backward(); opt.step()
         lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
     report(f"DDP ({len(d.buckets)} buckets) loss curve", losses, ref_losses2, 0.02)
+    # same again with the buckets inside an NVSwitch multicast buffer (zero-copy NVLS all-reduce; default from 4 ranks)
+    from b200dist.comm import get_communicator as _gc
+
+    _c = _gc(None); _prev = _c.nvls_min_world; _c.nvls_min_world = 2
+    m = toy().to(dev).to(torch.bfloat16)
+    d = DDP(m, bucket_cap_mb=1.0, first_bucket_mb=0.25)
+    _c.nvls_min_world = _prev
+    opt = FusedSGD(d.parameters(), lr=0.05, momentum=0.9)
+    losses = []
+    for t in data:
+        t = t.chunk(world)[rank].to(dev)
+        opt.zero_grad()
+        l = ops.cross_entropy(d(t[:, :-1]), t[:, 1:]); l.backward(); d.finish_backward(); opt.step()
+        lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+    report(f"DDP buckets in multicast memory (NVLS active: {d._mc is not None}) loss curve", losses, ref_losses2, 0.02)
     # ---------------- TP + SP ----------------
     mesh = init_device_mesh("cuda", (world,), ("tp",))
     for sp in (True, False):
