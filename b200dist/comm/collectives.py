@@ -49,6 +49,8 @@ class Communicator:
         self.nvls_threshold = int(os.environ.get("B200DIST_NVLS_MIN_BYTES", str(1 << 20)))
         self._nvls = None if os.environ.get("B200DIST_NVLS", "1") != "0" else False
         self._nvls_buf = [None] * N_CHANNELS
+        # broadcast through the switch (multimem.st from the root): correctness-checked, not yet timed at 8 GPUs -> opt-in
+        self.nvls_broadcast = os.environ.get("B200DIST_NVLS_BROADCAST", "0") not in ("", "0")
         # through the switch a GPU moves (1 + 1/W) x bytes per direction, the pull two-shot 2 (W-1)/W x bytes: NVLS wins
         # from W = 4 (1.25 vs 1.5), loses at W = 2 (1.5 vs 1.0)
         self.nvls_min_world = int(os.environ.get("B200DIST_NVLS_MIN_WORLD", "4"))
@@ -361,6 +363,20 @@ class Communicator:
             return t
         assert t.is_contiguous()
         nbytes = t.numel() * t.element_size()
+        if (self.nvls_broadcast and self.world >= self.nvls_min_world and nbytes >= self.nvls_threshold and nbytes % 16 == 0
+                and t.data_ptr() % 16 == 0 and self._nvls_ready()):
+            mc = self._nvls_buf[channel]
+            if mc is None or mc.nbytes < nbytes:
+                mc = self._nvls_alloc(channel, nbytes)
+            if mc is not None:
+                # the root streams its tensor through the switch (multimem.st); the others copy their replica out
+                self._seq[channel] += 1
+                if self._order is not None:
+                    self._order.record(channel, "broadcast_nvls", nbytes)
+                L.call("comm_broadcast_nvls", self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world),
+                       I(channel), U(self._seq[channel] & 0xFFFFFFFF), L.ptr(t), C.c_void_p(mc.mc_ptr),
+                       C.c_void_p(mc.local_ptr), L.ptr(t), LL(nbytes), I(src), I(self.max_ctas), self._s())
+                return t
         pad = (nbytes + 15) // 16 * 16
         buf = self._stage(channel, pad)
         if self.rank == src:

@@ -172,6 +172,61 @@ __global__ void __launch_bounds__(512, 1) nvls_allreduce_kernel(McCtx c, T* __re
   }
 }
 
+// Broadcast through the switch: the root streams its payload with multimem.st (one egress copy, replicated by the
+// NVSwitch into every rank's buffer), then releases a flag; the other ranks copy their local replica out.
+//   row 0 arrive/wait (all ranks): everybody has left the previous collective on this channel, the buffer is free
+//   row 1, slot `root`            : "payload landed"
+// `src` (root only) may be any device pointer, including the root's own replica (registered in-place use);
+// `out` == nullptr skips the copy-out (the caller reads the replica in place).
+__global__ void __launch_bounds__(512, 1) nvls_broadcast_kernel(McCtx c, const uint4* __restrict__ src, uint4* __restrict__ mc,
+                                                               const uint4* __restrict__ replica, uint4* __restrict__ out,
+                                                               long long n16, int root) {
+  __shared__ int is_last;
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (c.rank == root) {
+    constexpr int kU = 8;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride * kU) {
+      uint4 v[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) if (i + u * stride < n16) v[u] = src[i + u * stride];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (i + u * stride < n16)
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                       :: "l"(mc + i + u * stride), "f"(__uint_as_float(v[u].x)), "f"(__uint_as_float(v[u].y)),
+                          "f"(__uint_as_float(v[u].z)), "f"(__uint_as_float(v[u].w)) : "memory");
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
+      is_last = (done == gridDim.x);
+      if (is_last) c.counter[192 + c.channel] = 0;
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x < c.world) {
+      __threadfence_system();
+      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + root, c.seq);
+    }
+    return;
+  }
+  if (threadIdx.x == 0) mc_spin(mc_flag_row(c, c.rank, 1) + root, c.seq);
+  __syncthreads();
+  if (out == nullptr) return;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride) {
+    uint4 v;   // written by the switch during this kernel: coherent load
+    asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(replica + i));
+    out[i] = v;
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -312,6 +367,30 @@ B200_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counte
   if (dtype == 0) nvls_allreduce_kernel<__nv_bfloat16><<<(int)g, 512, 0, stream>>>(c, (__nv_bfloat16*)mc_ptr, n, scale);
   else if (dtype == 1) nvls_allreduce_kernel<float><<<(int)g, 512, 0, stream>>>(c, (float*)mc_ptr, n, scale);
   else { b200_set_error("allreduce_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Broadcast `bytes` (multiple of 16) from `root` through the multicast buffer.  src: the root's payload (ignored on
+// other ranks); mc_ptr / replica_ptr: multicast address and this rank's local replica of the SAME region;
+// out: destination on non-root ranks, or NULL to leave the data in the replica.
+B200_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                      unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
+                                      long long bytes, int root, int max_ctas, cudaStream_t stream) {
+  if (world < 2 || world > 8) { b200_set_error("broadcast_nvls: world %d out of range", world); return B200_ERR_LIMIT; }
+  if (bytes & 15) { b200_set_error("broadcast_nvls: bytes must be a multiple of 16"); return B200_ERR_SHAPE; }
+  McCtx c;
+  memset(&c, 0, sizeof(c));
+  for (int r = 0; r < world; ++r) c.flags[r] = reinterpret_cast<uint32_t*>(const_cast<void*>(flag_ptrs[r]));
+  c.counter = reinterpret_cast<uint32_t*>(counter);
+  c.rank = rank; c.world = world; c.channel = channel; c.seq = seq;
+  const long long n16 = bytes >> 4;
+  long long g = (n16 + 512 * 8 - 1) / (512 * 8);
+  int cap = max_ctas > 0 ? max_ctas : b200_sm_count();
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  nvls_broadcast_kernel<<<(int)g, 512, 0, stream>>>(c, (const uint4*)src, (uint4*)mc_ptr, (const uint4*)replica_ptr,
+                                                     (uint4*)out, n16, root);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

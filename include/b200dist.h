@@ -238,5 +238,8 @@ B200DIST_API int b200_mc_release(void* state);
 B200DIST_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                       unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas,
                                       cudaStream_t stream);
+B200DIST_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                      unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
+                                      long long bytes, int root, int max_ctas, cudaStream_t stream);
 
 #endif  /* B200DIST_H_ */

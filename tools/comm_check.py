@@ -88,6 +88,15 @@ def main():
         comm.broadcast(bb, src=0)
         comm.broadcast2_min_world = 3
         check(f"broadcast two-stage {dt} {bb.numel()} elems", bb, rbb)
+        prev = (comm.nvls_broadcast, comm.nvls_min_world)
+        comm.nvls_broadcast, comm.nvls_min_world = True, 2      # broadcast through the switch (multimem.st), both roots
+        for root in (0, world - 1):
+            for rep in range(2):
+                bn = torch.randint(-8, 8, (bb.numel(),), device=dev).to(dt); rbn = bn.clone()
+                dist.broadcast(rbn, src=root)
+                comm.broadcast(bn, src=root)
+                check(f"broadcast NVLS {dt} root {root} call {rep}", bn, rbn)
+        comm.nvls_broadcast, comm.nvls_min_world = prev
         n = 1 << 18
         x = torch.randint(-8, 8, (n,), device=dev).to(dt)
         out = torch.empty(n * world, device=dev, dtype=dt); ref = torch.empty_like(out)
