@@ -20,6 +20,7 @@ from dataclasses import dataclass
 from typing import Optional
 
 import torch
+import torch.utils.checkpoint
 from torch import nn
 
 from .. import ops
@@ -196,8 +197,15 @@ class Transformer(nn.Module):
         self.layers = nn.ModuleList(TransformerBlock(i, model_args) for i in range(model_args.n_layers))
         self.norm = RMSNorm(model_args.dim, eps=model_args.norm_eps)
         self.output = Linear(model_args.dim, model_args.vocab_size)
+        # Per-block activation checkpointing (the reference only describes it, docs/guide/troubleshooting.md:70-83):
+        # roughly 34 -> 2 bytes per token per hidden unit per layer of live activations, for one extra forward per block.
+        self.activation_checkpointing = False
         if init:
             self.init_weights()
+
+    def enable_activation_checkpointing(self, enabled: bool = True) -> "Transformer":
+        self.activation_checkpointing = enabled
+        return self
 
     def _precompute_freqs(self) -> torch.Tensor:
         a = self.model_args
@@ -236,8 +244,12 @@ class Transformer(nn.Module):
                              f"({self.freqs_cis.shape[0]} positions = 2 x max_seq_len); build the model with a larger max_seq_len")
         if self.freqs_cis.device != h.device:
             self.freqs_cis = self.freqs_cis.to(h.device)
+        ckpt = self.activation_checkpointing and torch.is_grad_enabled()
         for layer in self.layers:
-            h = layer(h, self.freqs_cis, pos_offset)
+            if ckpt:   # keep only the block input; the block is re-run during backward
+                h = torch.utils.checkpoint.checkpoint(layer, h, self.freqs_cis, pos_offset, use_reentrant=False)
+            else:
+                h = layer(h, self.freqs_cis, pos_offset)
         h = self.norm(h)
         return self.output(h).float()
 

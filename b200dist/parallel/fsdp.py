@@ -226,13 +226,16 @@ class FSDP(nn.Module):
 
     def _make_pre_forward(self, u: _Unit):
         def hook(mod, args):
-            self._unshard(u, self._next_unit(u, +1))
+            # during backward this is a recomputation (activation checkpointing): the next unit needed is the PREVIOUS one
+            self._unshard(u, self._next_unit(u, -1 if self._in_backward else +1))
         return hook
 
     def _make_post_forward(self, u: _Unit):
         def hook(mod, args, out):
             # the last block is needed again immediately by backward: keep it (standard FSDP trick)
             last = torch.is_grad_enabled() and self.units and u is self.units[-1]
+            if self._in_backward:
+                return   # recomputed forward: the unit's backward runs next, it is freed after its gradients are reduced
             if self.reshard_after_forward and not last:
                 self._free(u)
         return hook

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--fused", action="store_true")
     ap.add_argument("--no-sp", action="store_true")
+    ap.add_argument("--activation-checkpointing", action="store_true", help="recompute each block in backward (b200dist arm)")
     ap.add_argument("--vocab-parallel-loss", action="store_true", help="keep the logits vocabulary-sharded (no [M, V] all-gather)")
     ap.add_argument("--impl", default="b200dist", choices=["b200dist", "reference"])
     ap.add_argument("--verbose", action="store_true", help="print the loss of every step (adds a sync per step)")
@@ -67,6 +68,8 @@ def main():
         tp_comm = mesh["tp"].communicator()
         if a.fused:
             enable_fused_tp(model, mesh["tp"])
+        if a.activation_checkpointing:
+            model.enable_activation_checkpointing()
         torch.cuda.empty_cache()
         model = FSDP(model, process_group=mesh.get_group("dp"))
         opt = model.build_optimizer("adamw", lr=3e-4, betas=(0.9, 0.95), weight_decay=0.1)

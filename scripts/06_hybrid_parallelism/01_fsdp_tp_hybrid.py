@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--lr", type=float, default=3e-3)
     ap.add_argument("--no-sp", action="store_true")
+    ap.add_argument("--activation-checkpointing", action="store_true")
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float32"])
     a = ap.parse_args()
     rank, world, local, device = setup()
@@ -44,6 +45,8 @@ def main():
     torch.manual_seed(0)
     model = Transformer.from_name(a.model, device=device, dtype=dtype, max_seq_len=max(a.seq_len, 256))
     llama_tp_plan(model, mesh["tp"], sequence_parallel=not a.no_sp)
+    if a.activation_checkpointing:
+        model.enable_activation_checkpointing()
     model = FSDP(model, process_group=mesh.get_group("dp"))
     opt = model.build_optimizer("adamw", lr=a.lr)
     timer = StepTimer(device)

@@ -133,3 +133,43 @@ def test_fsdp_matches_single_process(tmp_path):
 def test_fsdp_no_reshard(tmp_path):
     ref = _single_process_reference(2, 2, "adamw")
     run_distributed(_fsdp_worker, 2, args=(2, ref, False, str(tmp_path)))
+
+
+def _fsdp_ckpt_worker(rank, world, steps, ref_sd):
+    from b200dist import ops
+    from b200dist.parallel import FSDP
+
+    model = _toy_llama().enable_activation_checkpointing()
+    fsdp = FSDP(model, reshard_after_forward=True)
+    gathers = []
+    orig = fsdp._issue_gather
+    fsdp._issue_gather = lambda u: (gathers.append(u.name) if (u.sharded and world > 1) else None, orig(u))[1]
+    opt = fsdp.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    for t in _batches(steps):
+        shard = t.chunk(world)[rank]
+        opt.zero_grad()
+        ops.cross_entropy(fsdp(shard[:, :-1]), shard[:, 1:]).backward()
+        opt.step()
+    sd = fsdp.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in sd.items():
+        if not v.is_complex():
+            assert torch.allclose(v, ref_sd[k], atol=3e-5, rtol=1e-4), f"rank {rank} {k}: {(v - ref_sd[k]).abs().max()}"
+    # recomputation must not add parameter gathers: per step at most two per block unit (forward + backward)
+    per_unit = {}
+    for n in gathers:
+        per_unit[n] = per_unit.get(n, 0) + 1
+    assert max(per_unit.values()) <= 2 * steps, per_unit
+
+
+def test_activation_checkpointing_single_process_and_fsdp():
+    from b200dist import ops
+
+    # single process: identical gradients with and without recomputation
+    t = _batches(1)[0]
+    a, b = _toy_llama(), _toy_llama().enable_activation_checkpointing()
+    ops.cross_entropy(a(t[:, :-1]), t[:, 1:]).backward()
+    ops.cross_entropy(b(t[:, :-1]), t[:, 1:]).backward()
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-6), n
+    ref = _single_process_reference(2, 2, "adamw")
+    run_distributed(_fsdp_ckpt_worker, 2, args=(2, ref))
