@@ -32,6 +32,8 @@ CPU tensors (gloo unit tests) run the same control flow on torch.distributed col
 """
 from __future__ import annotations
 
+import contextlib
+
 import math
 from typing import Dict, List, Optional
 
@@ -275,10 +277,11 @@ class FSDP(nn.Module):
     def _make_sink(self, u: _Unit, slot: int):
         """Weight-gradient sink: the wgrad GEMM writes dW directly into the unit's symmetric staging slot."""
         def sink(dy2d, x2d) -> bool:
-            if not self.require_backward_grad_sync:
-                return False  # gradient accumulation: let autograd accumulate locally
+            p = u.params[slot]
+            if not self.require_backward_grad_sync or p.grad is not None:
+                return False  # gradient accumulation (no_sync micro-steps, or their final step): autograd accumulates in p.grad
             self._begin_backward()
-            p, o = u.params[slot], u.offsets[slot]
+            o = u.offsets[slot]
             view = self._claim_stage(u).tensor(self.dtype, 0, u.total)[o:o + p.numel()].view(p.shape)
             N.gemm(dy2d, x2d, a_mn=True, b_mn=True, out=view, accumulate=u.sink_written[slot])
             u.sink_written[slot] = True
@@ -293,6 +296,8 @@ class FSDP(nn.Module):
     def _reduce_unit(self, u: _Unit) -> None:
         u.pending_grads = -1  # launched
         if not self.require_backward_grad_sync:
+            if u is not self.root_unit and self.reshard_after_forward:
+                self._free(u)   # accumulation micro-step: gradients stay in p.grad, the gathered weights can go
             return
         hp = self._opt.hp if self._opt is not None else None
         t = self._step_t + 1
@@ -382,6 +387,18 @@ class FSDP(nn.Module):
         if self.root_unit is not None and self.world > 1:
             self._free(self.root_unit)
         self._in_backward = False
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Gradient accumulation: backward passes inside the block keep their (unsharded) gradients in ``p.grad`` and skip
+        the reduce-scatter / optimizer fusion; the first backward outside reduces the accumulated sum (the reference only
+        describes accumulation, docs/guide/troubleshooting.md:70-83; torch FSDP offers the same context manager)."""
+        prev = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = prev
 
     # ------------------------------------------------------------------ forward
     def forward(self, *args, **kwargs):

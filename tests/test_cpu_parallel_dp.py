@@ -173,3 +173,28 @@ def test_activation_checkpointing_single_process_and_fsdp():
         assert torch.allclose(p.grad, q.grad, atol=1e-6), n
     ref = _single_process_reference(2, 2, "adamw")
     run_distributed(_fsdp_ckpt_worker, 2, args=(2, ref))
+
+
+def _fsdp_accum_worker(rank, world, ref_sd):
+    from b200dist import ops
+    from b200dist.parallel import FSDP
+
+    fsdp = FSDP(_toy_llama())
+    opt = fsdp.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    for t in _batches(2):
+        shard = t.chunk(world)[rank]
+        halves = shard.chunk(2)                       # two micro-steps per optimizer step
+        opt.zero_grad()
+        with fsdp.no_sync():
+            (ops.cross_entropy(fsdp(halves[0][:, :-1]), halves[0][:, 1:]) / 2).backward()
+        (ops.cross_entropy(fsdp(halves[1][:, :-1]), halves[1][:, 1:]) / 2).backward()
+        opt.step()
+    sd = fsdp.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in sd.items():
+        if not v.is_complex():
+            assert torch.allclose(v, ref_sd[k], atol=3e-5, rtol=1e-4), f"rank {rank} {k}: {(v - ref_sd[k]).abs().max()}"
+
+
+def test_fsdp_gradient_accumulation_no_sync():
+    ref = _single_process_reference(2, 2, "adamw")
+    run_distributed(_fsdp_accum_worker, 2, args=(ref,))

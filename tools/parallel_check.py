@@ -83,6 +83,21 @@ def main():
         ok &= good
         if rank == 0:
             print(f"[{'PASS' if good else 'FAIL'}] FSDP reshard={reshard} final weights: max diff {err:.4g}", flush=True)
+    # ---------------- FSDP + activation checkpointing + gradient accumulation (no_sync micro-steps) ----------------
+    m = toy().to(dev).to(torch.bfloat16).enable_activation_checkpointing()
+    f = FSDP(m)
+    opt = f.build_optimizer("adamw", lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    losses = []
+    for t in data:
+        t = t.chunk(world)[rank].to(dev)
+        h0, h1 = t.chunk(2)
+        opt.zero_grad()
+        with f.no_sync():
+            l0 = ops.cross_entropy(f(h0[:, :-1]), h0[:, 1:]) / 2; l0.backward()
+        l1 = ops.cross_entropy(f(h1[:, :-1]), h1[:, 1:]) / 2; l1.backward()
+        opt.step()
+        lt = (l0 + l1).detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+    report("FSDP + activation checkpointing + 2 accumulation micro-steps loss curve", losses, ref_losses, 0.02)
     # ---------------- DDP (bucketed all-reduce over peer memory) ----------------
     ref_m2, ref_losses2 = single("sgd")
     m = toy().to(dev).to(torch.bfloat16)
