@@ -62,6 +62,9 @@ def _im2col(xh: torch.Tensor, KH, KW, stride, pad, Ho, Wo, Cp) -> torch.Tensor:
 
 
 _KEEP_COL_BYTES = int(os.environ.get("B200DIST_CONV_KEEP_COL_MB", "2048")) << 20   # per conv; 0 disables
+# implicit-GEMM path (stride-1 K x K convs with C % 64 == 0): forward and input-gradient read the activation through a 4-D
+# tensor map, no patch matrix; the weight gradient still builds one (in backward).  B200DIST_CONV_IGEMM=0 disables.
+_IGEMM = os.environ.get("B200DIST_CONV_IGEMM", "1") not in ("", "0")
 
 
 class _Conv2dFn(Function):
@@ -73,9 +76,19 @@ class _Conv2dFn(Function):
         Ho, Wo = _conv_geom(H, W, KH, KW, stride, pad)
         Cp = (Cc + 7) // 8 * 8
         direct = KH == 1 and KW == 1 and stride == 1 and pad == 0 and Cp == Cc
+        out_dtype = torch.float32 if x.dtype == torch.float32 else _BF16
+        igemm = (_IGEMM and not direct and stride == 1 and Cc % 64 == 0 and K % 8 == 0 and out_dtype == _BF16
+                 and Ho > 0 and Wo > 0)
+        if igemm:
+            y = N.conv2d_igemm(xh.contiguous(), _w_matrix(w, Cc), KH, KW, pad,
+                               bias=bias.to(_BF16) if bias is not None else None)
+            ctx.save_for_backward(xh, w, None)
+            ctx.geom = (stride, pad, Ho, Wo, Cp, direct, x.dtype, bias is not None, K)
+            ctx.igemm = True
+            return _nchw_view(y)
+        ctx.igemm = False
         a = xh.reshape(Nn * H * W, Cc) if direct else _im2col(xh, KH, KW, stride, pad, Ho, Wo, Cp)
         wm = _w_matrix(w, Cp)
-        out_dtype = torch.float32 if x.dtype == torch.float32 else _BF16
         Kp = (K + 7) // 8 * 8
         if Kp != K:  # GEMM N must be a multiple of 8 (e.g. 65 output channels): pad, then slice
             wm = F.pad(wm, (0, 0, 0, Kp - K))
@@ -102,7 +115,12 @@ class _Conv2dFn(Function):
         wm = _w_matrix(w, Cp)
         if Kp != K:
             wm = F.pad(wm, (0, 0, 0, Kp - K))
-        if ctx.needs_input_grad[0]:
+        if ctx.needs_input_grad[0] and ctx.igemm and K % 64 == 0 and Cc % 8 == 0:
+            # input gradient = stride-1 conv of dY with the spatially flipped, channel-transposed filter, pad' = K - 1 - pad
+            wflip = w.flip(2, 3).permute(1, 2, 3, 0).reshape(Cc, KH * KW * K).to(_BF16).contiguous()
+            dxh = N.conv2d_igemm(dyh.view(Nn, Ho, Wo, K), wflip, KH, KW, KH - 1 - pad)
+            dx = _nchw_view(dxh).to(x_dtype)
+        elif ctx.needs_input_grad[0]:
             dcol = N.gemm(dyh, wm, b_mn=True, out_dtype=_BF16)  # [rows, KH*KW*Cp]
             if direct:
                 dxh = dcol.view(Nn, H, W, Cc)

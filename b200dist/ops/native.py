@@ -291,3 +291,16 @@ def adamw_step(p, g, m, v, *, lr, beta1, beta2, eps, wd, step, grad_scale=1.0, p
 def sgd_step(p, g, buf, *, lr, momentum, wd, first_step, grad_scale=1.0, p_lowp=None):
     L.call("sgd", L.ptr(p), I(L.dtype_code(p.dtype)), L.ptr(p_lowp), L.ptr(g), I(L.dtype_code(g.dtype)), L.ptr(buf),
            LL(p.numel()), F(lr), F(momentum), F(wd), F(grad_scale), I(int(first_step)), _s())
+
+
+def conv2d_igemm(x_nhwc, wmat, KH: int, KW: int, pad: int, bias=None, residual=None, act: int = 0):
+    """Implicit-GEMM stride-1 convolution: x [N, H, W, C] bf16 contiguous, wmat [Cout, KH * KW * C] bf16 -> [N, Ho, Wo, Cout].
+    C % 64 == 0 and Cout % 8 == 0 (see csrc/gemm_tcgen05.cu, launch_conv_igemm)."""
+    Nn, H, W, Cc = x_nhwc.shape
+    Cout = wmat.shape[0]
+    assert x_nhwc.is_contiguous() and wmat.is_contiguous() and wmat.shape[1] == KH * KW * Cc
+    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    out = torch.empty((Nn, Ho, Wo, Cout), dtype=torch.bfloat16, device=x_nhwc.device)
+    L.call("conv2d_igemm_bf16", L.ptr(x_nhwc), L.ptr(wmat), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH), I(KW),
+           I(pad), L.ptr(bias), L.ptr(residual), I(act), _s())
+    return out

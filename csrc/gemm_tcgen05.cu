@@ -59,6 +59,17 @@ struct FusedParams {
   void* d_ptrs[8];              // rank p's staging buffer [world, d_chunk_rows, N]
   long long d_chunk_rows;       // rows owned by each rank (0 = scatter disabled)
   int m_rot;                    // m-block rotation so that tiles start at a given chunk
+  // ---- implicit-GEMM convolution (A operand = NHWC activation read through a 4-D tensor map) ----
+  //   Stride-1 conv as a GEMM whose M rows are OUTPUT pixels and whose K index is (kh, kw, c): k-block (tap, 64-channel
+  //   slice) of an m-block covering output pixels [n0.., h0.., w0..] is the activation box at (h0 + kh - pad,
+  //   w0 + kw - pad): one shifted TMA box load per k-block, out-of-range coordinates zero-filled by the TMA unit
+  //   (= the conv padding).  No patch matrix is ever written.  CG = 1 only.
+  int conv_on;
+  int c_Ho, c_Wo, c_N;          // output extent
+  int c_hbox, c_wbox, c_nbox;   // output-pixel box of one m-block (c_nbox * c_hbox * c_wbox <= 128 rows)
+  int c_tiles_h, c_tiles_w;
+  int c_KW, c_pad, c_cblocks;   // kernel width, padding, C / 64
+  int c_box_bytes;              // bytes one box load delivers (the rest of the 128-row A stage stays stale: rows unused)
 };
 
 constexpr int kBlockM = 128;   // rows per CTA (UMMA M = 128 * CTA_GROUP)
@@ -277,9 +288,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint32_t sb = sa + Cfg::kABytes;
           const uint32_t fb = full0 + 8u * stage;
-          if (is_leader) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
+          if constexpr (FUSED && CG == 1) {
+            mbar_expect_tx(full_bar(stage), fp.conv_on ? (uint32_t)(fp.c_box_bytes + Cfg::kBBytes) : (uint32_t)Cfg::kStageBytes);
+          } else {
+            if (is_leader) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
+          }
           const int k0 = kb * kBlockK;
-          if constexpr (!A_MN) {
+          bool a_done = false;
+          if constexpr (FUSED && CG == 1 && !A_MN) {
+            if (fp.conv_on) {
+              const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
+              const int tn = m_blk / (fp.c_tiles_w * fp.c_tiles_h);
+              const int tap = kb / fp.c_cblocks, cb = kb - tap * fp.c_cblocks;
+              const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
+              tma_load_4d(sa, &tmap_a, fb, cb * 64, tw * fp.c_wbox + kw - fp.c_pad, th * fp.c_hbox + kh - fp.c_pad,
+                          tn * fp.c_nbox);
+              a_done = true;
+            }
+          }
+          if (a_done) {
+          } else if constexpr (!A_MN) {
             if constexpr (CG == 2) tma_load_2d_2sm(sa, &tmap_a, fb, k0, m0);
             else tma_load_2d(sa, &tmap_a, fb, k0, m0);
           } else {
@@ -350,13 +378,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int m_blk, n_blk;
       tile_coords(tile / p.splits, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
       if constexpr (FUSED) m_blk = (m_blk + fp.m_rot) % p.num_m_blocks;
-      const int row = (m_blk * CG + (int)cta_rank) * kBlockM + quarter * 32 + lane;
+      long long row = (m_blk * CG + (int)cta_rank) * kBlockM + quarter * 32 + lane;
+      bool row_ok = row < p.M;
+      if constexpr (FUSED && CG == 1) {
+        if (fp.conv_on) {   // tile-local row r = (image, h, w) inside the output-pixel box -> NHWC pixel index
+          const int r = quarter * 32 + lane;
+          const int hw = fp.c_hbox * fp.c_wbox;
+          const int in = r / hw, rem = r - in * hw, hh = rem / fp.c_wbox, ww = rem - hh * fp.c_wbox;
+          const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
+          const int tn = m_blk / (fp.c_tiles_w * fp.c_tiles_h);
+          const int n = tn * fp.c_nbox + in, h = th * fp.c_hbox + hh, w = tw * fp.c_wbox + ww;
+          row_ok = in < fp.c_nbox && n < fp.c_N && h < fp.c_Ho && w < fp.c_Wo;
+          row = ((long long)n * fp.c_Ho + h) * fp.c_Wo + w;
+        }
+      }
       const int n_tile0 = n_blk * BN;
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN;
-      const bool row_ok = row < p.M;
-      OutT* drow = reinterpret_cast<OutT*>(p.D) + (long long)row * p.ldd;
+      OutT* drow = reinterpret_cast<OutT*>(p.D) + row * p.ldd;
       if constexpr (FUSED) {
         if (fp.d_chunk_rows > 0 && row_ok) {   // GEMM -> reduce-scatter: this row belongs to rank `owner`
           const long long owner = row / fp.d_chunk_rows;
@@ -364,7 +404,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                  ((long long)fp.rank * fp.d_chunk_rows + (row - owner * fp.d_chunk_rows)) * p.ldd;
         }
       }
-      const __nv_bfloat16* rrow = p.residual ? p.residual + (long long)row * p.ldr : nullptr;
+      const __nv_bfloat16* rrow = p.residual ? p.residual + row * p.ldr : nullptr;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int n0 = n_tile0 + c * 32;
@@ -671,6 +711,76 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
   return B200_OK;
 }
 
+// Implicit-GEMM convolution launcher (stride 1): out[n, ho, wo, :] = sum_{kh, kw, c} x[n, ho + kh - pad, wo + kw - pad, c] *
+// wmat[:, (kh, kw, c)]  (+ bias, + residual, activation) with x NHWC bf16 and wmat [Cout, KH * KW * C] K-major.
+static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nimg, int H, int W, int C, int Cout, int KH,
+                             int KW, int pad, const void* bias, const void* residual, int act, cudaStream_t stream) {
+  constexpr int CG = 1, BN = 128;
+  using Cfg = GemmCfg<CG, BN>;
+  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  if (Ho <= 0 || Wo <= 0 || (C % 64) || (Cout % 8) || Nimg <= 0) {
+    b200_set_error("conv_igemm: needs C %% 64 == 0, Cout %% 8 == 0 and a non-empty output (C=%d Cout=%d Ho=%d Wo=%d)", C, Cout, Ho, Wo);
+    return B200_ERR_SHAPE;
+  }
+  FusedParams fp = {};
+  fp.conv_on = 1;
+  fp.c_Ho = Ho; fp.c_Wo = Wo; fp.c_N = Nimg;
+  fp.c_wbox = Wo < kBlockM ? Wo : kBlockM;
+  fp.c_hbox = kBlockM / fp.c_wbox; if (fp.c_hbox > Ho) fp.c_hbox = Ho; if (fp.c_hbox < 1) fp.c_hbox = 1;
+  fp.c_nbox = 1;
+  if (fp.c_hbox == Ho && fp.c_wbox == Wo) {
+    fp.c_nbox = kBlockM / (Ho * Wo); if (fp.c_nbox > Nimg) fp.c_nbox = Nimg; if (fp.c_nbox < 1) fp.c_nbox = 1;
+  }
+  fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
+  fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
+  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64;
+  fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
+  GemmParams p = {};
+  p.M = Nimg * Ho * Wo; p.N = Cout; p.K = KH * KW * C;
+  p.D = out; p.ldd = Cout;
+  p.bias = reinterpret_cast<const __nv_bfloat16*>(bias);
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(residual); p.ldr = Cout;
+  p.alpha = 1.f; p.act = act;
+  p.num_m_blocks = ceil_div(Nimg, fp.c_nbox) * fp.c_tiles_h * fp.c_tiles_w;
+  p.num_n_blocks = ceil_div(Cout, BN);
+  p.num_k_blocks = p.K / kBlockK;
+  p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  p.splits = 1; p.kb_per_split = p.num_k_blocks;
+  CUtensorMap ta, tb;
+  {
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
+    const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
+    if (int rc = b200_make_tmap(&ta, x, 2, 4, dims, str, box, 1)) return rc;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N};
+    const uint64_t str[1] = {(uint64_t)p.K * 2};
+    const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)Cfg::kLoadN};
+    if (int rc = b200_make_tmap(&tb, wmat, 2, 2, dims, str, box, 1)) return rc;
+  }
+  auto kern = gemm_tcgen05_kernel<CG, BN, false, false, __nv_bfloat16, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int ctas = b200_sm_count();
+  if (ctas > p.num_tiles) ctas = p.num_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  return B200_OK;
+}
+
 // Wave-quantisation-aware choice between the three tile configurations.
 static int pick_config(int M, int N, int sms) {
   auto eff = [&](int tm, int tn, int units) {
@@ -810,4 +920,15 @@ B200_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* 
   fp.m_rot = ((rank + 1) % world) * blocks_per_chunk;  // first the neighbour's rows, own rows last
   if (b_mn_major) return launch_gemm_fused<true>(A, B, p, lda, ldb, fp, stream);
   return launch_gemm_fused<false>(A, B, p, lda, ldb, fp, stream);
+}
+
+// Implicit-GEMM convolution, stride 1, NHWC bf16 (conv2d fprop, and dgrad when called with dY and
+// the flipped / transposed filter matrix and pad' = K - 1 - pad).  x [N, H, W, C], wmat [Cout, KH * KW * C],
+// out [N, Ho, Wo, Cout]; bias [Cout] and residual [N, Ho, Wo, Cout] optional; act as in b200_gemm_bf16.
+// C % 64 == 0, Cout % 8 == 0.  Replaces the cuDNN convolution behind torchvision's ResNet (scripts/main.py:249) without
+// materialising the im2col patch matrix.
+B200_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
+                                    int KH, int KW, int pad, const void* bias, const void* residual, int act,
+                                    cudaStream_t stream) {
+  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, bias, residual, act, stream);
 }

@@ -52,6 +52,13 @@ B200DIST_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* con
                                long long lda, long long ldb, int b_mn_major, const void* residual, long long ldr,
                                int world, int rank, cudaStream_t stream);
 
+/* implicit-GEMM convolution (stride 1, NHWC bf16): the A operand is read straight from the activation through a 4-D
+ * tensor map, one shifted TMA box per (filter tap, 64-channel slice); also serves dgrad (dY, flipped filter, pad' = K-1-pad).
+ * replaces cuDNN behind torchvision ResNet / SimpleUNet convolutions: scripts/main.py:249, multinode_ddp_unet.py:190-198 */
+B200DIST_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
+                                    int KH, int KW, int pad, const void* bias, const void* residual, int act,
+                                    cudaStream_t stream);
+
 /* ---- Attention (tcgen05 flash attention) ----
  * replaces F.scaled_dot_product_attention: fsdp_tp/llama2_model.py:218-223; explicit softmax attention: scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122 */
 B200DIST_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, void* O, float* LSE,

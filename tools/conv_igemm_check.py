@@ -1,0 +1,65 @@
+"""Numerics + timing of the implicit-GEMM convolution (fprop and dgrad) against F.conv2d and the im2col path.
+    python tools/conv_igemm_check.py"""
+import sys
+from pathlib import Path
+
+import torch
+import torch.nn.functional as F
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from b200dist.ops import conv as cops  # noqa: E402
+from b200dist.ops import native as N  # noqa: E402
+
+dev = torch.device("cuda", 0)
+torch.manual_seed(0)
+fails = 0
+
+
+def ev(fn, it=10):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(it):
+        fn()
+    e.record(); torch.cuda.synchronize()
+    return s.elapsed_time(e) / it * 1e3
+
+
+for (B, C, H, W, K, ks, pad) in [(2, 64, 56, 56, 64, 3, 1), (3, 128, 28, 28, 128, 3, 1), (2, 256, 14, 14, 256, 3, 1),
+                                 (5, 512, 7, 7, 512, 3, 1), (2, 256, 56, 56, 64, 1, 0), (2, 64, 45, 90, 128, 3, 1),
+                                 (1, 64, 20, 181, 72, 3, 1), (2, 64, 9, 9, 64, 3, 0), (256, 64, 56, 56, 64, 3, 1)]:
+    x = torch.randn(B, C, H, W, device=dev).bfloat16()
+    w = (torch.randn(K, C, ks, ks, device=dev) * (1.0 / (C * ks * ks) ** 0.5)).bfloat16()
+    xh = x.permute(0, 2, 3, 1).contiguous()
+    wm = w.permute(0, 2, 3, 1).reshape(K, ks * ks * C).contiguous()
+    y = N.conv2d_igemm(xh, wm, ks, ks, pad)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float(), w.float(), padding=pad).permute(0, 2, 3, 1)
+    err = float((y.float() - ref).abs().max()); scale = float(ref.abs().max())
+    ok = err <= 0.02 * scale + 0.02
+    fails += (not ok)
+    msg = f"[{'PASS' if ok else 'FAIL'}] igemm fprop B{B} C{C} {H}x{W} -> K{K} k{ks} p{pad}: max_err={err:.4g} (|ref| {scale:.3g})"
+    # dgrad through the same kernel: dY [B, Ho, Wo, K] with the flipped filter, pad' = ks - 1 - pad
+    if K % 64 == 0 and C % 8 == 0:
+        dy = torch.randn_like(ref).bfloat16().contiguous()
+        wflip = w.flip(2, 3).permute(1, 2, 3, 0).reshape(C, ks * ks * K).contiguous()
+        dx = N.conv2d_igemm(dy, wflip, ks, ks, ks - 1 - pad)
+        torch.cuda.synchronize()
+        xr = x.float().requires_grad_(True)
+        F.conv2d(xr, w.float(), padding=pad).backward(dy.float().permute(0, 3, 1, 2))
+        dref = xr.grad.permute(0, 2, 3, 1)
+        e2 = float((dx.float() - dref).abs().max()); s2 = float(dref.abs().max())
+        ok2 = e2 <= 0.02 * s2 + 0.02 and dx.shape == dref.shape
+        fails += (not ok2)
+        msg += f" | dgrad max_err={e2:.4g} (|ref| {s2:.3g}) {'PASS' if ok2 else 'FAIL'}"
+    if B >= 128:
+        t_ig = ev(lambda: N.conv2d_igemm(xh, wm, ks, ks, pad))
+        xc = x.contiguous(memory_format=torch.channels_last)
+        t_old = ev(lambda: cops.conv2d(xc, w, None, 1, pad))
+        t_cudnn = ev(lambda: F.conv2d(xc, w, padding=pad))
+        msg += f" | time igemm {t_ig:.0f} us, im2col+GEMM {t_old:.0f} us, cuDNN {t_cudnn:.0f} us"
+    print(msg, flush=True)
+print(f"== conv igemm: failures {fails}")
+sys.exit(1 if fails else 0)
