@@ -65,6 +65,7 @@ _KEEP_COL_BYTES = int(os.environ.get("B200DIST_CONV_KEEP_COL_MB", "2048")) << 20
 # implicit-GEMM path (stride-1 K x K convs with C % 64 == 0): forward and input-gradient read the activation through a 4-D
 # tensor map, no patch matrix; the weight gradient still builds one (in backward).  B200DIST_CONV_IGEMM=0 disables.
 _IGEMM = os.environ.get("B200DIST_CONV_IGEMM", "1") not in ("", "0")
+_IGEMM_WGRAD = os.environ.get("B200DIST_CONV_IGEMM_WGRAD", "1") not in ("", "0")   # implicit-GEMM weight gradient
 
 
 class _Conv2dFn(Function):
@@ -129,7 +130,10 @@ class _Conv2dFn(Function):
                 L.call("col2im", L.ptr(dcol), L.ptr(dxh), I(Nn), I(H), I(W), I(Cc), I(Cp), I(KH), I(KW), I(stride), I(pad),
                        I(Ho), I(Wo), I(0), _s())
             dx = _nchw_view(dxh).to(x_dtype)
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and ctx.igemm and _IGEMM_WGRAD and Nn * Ho * Wo >= 128:
+            dwm = N.conv2d_igemm_wgrad(xh.contiguous(), dyh.view(Nn, Ho, Wo, K), KH, KW, pad)     # [K, KH*KW*C] fp32
+            dw = dwm.view(K, KH, KW, Cc).permute(0, 3, 1, 2).to(w.dtype)
+        elif ctx.needs_input_grad[1]:
             a = xh.reshape(Nn * H * W, Cc) if direct else (col if col is not None else
                                                             _im2col(xh, KH, KW, stride, pad, Ho, Wo, Cp))
             dwm = N.gemm(dyh, a, a_mn=True, b_mn=True, out_dtype=torch.float32)[:K]  # [K, KH*KW*Cp]

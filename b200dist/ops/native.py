@@ -304,3 +304,16 @@ def conv2d_igemm(x_nhwc, wmat, KH: int, KW: int, pad: int, bias=None, residual=N
     L.call("conv2d_igemm_bf16", L.ptr(x_nhwc), L.ptr(wmat), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH), I(KW),
            I(pad), L.ptr(bias), L.ptr(residual), I(act), _s())
     return out
+
+
+def conv2d_igemm_wgrad(x_nhwc, dy_nhwc, KH: int, KW: int, pad: int, out=None, accumulate: bool = False):
+    """Implicit-GEMM weight gradient of a stride-1 convolution: x [N, H, W, C], dy [N, Ho, Wo, Cout] bf16 contiguous ->
+    fp32 [Cout, KH * KW * C] in (kh, kw, c) column order.  C % 64 == 0, Cout % 8 == 0."""
+    Nn, H, W, Cc = x_nhwc.shape
+    Cout = dy_nhwc.shape[-1]
+    assert x_nhwc.is_contiguous() and dy_nhwc.is_contiguous()
+    if out is None:
+        out = torch.empty((Cout, KH * KW * Cc), dtype=torch.float32, device=x_nhwc.device)
+    L.call("conv2d_igemm_wgrad", L.ptr(x_nhwc), L.ptr(dy_nhwc), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH), I(KW),
+           I(pad), I(int(accumulate)), _s())
+    return out

@@ -64,7 +64,12 @@ struct FusedParams {
   //   slice) of an m-block covering output pixels [n0.., h0.., w0..] is the activation box at (h0 + kh - pad,
   //   w0 + kw - pad): one shifted TMA box load per k-block, out-of-range coordinates zero-filled by the TMA unit
   //   (= the conv padding).  No patch matrix is ever written.  CG = 1 only.
+  //   conv_on == 2 is the WEIGHT GRADIENT: dW[co, (kh, kw, c)] = sum over output pixels of dY[pixel, co] * X[pixel + tap, c].
+  //   M = Cout, N = KH * KW * C, K = output pixels; k-block = a box of <= 64 output pixels; A (MN-major) = that box of dY
+  //   (two 64-channel slabs), B (MN-major) = per 64-column slab the box of X shifted by the slab's tap.  Rows of a stage
+  //   that no box ever writes are zeroed once at kernel start so they contribute nothing.
   int conv_on;
+  int c_C;                      // input channels (weight gradient: column -> (tap, channel))
   int c_Ho, c_Wo, c_N;          // output extent
   int c_hbox, c_wbox, c_nbox;   // output-pixel box of one m-block (c_nbox * c_hbox * c_wbox <= 128 rows)
   int c_tiles_h, c_tiles_w;
@@ -191,6 +196,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     tmem_alloc<CG>(tmem_ptr_addr, Cfg::kTmemCols);
     tmem_relinquish<CG>();
   }
+  if constexpr (FUSED && CG == 1 && A_MN && B_MN) {
+    if (fp.conv_on == 2) {   // zero every operand stage: rows beyond a pixel box are never written by TMA
+      uint8_t* base = smem_raw + (smem_base - smem_u32(smem_raw));
+      uint4* z = reinterpret_cast<uint4*>(base);
+      for (int i = threadIdx.x; i < kStages * Cfg::kStageBytes / 16; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+      fence_proxy_async_all();
+    }
+  }
   tc_fence_before();
   if constexpr (CG == 2) cluster_sync(); else __syncthreads();
   tc_fence_after();
@@ -289,14 +302,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           const uint32_t sb = sa + Cfg::kABytes;
           const uint32_t fb = full0 + 8u * stage;
           if constexpr (FUSED && CG == 1) {
-            mbar_expect_tx(full_bar(stage), fp.conv_on ? (uint32_t)(fp.c_box_bytes + Cfg::kBBytes) : (uint32_t)Cfg::kStageBytes);
+            uint32_t tx = (uint32_t)Cfg::kStageBytes;
+            if (fp.conv_on == 1) tx = (uint32_t)(fp.c_box_bytes + Cfg::kBBytes);
+            else if (fp.conv_on == 2) tx = (uint32_t)((kBlockM / 64 + kLoadN / 64) * fp.c_box_bytes);
+            mbar_expect_tx(full_bar(stage), tx);
           } else {
             if (is_leader) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
           }
           const int k0 = kb * kBlockK;
           bool a_done = false;
+          if constexpr (FUSED && CG == 1 && A_MN && B_MN) {
+            if (fp.conv_on == 2) {
+              // k-block = box of output pixels (w fastest, then h, then image)
+              const int tw = kb % fp.c_tiles_w, th = (kb / fp.c_tiles_w) % fp.c_tiles_h;
+              const int tn = kb / (fp.c_tiles_w * fp.c_tiles_h);
+              const int pw = tw * fp.c_wbox, ph = th * fp.c_hbox, pn = tn * fp.c_nbox;
+#pragma unroll
+              for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
+#pragma unroll
+              for (int j = 0; j < kLoadN / 64; ++j) {
+                const int col = n0 + j * 64;
+                const int tap = col / fp.c_C, c0 = col - tap * fp.c_C;
+                const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
+                tma_load_4d(sb + j * 8192, &tmap_b, fb, c0, pw + kw - fp.c_pad, ph + kh - fp.c_pad, pn);
+              }
+              if (++stage == kStages) { stage = 0; phase ^= 1u; }
+              continue;
+            }
+          }
           if constexpr (FUSED && CG == 1 && !A_MN) {
-            if (fp.conv_on) {
+            if (fp.conv_on == 1) {
               const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
               const int tn = m_blk / (fp.c_tiles_w * fp.c_tiles_h);
               const int tap = kb / fp.c_cblocks, cb = kb - tap * fp.c_cblocks;
@@ -381,7 +416,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       long long row = (m_blk * CG + (int)cta_rank) * kBlockM + quarter * 32 + lane;
       bool row_ok = row < p.M;
       if constexpr (FUSED && CG == 1) {
-        if (fp.conv_on) {   // tile-local row r = (image, h, w) inside the output-pixel box -> NHWC pixel index
+        if (fp.conv_on == 1) {   // tile-local row r = (image, h, w) inside the output-pixel box -> NHWC pixel index
           const int r = quarter * 32 + lane;
           const int hw = fp.c_hbox * fp.c_wbox;
           const int in = r / hw, rem = r - in * hw, hh = rem / fp.c_wbox, ww = rem - hh * fp.c_wbox;
@@ -781,6 +816,87 @@ static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nim
   return B200_OK;
 }
 
+// Implicit-GEMM weight gradient (stride 1): dW[co, (kh, kw, c)] (fp32, [Cout, KH*KW*C]) = sum over n, ho, wo of
+// dY[n, ho, wo, co] * X[n, ho + kh - pad, wo + kw - pad, c].  Split-K over pixel boxes with fp32 red.add.
+static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg, int H, int W, int C, int Cout, int KH,
+                             int KW, int pad, int accumulate, cudaStream_t stream) {
+  constexpr int CG = 1, BN = 128;
+  using Cfg = GemmCfg<CG, BN>;
+  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  if (Ho <= 0 || Wo <= 0 || (C % 64) || (Cout % 8) || Nimg <= 0) {
+    b200_set_error("conv_wgrad: needs C %% 64 == 0, Cout %% 8 == 0 and a non-empty output (C=%d Cout=%d)", C, Cout);
+    return B200_ERR_SHAPE;
+  }
+  FusedParams fp = {};
+  fp.conv_on = 2;
+  fp.c_C = C;
+  fp.c_Ho = Ho; fp.c_Wo = Wo; fp.c_N = Nimg;
+  fp.c_wbox = Wo < kBlockK ? Wo : kBlockK;
+  fp.c_hbox = kBlockK / fp.c_wbox; if (fp.c_hbox > Ho) fp.c_hbox = Ho; if (fp.c_hbox < 1) fp.c_hbox = 1;
+  fp.c_nbox = 1;
+  if (fp.c_hbox == Ho && fp.c_wbox == Wo) {
+    fp.c_nbox = kBlockK / (Ho * Wo); if (fp.c_nbox > Nimg) fp.c_nbox = Nimg; if (fp.c_nbox < 1) fp.c_nbox = 1;
+  }
+  fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
+  fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
+  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64;
+  fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
+  GemmParams p = {};
+  p.M = Cout; p.N = KH * KW * C;
+  p.D = dw; p.ldd = p.N;
+  p.alpha = 1.f; p.accumulate = accumulate;
+  p.num_m_blocks = ceil_div(p.M, kBlockM);
+  p.num_n_blocks = ceil_div(p.N, BN);
+  p.num_k_blocks = ceil_div(Nimg, fp.c_nbox) * fp.c_tiles_h * fp.c_tiles_w;
+  p.K = p.num_k_blocks * kBlockK;
+  p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  // always split-K (the reduction runs over every output pixel): the epilogue accumulates with red.global.add
+  int s = b200_sm_count() / p.num_tiles; if (s < 2) s = 2;
+  const int max_by_k = p.num_k_blocks / 4 > 0 ? p.num_k_blocks / 4 : 1;
+  if (s > max_by_k) s = max_by_k;
+  if (s < 2) s = 2;                      // splits > 1 selects the red.add epilogue (correct for any split count >= 2)
+  if (s > p.num_k_blocks) s = p.num_k_blocks;
+  if (s < 2) { b200_set_error("conv_wgrad: fewer than two pixel boxes"); return B200_ERR_UNSUPPORTED; }
+  p.kb_per_split = ceil_div(p.num_k_blocks, s);
+  p.splits = ceil_div(p.num_k_blocks, p.kb_per_split);
+  if (p.splits < 2) { p.kb_per_split = ceil_div(p.num_k_blocks, 2); p.splits = ceil_div(p.num_k_blocks, p.kb_per_split); }
+  if (!accumulate) B200_CUDA_CHECK(cudaMemsetAsync(dw, 0, (size_t)p.M * p.N * 4, stream));
+  p.num_tiles *= p.splits;
+  CUtensorMap ta, tb;
+  {
+    const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)Nimg};
+    const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
+    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
+    if (int rc = b200_make_tmap(&ta, dy, 2, 4, dims, str, box, 1)) return rc;
+  }
+  {
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
+    const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
+    if (int rc = b200_make_tmap(&tb, x, 2, 4, dims, str, box, 1)) return rc;
+  }
+  auto kern = gemm_tcgen05_kernel<CG, BN, true, true, float, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int ctas = b200_sm_count();
+  if (ctas > p.num_tiles) ctas = p.num_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  return B200_OK;
+}
+
 // Wave-quantisation-aware choice between the three tile configurations.
 static int pick_config(int M, int N, int sms) {
   auto eff = [&](int tm, int tn, int units) {
@@ -931,4 +1047,11 @@ B200_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, 
                                     int KH, int KW, int pad, const void* bias, const void* residual, int act,
                                     cudaStream_t stream) {
   return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, bias, residual, act, stream);
+}
+
+// Implicit-GEMM weight gradient of a stride-1 convolution (wgrad): x [N, H, W, C] and
+// dy [N, Ho, Wo, Cout] NHWC bf16 -> dw [Cout, KH * KW * C] fp32 (zeroed first unless accumulate).  C % 64 == 0.
+B200_API int b200_conv2d_igemm_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
+                                     int KH, int KW, int pad, int accumulate, cudaStream_t stream) {
+  return b200::launch_conv_wgrad(x, dy, dw, N, H, W, C, Cout, KH, KW, pad, accumulate, stream);
 }

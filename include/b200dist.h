@@ -58,6 +58,8 @@ B200DIST_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* con
 B200DIST_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
                                     int KH, int KW, int pad, const void* bias, const void* residual, int act,
                                     cudaStream_t stream);
+B200DIST_API int b200_conv2d_igemm_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
+                                     int KH, int KW, int pad, int accumulate, cudaStream_t stream);
 
 /* ---- Attention (tcgen05 flash attention) ----
  * replaces F.scaled_dot_product_attention: fsdp_tp/llama2_model.py:218-223; explicit softmax attention: scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122 */

@@ -54,6 +54,24 @@ for (B, C, H, W, K, ks, pad) in [(2, 64, 56, 56, 64, 3, 1), (3, 128, 28, 28, 128
         ok2 = e2 <= 0.02 * s2 + 0.02 and dx.shape == dref.shape
         fails += (not ok2)
         msg += f" | dgrad max_err={e2:.4g} (|ref| {s2:.3g}) {'PASS' if ok2 else 'FAIL'}"
+    if K % 8 == 0:   # weight gradient through the pixel-box split-K kernel
+        dyw = torch.randn_like(ref).bfloat16().contiguous()
+        dwm = N.conv2d_igemm_wgrad(xh, dyw, ks, ks, pad)
+        torch.cuda.synchronize()
+        wr = w.float().requires_grad_(True)
+        F.conv2d(x.float(), wr, padding=pad).backward(dyw.float().permute(0, 3, 1, 2))
+        wref = wr.grad.permute(0, 2, 3, 1).reshape(K, -1)
+        e3 = float((dwm - wref).abs().max()); s3 = float(wref.abs().max())
+        ok3 = e3 <= 0.02 * s3 + 0.02
+        fails += (not ok3)
+        msg += f" | wgrad max_err={e3:.4g} (|ref| {s3:.3g}) {'PASS' if ok3 else 'FAIL'}"
+        if B >= 128:
+            t_wg = ev(lambda: N.conv2d_igemm_wgrad(xh, dyw, ks, ks, pad))
+            col = cops._im2col(xh, ks, ks, 1, pad, ref.shape[1], ref.shape[2], C)
+            dy2 = dyw.view(-1, K)
+            t_g = ev(lambda: N.gemm(dy2, col, a_mn=True, b_mn=True, out_dtype=torch.float32))
+            t_i = ev(lambda: cops._im2col(xh, ks, ks, 1, pad, ref.shape[1], ref.shape[2], C))
+            msg += f" | wgrad time igemm {t_wg:.0f} us vs GEMM {t_g:.0f} + im2col {t_i:.0f} us"
     if B >= 128:
         t_ig = ev(lambda: N.conv2d_igemm(xh, wm, ks, ks, pad))
         xc = x.contiguous(memory_format=torch.channels_last)
