@@ -36,3 +36,16 @@ def test_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+def test_conv_implicit_gemm_fprop_dgrad_wgrad():
+    """Implicit-GEMM convolution (4-D tensor-map operands) vs F.conv2d in fp32: forward, input gradient (flipped filter)
+    and weight gradient (pixel-box split-K) over ResNet / UNet shapes incl. odd extents; tools/conv_igemm_check.py."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "tools" / "conv_igemm_check.py")], capture_output=True, text=True,
+                       timeout=300, cwd=str(root))
+    assert r.returncode == 0 and "failures 0" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
