@@ -80,10 +80,18 @@ class FSDP(nn.Module):
     def __init__(self, module: nn.Module, process_group=None, units: Optional[List] = None,
                  reshard_after_forward: bool = True, fused_optimizer: bool = True,
                  comm_max_ctas: int = 64, sync_module_states: bool = True, copy_engine_gather: bool = True,
-                 copy_engine_reduce: bool = True):
+                 copy_engine_reduce: bool = True, replicate_group=None):
         super().__init__()
         self.module = module
         self.comm = get_communicator(process_group)
+        # HYBRID_SHARD (the reference only tabulates it, docs/guide/05_fully_sharded_fsdp.md:114-132): shard inside
+        # ``process_group``, replicate across ``replicate_group``.  Each shard's reduced gradient is averaged over the
+        # replicas before the optimizer step, which therefore runs unfused (reduce-scatter, all-reduce, then AdamW).
+        self.replicate_comm = get_communicator(replicate_group) if replicate_group is not None else None
+        if self.replicate_comm is not None and self.replicate_comm.world > 1:
+            fused_optimizer = False
+        else:
+            self.replicate_comm = None
         self.world, self.rank = self.comm.world, self.comm.rank
         self.native = self.comm.native and next(module.parameters()).is_cuda
         self.reshard_after_forward = reshard_after_forward and self.world > 1
@@ -121,6 +129,10 @@ class FSDP(nn.Module):
         self.exec_units: List[_Unit] = ([self.root_unit] if self.root_unit else []) + self.units
         for i, u in enumerate(self.exec_units):
             u.index = i
+        if sync_module_states and self.replicate_comm is not None:
+            for u in self.exec_units:   # all replicas start from replica 0's weights
+                for p in u.params:
+                    self.replicate_comm.broadcast(p.data, src=0) if p.data.is_contiguous() else None
         if sync_module_states and self.world > 1:
             for u in self.exec_units:
                 for p in u.params:
@@ -519,6 +531,8 @@ class ShardedOptimizer:
                 continue  # fused path already applied the update
             f._ensure_state(u)
             g = u.grad_shard
+            if f.replicate_comm is not None:   # HYBRID_SHARD: average this shard's gradient over the replicas
+                f.replicate_comm.all_reduce(g, scale=1.0 / f.replicate_comm.world, channel=5)
             if f.world == 1:
                 master, target = u.master, u.full
             else:

@@ -198,3 +198,27 @@ def _fsdp_accum_worker(rank, world, ref_sd):
 def test_fsdp_gradient_accumulation_no_sync():
     ref = _single_process_reference(2, 2, "adamw")
     run_distributed(_fsdp_accum_worker, 2, args=(ref,))
+
+
+def _hybrid_shard_worker(rank, world, ref_sd):
+    from b200dist import ops
+    from b200dist.parallel import FSDP, init_device_mesh
+
+    mesh = init_device_mesh("cpu", (2, 2), ("replicate", "shard"))
+    fsdp = FSDP(_toy_llama(), process_group=mesh.get_group("shard"), replicate_group=mesh.get_group("replicate"))
+    assert fsdp.world == 2 and fsdp.replicate_comm.world == 2 and not fsdp.fused_optimizer
+    opt = fsdp.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    for t in _batches(2):
+        shard = t.chunk(world)[rank]                 # every rank of the 2 x 2 mesh sees a different quarter of the batch
+        opt.zero_grad()
+        ops.cross_entropy(fsdp(shard[:, :-1]), shard[:, 1:]).backward()
+        opt.step()
+    sd = fsdp.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in sd.items():
+        if not v.is_complex():
+            assert torch.allclose(v, ref_sd[k], atol=3e-5, rtol=1e-4), f"rank {rank} {k}: {(v - ref_sd[k]).abs().max()}"
+
+
+def test_fsdp_hybrid_shard_2x2():
+    ref = _single_process_reference(2, 4, "adamw")
+    run_distributed(_hybrid_shard_worker, 4, args=(ref,))
