@@ -583,4 +583,5 @@ class ShardedOptimizer:
             if s.get("m") is not None:
                 f._ensure_state(u)
                 u.m.copy_(s["m"].to(u.m.device))
-                u.v.copy_(s["v"].to(u.v.device))
+                if s.get("v") is not None and u.v is not None:
+                    u.v.copy_(s["v"].to(u.v.device))

@@ -145,12 +145,25 @@ def save_sharded_checkpoint(model, optimizer, epoch: int, directory: str) -> Non
         if rank != 0:
             entries = {}
     payload = {"model": {k: {**e, "tensor": e["tensor"].detach().cpu()} for k, e in entries.items()},
-               "optimizer": optimizer.state_dict() if optimizer is not None else {}, "epoch": epoch}
+               "optimizer": _to_cpu(optimizer.state_dict()) if optimizer is not None else {}, "epoch": epoch,
+               # per-rank generator state: an exact resume replays the same dropout masks / synthetic batches
+               "rng": {"cpu": torch.get_rng_state(),
+                       "cuda": torch.cuda.get_rng_state() if torch.cuda.is_available() else None}}
     torch.save(payload, os.path.join(directory, f"shard_{rank:05d}.pt"))
     if rank == 0:
         with open(os.path.join(directory, "index.json"), "w") as f:
             json.dump({"format": "b200dist-sharded-v1", "world_size": world, "epoch": epoch}, f)
     _barrier()
+
+
+def _to_cpu(obj):
+    if torch.is_tensor(obj):
+        return obj.detach().cpu()
+    if isinstance(obj, dict):
+        return {k: _to_cpu(v) for k, v in obj.items()}
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_to_cpu(v) for v in obj)
+    return obj
 
 
 def _assemble(name: str, pieces: list) -> torch.Tensor:
@@ -200,4 +213,18 @@ def load_sharded_checkpoint(model, optimizer, directory: str) -> int:
         loader(full["model_state_dict"])
     else:
         unwrap_model(model).load_state_dict(full["model_state_dict"])
+    # optimizer + generator state are per rank: restored when the job has the world size the checkpoint was written with
+    with open(os.path.join(directory, "index.json")) as f:
+        saved_world = json.load(f)["world_size"]
+    world = dist.get_world_size() if _is_dist() else 1
+    mine = os.path.join(directory, f"shard_{_rank():05d}.pt")
+    if saved_world == world and os.path.exists(mine):
+        shard = torch.load(mine, map_location="cpu", weights_only=False)
+        if optimizer is not None and shard.get("optimizer"):
+            optimizer.load_state_dict(shard["optimizer"])
+        rng = shard.get("rng") or {}
+        if rng.get("cpu") is not None:
+            torch.set_rng_state(rng["cpu"])
+        if rng.get("cuda") is not None and torch.cuda.is_available():
+            torch.cuda.set_rng_state(rng["cuda"])
     return int(full["epoch"])

@@ -222,3 +222,39 @@ def _hybrid_shard_worker(rank, world, ref_sd):
 def test_fsdp_hybrid_shard_2x2():
     ref = _single_process_reference(2, 4, "adamw")
     run_distributed(_hybrid_shard_worker, 4, args=(ref,))
+
+
+def _fsdp_resume_worker(rank, world, tmpdir):
+    from b200dist import ops
+    from b200dist.parallel import FSDP
+    from b200dist.utils import checkpointing as ck
+
+    data = _batches(4)
+
+    def run(fsdp, opt, batches):
+        for t in batches:
+            shard = t.chunk(world)[rank]
+            opt.zero_grad()
+            ops.cross_entropy(fsdp(shard[:, :-1]), shard[:, 1:]).backward()
+            opt.step()
+
+    a = FSDP(_toy_llama())
+    oa = a.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    run(a, oa, data[:2])
+    ck.save_sharded_checkpoint(a, oa, 2, f"{tmpdir}/ck")
+    run(a, oa, data[2:])
+    want = a.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    # a fresh job resumes from the sharded checkpoint: weights, AdamW moments and step count must all come back
+    b = FSDP(_toy_llama())
+    ob = b.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    assert ck.load_sharded_checkpoint(b, ob, f"{tmpdir}/ck") == 2
+    assert b._step_t == 2
+    run(b, ob, data[2:])
+    got = b.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in want.items():
+        if not v.is_complex():
+            assert torch.allclose(got[k], v, atol=1e-6, rtol=1e-5), f"rank {rank} {k}: {(got[k] - v).abs().max()}"
+
+
+def test_fsdp_sharded_checkpoint_exact_resume(tmp_path):
+    run_distributed(_fsdp_resume_worker, 2, args=(str(tmp_path),))
