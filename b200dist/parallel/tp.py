@@ -416,6 +416,35 @@ def gather_tp_state_dict(module: nn.Module, tp_mesh: DeviceMesh) -> Dict[str, to
     return sd
 
 
+def load_tp_state_dict(module: nn.Module, tp_mesh: DeviceMesh, full_sd: Dict[str, torch.Tensor], strict: bool = True) -> None:
+    """Inverse of ``gather_tp_state_dict``: load a FULL (reference-layout) state dict into a module that has been
+    through ``parallelize_module`` - every rank slices out its own shard of the column- / row-parallel tensors.  This is
+    how a consolidated checkpoint (``utils.load_checkpoint`` format, or one written by the reference) resumes a TP run."""
+    T, r = tp_mesh.size(), tp_mesh.get_local_rank()
+    dims = {}
+    for mname, mod in module.named_modules():
+        ti = getattr(mod, "_tp_info", None)
+        if ti and "dim" in ti:
+            for pname, _ in mod.named_parameters(recurse=False):
+                if pname == "weight" or (pname == "bias" and ti["style"] == "colwise"):
+                    dims[f"{mname}.{pname}" if mname else pname] = ti["dim"] if pname == "weight" else 0
+    own = module.state_dict()
+    missing = [k for k in own if k not in full_sd]
+    if strict and missing:
+        raise KeyError(f"load_tp_state_dict: missing keys {missing[:5]}")
+    with torch.no_grad():
+        for k, dst in own.items():
+            if k not in full_sd:
+                continue
+            src = full_sd[k]
+            if k in dims and T > 1:
+                src = src.chunk(T, dim=dims[k])[r]
+            if dst.is_complex() or tuple(src.shape) != tuple(dst.shape):
+                if tuple(src.shape) != tuple(dst.shape):
+                    raise ValueError(f"load_tp_state_dict: {k} has shape {tuple(src.shape)}, expected {tuple(dst.shape)}")
+            dst.copy_(src.to(dst.device))
+
+
 # --------------------------------------------------------------------------- vocabulary-parallel cross-entropy
 class _VocabParallelXent(Function):
     """Cross-entropy on vocabulary-sharded logits without gathering them.

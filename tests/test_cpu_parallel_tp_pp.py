@@ -49,6 +49,15 @@ def _tp_worker(rank, world, sp):
         assert full[k].shape == v.shape, k
         if not v.is_complex():
             assert torch.allclose(full[k], v), k
+    # and back: a full (reference-layout) state dict loads into the sharded module
+    from b200dist.parallel.tp import load_tp_state_dict
+
+    other = {k: (v + 1.0 if (v.is_floating_point() and not v.is_complex()) else v) for k, v in ref.state_dict().items()}
+    load_tp_state_dict(model, mesh["tp"], other)
+    again = gather_tp_state_dict(model, mesh["tp"])
+    for k, v in other.items():
+        if not v.is_complex():
+            assert torch.allclose(again[k], v), k
 
 
 def test_tp_sp_llama_matches_unsharded():
