@@ -143,3 +143,110 @@ def ring_attention(q, k, v, comm, causal: bool = True, scale=None):
     if comm.world == 1:
         return ops.attention(q, k, v, causal=causal, scale=scale)
     return _RingAttn.apply(q.contiguous(), k.contiguous(), v.contiguous(), comm, causal, scale)
+
+
+# --------------------------------------------------------------------------- zig-zag (load-balanced causal) variant
+def zigzag_positions(seq_len: int, world: int, rank: int):
+    """Global token ranges held by ``rank`` under the zig-zag layout: the sequence is cut into 2 * world blocks and rank r
+    owns blocks r and 2 * world - 1 - r, so every rank has the same amount of causal work (with contiguous chunks rank
+    P-1 attends to P chunks and rank 0 to one).  Returns [(start, stop), (start, stop)]."""
+    assert seq_len % (2 * world) == 0, "zig-zag ring attention needs seq_len % (2 * world) == 0"
+    h = seq_len // (2 * world)
+    return [(rank * h, (rank + 1) * h), ((2 * world - 1 - rank) * h, (2 * world - rank) * h)]
+
+
+def zigzag_shard(x: torch.Tensor, world: int, rank: int, dim: int = 1) -> torch.Tensor:
+    """Slice a full-sequence tensor into this rank's zig-zag shard (the two blocks concatenated along ``dim``)."""
+    (a0, a1), (b0, b1) = zigzag_positions(x.shape[dim], world, rank)
+    return torch.cat([x.narrow(dim, a0, a1 - a0), x.narrow(dim, b0, b1 - b0)], dim=dim).contiguous()
+
+
+def zigzag_unshard(parts, dim: int = 1) -> torch.Tensor:
+    """Inverse of ``zigzag_shard`` given the shards of all ranks in rank order."""
+    world = len(parts)
+    h = parts[0].shape[dim] // 2
+    blocks = [None] * (2 * world)
+    for r, p in enumerate(parts):
+        blocks[r] = p.narrow(dim, 0, h)
+        blocks[2 * world - 1 - r] = p.narrow(dim, h, h)
+    return torch.cat(blocks, dim=dim)
+
+
+class _ZigzagRingAttn(Function):
+    """Causal ring attention over zig-zag shards: every (local q block, visiting k/v block) pair is one call of the chunk
+    kernel with the blocks' global offsets; pairs that lie entirely in the future are skipped.  Each rank runs exactly
+    2 * world + 1 block pairs (of which two are diagonal), independent of its rank."""
+
+    @staticmethod
+    def _pairs(P, r, t):
+        """Block-pair list for visiting rank j = (r - t) % P: [(q_seg, kv_seg, q_block, kv_block)], future pairs dropped."""
+        j = (r - t) % P
+        qb, kb = (r, 2 * P - 1 - r), (j, 2 * P - 1 - j)
+        return j, [(a, b, qb[a], kb[b]) for a in range(2) for b in range(2) if kb[b] <= qb[a]]
+
+    @staticmethod
+    def forward(ctx, q, k, v, comm, scale):
+        P, r = comm.world, comm.rank
+        B, s, H, hd = q.shape
+        h = s // 2
+        kv = torch.stack([k, v]).contiguous()                                   # [2, B, s, Hkv, hd]
+        chunks = _gather_schedule(kv, comm)
+        qs = [q[:, :h].contiguous(), q[:, h:].contiguous()]
+        o = [torch.zeros((B, h, H, hd), dtype=torch.float32, device=q.device) for _ in range(2)]
+        lse = [torch.full((B, H, h), float("-inf"), dtype=torch.float32, device=q.device) for _ in range(2)]
+        for t in range(P):
+            _j, pairs = _ZigzagRingAttn._pairs(P, r, t)
+            for a, b, qblk, kblk in pairs:
+                kj = chunks[t][0][:, b * h:(b + 1) * h].contiguous()
+                vj = chunks[t][1][:, b * h:(b + 1) * h].contiguous()
+                o_i, lse_i = _chunk_attention(qs[a], kj, vj, True, scale, qblk * h, kblk * h)
+                o[a], lse[a] = _merge(o[a], lse[a], o_i, lse_i)
+        out = torch.cat(o, dim=1).to(q.dtype)
+        ctx.save_for_backward(q, k, v, out, lse[0], lse[1])
+        ctx.meta = (comm, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, out, lse0, lse1 = ctx.saved_tensors
+        comm, scale = ctx.meta
+        P, r = comm.world, comm.rank
+        B, s, H, hd = q.shape
+        h = s // 2
+        kv = torch.stack([k, v]).contiguous()
+        chunks = _gather_schedule(kv, comm)
+        qs = [q[:, :h].contiguous(), q[:, h:].contiguous()]
+        outs = [out[:, :h].contiguous(), out[:, h:].contiguous()]
+        dos = [do[:, :h].contiguous(), do[:, h:].contiguous()]
+        lses = [lse0, lse1]
+        dq = [torch.zeros((B, h, H, hd), dtype=torch.float32, device=q.device) for _ in range(2)]
+        dkv_part = torch.zeros((P,) + tuple(kv.shape), dtype=torch.float32, device=q.device)   # [owner, 2, B, s, Hkv, hd]
+        for t in range(P):
+            j, pairs = _ZigzagRingAttn._pairs(P, r, t)
+            for a, b, qblk, kblk in pairs:
+                kj = chunks[t][0][:, b * h:(b + 1) * h].contiguous()
+                vj = chunks[t][1][:, b * h:(b + 1) * h].contiguous()
+                if q.is_cuda:
+                    from ..ops import native as N
+
+                    dq_i, dk_i, dv_i = N.flash_attn_bwd(qs[a], kj, vj, outs[a], dos[a], lses[a], True, scale, qblk * h, kblk * h)
+                else:
+                    dq_i, dk_i, dv_i = _reference_chunk_bwd(qs[a], kj, vj, outs[a], dos[a], lses[a], True, scale,
+                                                            qblk * h, kblk * h)
+                dq[a] += dq_i.float()
+                dkv_part[j, 0, :, b * h:(b + 1) * h] += dk_i.float()
+                dkv_part[j, 1, :, b * h:(b + 1) * h] += dv_i.float()
+        mine = torch.empty(kv.shape, dtype=torch.float32, device=q.device)
+        comm.reduce_scatter(mine, dkv_part, channel=6)
+        return torch.cat(dq, dim=1).to(q.dtype), mine[0].to(k.dtype), mine[1].to(v.dtype), None, None
+
+
+def zigzag_ring_attention(q, k, v, comm, scale=None):
+    """Causal ring attention on ZIG-ZAG shards (``zigzag_shard``): q, k, v are [B, S/P, H, hd] holding blocks r and
+    2P-1-r of the sequence.  Same result as ``ring_attention`` on contiguous shards, but every rank does the same amount
+    of work.  Built from the chunk kernels ``ring_attention`` uses; validated on CPU."""
+    scale = float(scale if scale is not None else q.shape[-1] ** -0.5)
+    if comm.world == 1:
+        return ops.attention(q, k, v, causal=True, scale=scale)
+    assert q.shape[1] % 2 == 0
+    return _ZigzagRingAttn.apply(q.contiguous(), k.contiguous(), v.contiguous(), comm, scale)

@@ -79,3 +79,36 @@ def _halo_worker(rank, world):
 
 def test_halo_conv_matches_full_conv():
     run_distributed(_halo_worker, 3)
+
+
+def _zigzag_worker(rank, world, Hkv):
+    from b200dist import ops
+    from b200dist.comm import get_communicator
+    from b200dist.parallel.ring_attention import (_ZigzagRingAttn, zigzag_positions, zigzag_ring_attention, zigzag_shard,
+                                                  zigzag_unshard)
+
+    comm = get_communicator(None)
+    q, k, v, do = _attn_inputs(Hkv=Hkv)
+    qr, kr, vr = [t.clone().requires_grad_(True) for t in (q, k, v)]
+    ref = ops.attention(qr, kr, vr, causal=True)
+    ref.backward(do)
+    ql, kl, vl = [zigzag_shard(t, world, rank).requires_grad_(True) for t in (q, k, v)]
+    out = zigzag_ring_attention(ql, kl, vl, comm)
+    assert torch.allclose(out, zigzag_shard(ref.detach(), world, rank), atol=1e-5)
+    out.backward(zigzag_shard(do, world, rank))
+    for a, b, n in ((ql.grad, qr.grad, "dq"), (kl.grad, kr.grad, "dk"), (vl.grad, vr.grad, "dv")):
+        assert torch.allclose(a, zigzag_shard(b, world, rank), atol=1e-5), (n, (a - zigzag_shard(b, world, rank)).abs().max())
+    # layout helpers round-trip, and the work is balanced: every rank runs the same number of block pairs
+    parts = [zigzag_shard(q, world, r) for r in range(world)]
+    assert torch.equal(zigzag_unshard(parts), q)
+    assert zigzag_positions(16, world, rank)[0][0] == rank * (16 // (2 * world))
+    counts = [sum(len(_ZigzagRingAttn._pairs(world, r, t)[1]) for t in range(world)) for r in range(world)]
+    assert len(set(counts)) == 1 and counts[0] == 2 * world + 1, counts
+
+
+def test_zigzag_ring_attention_balanced_causal():
+    run_distributed(_zigzag_worker, 2, args=(4,))
+
+
+def test_zigzag_ring_attention_gqa_world4():
+    run_distributed(_zigzag_worker, 4, args=(2,))
