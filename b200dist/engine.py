@@ -40,8 +40,18 @@ def lm_loss(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
 class Trainer:
     def __init__(self, model: torch.nn.Module, optimizer: torch.optim.Optimizer,
                  loss_fn: Callable[[torch.Tensor, torch.Tensor], torch.Tensor] = lm_loss,
-                 device: Optional[torch.device] = None):
+                 device: Optional[torch.device] = None, cuda_graph: bool = False, graph_warmup: int = 3):
+        """``cuda_graph=True`` (single-GPU models, static shapes): after ``graph_warmup`` eager steps the whole step -
+        zero_grad, forward, loss, backward, optimizer - is captured into ONE CUDA graph and replayed from then on, which
+        removes the per-kernel launch cost of launch-bound models (several hundred launches per step for a ResNet).
+        Needs an optimizer whose step-dependent scalars live on the device (``FusedAdamW(capturable=True)``; FusedSGD bakes
+        its learning rate into the graph).  Wrappers that drive side streams from autograd hooks (DDP / FSDP) are not
+        captured: the flag is ignored for them.  EXPERIMENTAL: written against the capture rules, not yet run on a GPU."""
         self.model, self.optimizer, self.loss_fn = model, optimizer, loss_fn
+        self._graph_wanted = bool(cuda_graph) and not callable(getattr(model, "finish_backward", None))
+        self._graph_warmup = max(1, int(graph_warmup))
+        self._graph = None
+        self._static = None
         self.device = device or next(model.parameters()).device
         self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._staged = None
@@ -53,6 +63,42 @@ class Trainer:
     def train_step(self, inputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
         if self._fault is not None and self._fault == (self._rank, self.steps_done):
             raise InjectedFault(f"injected fault on rank {self._rank} before step {self.steps_done}")
+        if self._graph_wanted and inputs.is_cuda:
+            return self._graphed_step(inputs, targets)
+        return self._eager_step(inputs, targets)
+
+    def _graphed_step(self, inputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+        opt = self.optimizer
+        if self._graph is None:
+            if self.steps_done < self._graph_warmup:
+                return self._eager_step(inputs, targets)      # allocator, lazy state and func attributes settle here
+            self._static = (torch.empty_like(inputs), torch.empty_like(targets))
+            self._static[0].copy_(inputs); self._static[1].copy_(targets)
+            prepare = getattr(opt, "prepare_step", None)
+            if callable(prepare):
+                opt._external_prepare = True
+                prepare()
+            torch.cuda.synchronize(self.device)
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._static_loss = self._eager_step(self._static[0], self._static[1], count=False)
+            # capture records the work without running it: replay once so this call is a real step
+            self._graph.replay()
+            self.steps_done += 1
+            return self._static_loss
+        if inputs.shape != self._static[0].shape or targets.shape != self._static[1].shape:
+            raise ValueError("cuda_graph=True needs static shapes: got "
+                             f"{tuple(inputs.shape)} after capturing {tuple(self._static[0].shape)}")
+        self._static[0].copy_(inputs, non_blocking=True)
+        self._static[1].copy_(targets, non_blocking=True)
+        prepare = getattr(opt, "prepare_step", None)
+        if callable(prepare):
+            prepare()
+        self._graph.replay()
+        self.steps_done += 1
+        return self._static_loss
+
+    def _eager_step(self, inputs: torch.Tensor, targets: torch.Tensor, count: bool = True) -> torch.Tensor:
         self.optimizer.zero_grad(set_to_none=True)
         out = self.model(inputs)
         loss = self.loss_fn(out, targets)
@@ -61,7 +107,8 @@ class Trainer:
         if callable(finish):
             finish()  # parallel wrappers: wait for gradient collectives issued from hooks
         self.optimizer.step()
-        self.steps_done += 1
+        if count:
+            self.steps_done += 1
         return loss.detach()
 
     # ---------------------------------------------------------------- host -> device -> host step

@@ -288,6 +288,12 @@ def adamw_step(p, g, m, v, *, lr, beta1, beta2, eps, wd, step, grad_scale=1.0, p
            L.ptr(v), LL(p.numel()), F(lr), F(beta1), F(beta2), F(eps), F(wd), F(bc1), F(bc2), F(grad_scale), _s())
 
 
+def adamw_step_dev(p, g, m, v, scalars, *, beta1, beta2, eps, wd, grad_scale=1.0, p_lowp=None):
+    """AdamW reading {lr, 1 - beta1^t, sqrt(1 - beta2^t)} from the device tensor ``scalars`` (CUDA-graph friendly)."""
+    L.call("adamw_dev", L.ptr(p), I(L.dtype_code(p.dtype)), L.ptr(p_lowp), L.ptr(g), I(L.dtype_code(g.dtype)), L.ptr(m),
+           L.ptr(v), LL(p.numel()), F(beta1), F(beta2), F(eps), F(wd), L.ptr(scalars), F(grad_scale), _s())
+
+
 def sgd_step(p, g, buf, *, lr, momentum, wd, first_step, grad_scale=1.0, p_lowp=None):
     L.call("sgd", L.ptr(p), I(L.dtype_code(p.dtype)), L.ptr(p_lowp), L.ptr(g), I(L.dtype_code(g.dtype)), L.ptr(buf),
            LL(p.numel()), F(lr), F(momentum), F(wd), F(grad_scale), I(int(first_step)), _s())

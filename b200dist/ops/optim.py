@@ -13,14 +13,36 @@ from . import native as N
 
 
 class FusedAdamW(torch.optim.Optimizer):
+    """``capturable=True`` keeps the step-dependent scalars (lr, bias corrections) in a small DEVICE tensor per parameter
+    group, refreshed by ``prepare_step()`` with a stream-ordered copy, and runs the ``adamw_dev`` kernel that reads them:
+    ``step()`` can then be recorded into a CUDA graph once and replayed every iteration (``engine.Trainer(cuda_graph=True)``
+    calls ``prepare_step()`` before each replay; learning-rate schedules keep working).  One step count per group."""
+
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, grad_scale=1.0,
-                 foreach=None, fused=None):
+                 foreach=None, fused=None, capturable: bool = False):
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self.grad_scale = grad_scale
+        self.capturable = capturable
+        self._external_prepare = False     # True while a Trainer drives prepare_step() itself (capture / replay)
+
+    def prepare_step(self) -> None:
+        """Advance every group's step count and upload {lr, 1 - beta1^t, sqrt(1 - beta2^t)} to its device scalars."""
+        for group in self.param_groups:
+            dev = next((p.device for p in group["params"]), torch.device("cpu"))
+            group["_t"] = group.get("_t", 0) + 1
+            t, (b1, b2) = group["_t"], group["betas"]
+            host = group.get("_scalars_host")
+            if host is None:
+                host = group["_scalars_host"] = torch.zeros(4, dtype=torch.float32, pin_memory=dev.type == "cuda")
+                group["_scalars"] = torch.zeros(4, dtype=torch.float32, device=dev)
+            host[0], host[1], host[2] = group["lr"], 1.0 - b1 ** t, (1.0 - b2 ** t) ** 0.5
+            group["_scalars"].copy_(host, non_blocking=True)
 
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
+        if self.capturable and not self._external_prepare:
+            self.prepare_step()
         for group in self.param_groups:
             b1, b2 = group["betas"]
             for p in group["params"]:
@@ -33,9 +55,15 @@ class FusedAdamW(torch.optim.Optimizer):
                     st["exp_avg_sq"] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
                     if p.dtype == torch.bfloat16:
                         st["master"] = p.detach().float()
-                st["step"] += 1
+                st["step"] = group["_t"] if self.capturable else st["step"] + 1
                 g = p.grad
-                if p.is_cuda and p.is_contiguous() and g.is_contiguous() and g.dtype in (torch.float32, torch.bfloat16):
+                if (self.capturable and p.is_cuda and p.is_contiguous() and g.is_contiguous()
+                        and g.dtype in (torch.float32, torch.bfloat16)):
+                    master = st.get("master")
+                    N.adamw_step_dev(master if master is not None else p.data, g, st["exp_avg"], st["exp_avg_sq"],
+                                     group["_scalars"], beta1=b1, beta2=b2, eps=group["eps"], wd=group["weight_decay"],
+                                     grad_scale=self.grad_scale, p_lowp=p.data if master is not None else None)
+                elif p.is_cuda and p.is_contiguous() and g.is_contiguous() and g.dtype in (torch.float32, torch.bfloat16):
                     master = st.get("master")
                     N.adamw_step(master if master is not None else p.data, g, st["exp_avg"], st["exp_avg_sq"],
                                  lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"], wd=group["weight_decay"],

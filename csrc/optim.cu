@@ -129,6 +129,73 @@ B200_API int b200_adamw(void* p, int p_dtype, void* p_lowp, const void* g, int g
   return B200_OK;
 }
 
+// AdamW whose step-dependent scalars live in DEVICE memory: scalars[0] = lr, [1] = 1 - beta1^t, [2] = sqrt(1 - beta2^t).
+// A CUDA graph that contains this kernel stays valid from step to step: the host refreshes the three floats with a
+// stream-ordered copy before each replay instead of baking them into the launch (engine.Trainer(cuda_graph=True)).
+template <typename TP, typename TG>
+__global__ void adamw_dev_kernel(TP* __restrict__ p, __nv_bfloat16* __restrict__ p_lowp, const TG* __restrict__ g,
+                                 float* __restrict__ m, float* __restrict__ v, long long n, float beta1, float beta2,
+                                 float eps, float wd, const float* __restrict__ scalars, float grad_scale) {
+  const float lr = scalars[0], bc1 = scalars[1], bc2_sqrt = scalars[2];
+  const long long n8 = n >> 3;
+  const float step_size = lr / bc1;
+  const float decay = 1.f - lr * wd;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
+       i += (long long)gridDim.x * blockDim.x) {
+    float pv[8], gv[8], mv[8], vv[8];
+    Vec8<TP>::load(p + i * 8, pv);
+    Vec8<TG>::load(g + i * 8, gv);
+    Vec8<float>::load(m + i * 8, mv);
+    Vec8<float>::load(v + i * 8, vv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = gv[j] * grad_scale;
+      mv[j] = beta1 * mv[j] + (1.f - beta1) * gj;
+      vv[j] = beta2 * vv[j] + (1.f - beta2) * gj * gj;
+      const float denom = sqrtf(vv[j]) / bc2_sqrt + eps;
+      pv[j] = pv[j] * decay - step_size * (mv[j] / denom);
+    }
+    Vec8<TP>::store(p + i * 8, pv);
+    Vec8<float>::store(m + i * 8, mv);
+    Vec8<float>::store(v + i * 8, vv);
+    if (p_lowp) Vec8<__nv_bfloat16>::store(p_lowp + i * 8, pv);
+  }
+  if (blockIdx.x == 0) {
+    for (long long i = n8 * 8 + threadIdx.x; i < n; i += blockDim.x) {
+      const float gj = to_f<TG>(g[i]) * grad_scale;
+      float mj = beta1 * m[i] + (1.f - beta1) * gj;
+      float vj = beta2 * v[i] + (1.f - beta2) * gj * gj;
+      const float denom = sqrtf(vj) / bc2_sqrt + eps;
+      const float pj = to_f<TP>(p[i]) * decay - step_size * (mj / denom);
+      p[i] = from_f<TP>(pj);
+      m[i] = mj; v[i] = vj;
+      if (p_lowp) p_lowp[i] = __float2bfloat16_rn(pj);
+    }
+  }
+}
+
+B200_API int b200_adamw_dev(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* m, float* v,
+                            long long n, float beta1, float beta2, float eps, float wd, const float* scalars,
+                            float grad_scale, cudaStream_t stream) {
+  if (n <= 0) return B200_OK;
+  if (!aligned16(p) || !aligned16(g) || !aligned16(m) || !aligned16(v) || (p_lowp && !aligned16(p_lowp)) || !scalars) {
+    b200_set_error("adamw_dev: buffers must be 16-byte aligned and scalars non-null");
+    return B200_ERR_SHAPE;
+  }
+  const int grid = ew_grid((n >> 3) ? (n >> 3) : 1, 256);
+#define LAUNCH(TP, TG)                                                                          \
+  adamw_dev_kernel<TP, TG><<<grid, 256, 0, stream>>>((TP*)p, (__nv_bfloat16*)p_lowp, (const TG*)g, m, v, n, beta1, \
+                                                     beta2, eps, wd, scalars, grad_scale)
+  if (p_dtype == 1 && g_dtype == 1) LAUNCH(float, float);
+  else if (p_dtype == 1 && g_dtype == 0) LAUNCH(float, __nv_bfloat16);
+  else if (p_dtype == 0 && g_dtype == 0) LAUNCH(__nv_bfloat16, __nv_bfloat16);
+  else if (p_dtype == 0 && g_dtype == 1) LAUNCH(__nv_bfloat16, float);
+  else { b200_set_error("adamw_dev: bad dtype codes"); return B200_ERR_UNSUPPORTED; }
+#undef LAUNCH
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 // torch.optim.SGD semantics: d = g + wd*p; buf = d on the first step else momentum*buf + d; p -= lr*buf.
 B200_API int b200_sgd(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* buf,
                       long long n, float lr, float momentum, float wd, float grad_scale,

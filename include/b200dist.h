@@ -143,6 +143,11 @@ B200DIST_API int b200_sum_scale(const float* x, float* out, int n, float scale, 
 B200DIST_API int b200_adamw(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* m,
                         float* v, long long n, float lr, float beta1, float beta2, float eps,
                         float wd, float bc1, float bc2, float grad_scale, cudaStream_t stream);
+/* AdamW with the step-dependent scalars {lr, 1 - beta1^t, sqrt(1 - beta2^t)} read from device memory: usable inside a CUDA
+ * graph that is replayed every step (no counterpart in the reference, which runs eager torch.optim.AdamW) */
+B200DIST_API int b200_adamw_dev(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* m, float* v,
+                            long long n, float beta1, float beta2, float eps, float wd, const float* scalars,
+                            float grad_scale, cudaStream_t stream);
 B200DIST_API int b200_sgd(void* p, int p_dtype, void* p_lowp, const void* g, int g_dtype, float* buf,
                       long long n, float lr, float momentum, float wd, float grad_scale,
                       int first_step, cudaStream_t stream);

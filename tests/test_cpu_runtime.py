@@ -313,3 +313,31 @@ def test_public_header_declares_every_exported_symbol():
     exported = {l.split()[-1] for l in out.splitlines() if " T b200_" in l}
     declared = set(re.findall(r"\bb200_[a-z0-9_]+", (root / "include" / "b200dist.h").read_text()))
     assert exported and not (exported - declared), sorted(exported - declared)
+
+
+def test_capturable_adamw_matches_torch_and_tracks_lr():
+    """capturable=True keeps (lr, bias corrections) in a per-group tensor refreshed by prepare_step(): same numbers as
+    torch.optim.AdamW, including after a learning-rate change (the values a replayed CUDA graph would read)."""
+    from b200dist.ops import FusedAdamW
+
+    torch.manual_seed(0)
+    a = torch.nn.Parameter(torch.randn(6, 5)); b = torch.nn.Parameter(a.detach().clone())
+    oa = FusedAdamW([a], lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1, capturable=True)
+    ob = torch.optim.AdamW([b], lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    for i in range(5):
+        if i == 3:
+            oa.param_groups[0]["lr"] = ob.param_groups[0]["lr"] = 3e-3
+        g = torch.randn(6, 5)
+        a.grad, b.grad = g.clone(), g.clone()
+        oa.step(); ob.step()
+    assert torch.allclose(a, b, atol=1e-6)
+    sc = oa.param_groups[0]["_scalars"]
+    assert oa.param_groups[0]["_t"] == 5 and abs(float(sc[0]) - 3e-3) < 1e-9
+    assert abs(float(sc[1]) - (1 - 0.9 ** 5)) < 1e-6 and abs(float(sc[2]) - (1 - 0.95 ** 5) ** 0.5) < 1e-6
+    # a trainer asked for a graph on a CPU model simply runs eagerly
+    from b200dist.engine import Trainer
+
+    m = torch.nn.Linear(4, 3)
+    t = Trainer(m, FusedAdamW(m.parameters(), capturable=True), loss_fn=torch.nn.functional.cross_entropy, cuda_graph=True)
+    t.train_step(torch.randn(2, 4), torch.tensor([0, 2]))
+    assert t._graph is None and t.steps_done == 1

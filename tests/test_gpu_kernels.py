@@ -49,3 +49,16 @@ def test_conv_implicit_gemm_fprop_dgrad_wgrad():
     r = subprocess.run([sys.executable, str(root / "tools" / "conv_igemm_check.py")], capture_output=True, text=True,
                        timeout=300, cwd=str(root))
     assert r.returncode == 0 and "failures 0" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pytest.mark.skipif(__import__("os").environ.get("B200DIST_TEST_EXPERIMENTAL", "0") in ("", "0"),
+                    reason="experimental path (CUDA-graph training step): set B200DIST_TEST_EXPERIMENTAL=1")
+def test_cuda_graph_training_step_matches_eager():
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "tools" / "cuda_graph_check.py")], capture_output=True, text=True,
+                       timeout=300, cwd=str(root))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

@@ -1,0 +1,47 @@
+"""CUDA-graph training step (engine.Trainer(cuda_graph=True)) vs the eager step on one GPU: same loss sequence, and the
+launch-bound speed-up on a small model.  EXPERIMENTAL path - run this first when a GPU is available:
+    python tools/cuda_graph_check.py"""
+import sys
+import time
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from b200dist.engine import Trainer  # noqa: E402
+from b200dist.models.llama2 import ModelArgs, Transformer  # noqa: E402
+from b200dist.ops import FusedAdamW  # noqa: E402
+
+dev = torch.device("cuda", 0)
+cfg = dict(dim=512, n_layers=4, n_heads=8, vocab_size=4096, max_seq_len=512)
+g = torch.Generator().manual_seed(1)
+data = [torch.randint(0, 4096, (4, 257), generator=g).to(dev) for _ in range(12)]
+
+
+def run(graph: bool):
+    torch.manual_seed(0)
+    with torch.device(dev):
+        m = Transformer(ModelArgs(**cfg))
+    m = m.to(torch.bfloat16)
+    opt = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1, capturable=True)
+    tr = Trainer(m, opt, cuda_graph=graph, graph_warmup=3)
+    losses = []
+    for t in data:
+        losses.append(float(tr.train_step(t[:, :-1], t[:, 1:])))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        for t in data:
+            tr.train_step(t[:, :-1], t[:, 1:])
+    torch.cuda.synchronize()
+    return losses, (time.perf_counter() - t0) / (3 * len(data)) * 1e3, tr._graph is not None
+
+
+le, te, _ = run(False)
+lg, tg, captured = run(True)
+err = max(abs(a - b) for a, b in zip(le, lg))
+ok = captured and err < 2e-2
+print(f"[{'PASS' if ok else 'FAIL'}] cuda graph step: captured={captured} max loss diff vs eager {err:.3g}; "
+      f"eager {te:.2f} ms/step, graph {tg:.2f} ms/step")
+print("eager:", [round(x, 4) for x in le]); print("graph:", [round(x, 4) for x in lg])
+sys.exit(0 if ok else 1)
