@@ -22,19 +22,22 @@ def main(kind="ulysses"):
     rank, world, local, device = setup()
     from b200dist import ops
     from b200dist.comm import get_communicator
-    from b200dist.parallel import ring_attention, ulysses_attention
+    from b200dist.parallel import ring_attention, ulysses_attention, zigzag_ring_attention, zigzag_shard
     from b200dist.utils import cleanup_distributed
 
-    fn = ulysses_attention if kind == "ulysses" else ring_attention
+    zig = kind == "zigzag"
+    fn = {"ulysses": ulysses_attention, "ring": ring_attention,
+          "zigzag": lambda q, k, v, comm, causal=True: zigzag_ring_attention(q, k, v, comm)}[kind]
     comm = get_communicator(None)
     dtype = torch.bfloat16 if device.type == "cuda" else torch.float32
     s = a.seq_len // world
     g = torch.Generator().manual_seed(0)
     full = [torch.randn(a.batch, a.seq_len, a.heads, a.head_dim, generator=g).to(device).to(dtype) for _ in range(3)]
-    q, k, v = [t[:, rank * s:(rank + 1) * s].contiguous().requires_grad_(True) for t in full]
+    shard = (lambda t: zigzag_shard(t, world, rank)) if zig else (lambda t: t[:, rank * s:(rank + 1) * s].contiguous())
+    q, k, v = [shard(t).requires_grad_(True) for t in full]
     out = fn(q, k, v, comm, causal=True)
     if a.check:
-        ref = ops.attention(*full, causal=True)[:, rank * s:(rank + 1) * s]
+        ref = shard(ops.attention(*full, causal=True))
         err = float((out.float() - ref.float()).abs().max())
         print(f"[rank {rank}] max |{kind} - single-device| = {err:.4g}", flush=True)
     timer = StepTimer(device)
