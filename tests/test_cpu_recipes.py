@@ -68,23 +68,34 @@ def test_main_py_gloo_ddp(tmp_path):
     assert "images/s" in out and (tmp_path / "log.txt").read_text().count("Average epoch time") == 1
 
 
+def _run_many(jobs, workers=4):
+    """Run several (cmd, nproc) launches concurrently (each has its own rendezvous port); returns outputs in order."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(max_workers=workers) as ex:
+        futs = [ex.submit(_run, cmd, nproc) for cmd, nproc in jobs]
+        return [f.result() for f in futs]
+
+
 def test_recipe_scripts_run_on_cpu(tmp_path):
-    out = _run(["scripts/03_tensor_parallel_tp/01_device_mesh_basics.py"], nproc=2)
-    assert "✓" in out
-    out = _run(["scripts/03_tensor_parallel_tp/02_basic_tensor_parallel.py"], nproc=2)
-    assert "iter 4" in out
-    out = _run(["scripts/04_pipeline_parallel_pp/01_manual_model_split.py"], nproc=2)
-    assert "pipeline output" in out
-    out = _run(["scripts/04_pipeline_parallel_pp/03_pipeline_training.py", "--num-steps", "4", "--batch-size", "4", "--seq-len", "16",
-                "--dim", "32", "--layers-per-stage", "1", "--vocab", "100", "--pp", "2"], nproc=2)
-    assert "tokens/s" in out
-    out = _run(["scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py", "--iters", "3", "--seq-len", "32", "--tp_size", "2"], nproc=2)
-    assert "tokens/s" in out
-    out = _run(["scripts/01_data_parallel_ddp/multinode_ddp_basic.py", "--total_epochs", "2", "--backend", "gloo", "--save_every", "1",
-                "--snapshot", str(tmp_path / "snap.pt")], nproc=2)
+    outs = _run_many([
+        (["scripts/03_tensor_parallel_tp/01_device_mesh_basics.py"], 2),
+        (["scripts/03_tensor_parallel_tp/02_basic_tensor_parallel.py"], 2),
+        (["scripts/04_pipeline_parallel_pp/01_manual_model_split.py"], 2),
+        (["scripts/04_pipeline_parallel_pp/03_pipeline_training.py", "--num-steps", "4", "--batch-size", "4", "--seq-len", "16",
+          "--dim", "32", "--layers-per-stage", "1", "--vocab", "100", "--pp", "2"], 2),
+        (["scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py", "--iters", "3", "--seq-len", "32", "--tp_size", "2"], 2),
+        (["scripts/01_data_parallel_ddp/multinode_ddp_basic.py", "--total_epochs", "2", "--backend", "gloo", "--save_every", "1",
+          "--snapshot", str(tmp_path / "snap.pt")], 2),
+        (["scripts/07_domain_parallel/01_halo_conv.py"], 2),
+    ])
+    assert "✓" in outs[0]
+    assert "iter 4" in outs[1]
+    assert "pipeline output" in outs[2]
+    assert "tokens/s" in outs[3]
+    assert "tokens/s" in outs[4]
     assert (tmp_path / "snap.pt").exists()
-    out = _run(["scripts/07_domain_parallel/01_halo_conv.py"], nproc=2)
-    assert "with halo exchange" in out
+    assert "with halo exchange" in outs[6]
 
 
 def test_comm_bench_csv_columns(tmp_path):
@@ -97,16 +108,18 @@ def test_comm_bench_csv_columns(tmp_path):
 
 
 def test_comm_tools_and_fsdp_tp_examples_run_on_cpu(tmp_path):
-    out = _run(["tools/test_torchrun.py"], nproc=2)
-    assert "rank 1 has data 42" in out
-    out = _run(["tools/all_reduce_test.py", "--backend", "gloo", "--max-exp", "4", "--output", str(tmp_path / "ar.log")], nproc=2)
+    outs = _run_many([
+        (["tools/test_torchrun.py"], 2),
+        (["tools/all_reduce_test.py", "--backend", "gloo", "--max-exp", "4", "--output", str(tmp_path / "ar.log")], 2),
+        (["fsdp_tp/tensor_parallel_example.py", "--iters", "3"], 2),
+        (["fsdp_tp/fsdp_tp_example.py", "--iters", "2", "--seq-len", "32", "--tp_size", "2"], 2),
+        # import-compatible module names of the reference's fsdp_tp/ directory
+        (["-c", "import sys; sys.path.insert(0, 'fsdp_tp'); from llama2_model import Transformer, ModelArgs, apply_rotary_emb; "
+                "from log_utils import rank_log, get_logger, verify_min_gpu_count; print('imports ok')"], 1),
+    ])
+    assert "rank 1 has data 42" in outs[0]
     log = (tmp_path / "ar.log").read_text()
     assert log.count("all_reduce") == 2 and log.count("broadcast") == 2 and "elements=10000" in log
-    out = _run(["fsdp_tp/tensor_parallel_example.py", "--iters", "3"], nproc=2)
-    assert "tensor-parallel example done" in out
-    out = _run(["fsdp_tp/fsdp_tp_example.py", "--iters", "2", "--seq-len", "32", "--tp_size", "2"], nproc=2)
-    assert "tokens/s" in out
-    # import-compatible module names of the reference's fsdp_tp/ directory
-    out = _run(["-c", "import sys; sys.path.insert(0, 'fsdp_tp'); from llama2_model import Transformer, ModelArgs, apply_rotary_emb; "
-                      "from log_utils import rank_log, get_logger, verify_min_gpu_count; print('imports ok')"])
-    assert "imports ok" in out
+    assert "tensor-parallel example done" in outs[2]
+    assert "tokens/s" in outs[3]
+    assert "imports ok" in outs[4]
