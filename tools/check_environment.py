@@ -71,6 +71,13 @@ def main():
         t = torch.full((1024,), float(rank), device="cuda")
         get_communicator(None).all_reduce(t)
         checks["peer-memory all-reduce"] = bool((t == sum(range(world))).all())
+        try:   # informational: NVLS needs multicast support on every GPU (the pull kernels are used otherwise)
+            from b200dist.comm.peer_mem import multicast_supported
+
+            if rank == 0:
+                print(f"NVSwitch multicast (NVLS all-reduce path): {'available' if multicast_supported() else 'not available'}")
+        except Exception as e:  # noqa: BLE001
+            print(f"[rank {rank}] multicast query failed: {e}")
     ok = all(checks.values())
     if rank == 0:
         print("summary:")
