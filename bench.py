@@ -29,6 +29,12 @@ sys.path.insert(0, str(ROOT))
 
 MODEL_DEFAULT = "llama2-7b"
 SEQ_DEFAULT = 4096
+# Llama-2 sizes for the reference arm (its ModelArgs fields), so that arm imports nothing from b200dist
+REF_MODEL_DIMS = {
+    "llama2-7b": dict(dim=4096, n_layers=32, n_heads=32, n_kv_heads=32, vocab_size=32000, multiple_of=256),
+    "llama2-13b": dict(dim=5120, n_layers=40, n_heads=40, n_kv_heads=40, vocab_size=32000, multiple_of=256),
+    "llama2-tiny": dict(dim=512, n_layers=4, n_heads=8, vocab_size=32000),
+}
 
 
 class ClockSampler:
@@ -98,6 +104,7 @@ def parse():
     ap.add_argument("--n-layers", type=int, default=None, help="debug only: a reduced model is NOT the headline config")
     ap.add_argument("--ref-wrap", default="block", choices=["block", "root"],
                     help="reference arm: fully_shard per block (idiomatic) or root-only (as the recipe is written)")
+    ap.add_argument("--ref-reduce-fp32", action="store_true", help="reference arm: reduce gradients in fp32 instead of bf16")
     ap.add_argument("--lr", type=float, default=3e-4)
     ap.add_argument("--fsdp-ctas", type=int, default=64, help="CTAs per peer-memory collective kernel (FSDP)")
     ap.add_argument("--kernel-gather", action="store_true", help="FSDP all-gather with the SM pull kernel instead of DMA peer copies")
@@ -235,9 +242,12 @@ def run_reference(a, rank, world, local):
     Mirrors /root/reference/scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:102-180 with the model
     size / sequence length / dtype / loss parameterised as BASELINE.md §4 row 3 prescribes.
     """
-    ref_root = ROOT / "baseline" / "_ref"
-    if not (ref_root / "reference_src" / "fsdp_tp" / "llama2_model.py").exists():
-        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (reference not installed)"}))
+    from baseline.install_ref import ensure_reference, why_unavailable
+
+    ref_root = ensure_reference()  # installs baseline/_ref on first use when the reference tree is reachable
+    if ref_root is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why_unavailable()}))
         return None
     sys.path.insert(0, str(ref_root))
     sys.path.insert(0, str(ref_root / "reference_src" / "fsdp_tp"))
@@ -251,9 +261,7 @@ def run_reference(a, rank, world, local):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
         dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", local))
-    from b200dist.models.llama2 import PRESETS
-
-    cfg = dict(PRESETS[a.model])
+    cfg = dict(REF_MODEL_DIMS[a.model])  # nothing of b200dist is imported on this path
     cfg["max_seq_len"] = a.seq_len
     if a.n_layers:
         cfg["n_layers"] = a.n_layers
@@ -262,7 +270,10 @@ def run_reference(a, rank, world, local):
     with torch.device(dev):
         model = Transformer.from_model_args(ModelArgs(**cfg))
     mesh = dist.device_mesh.init_device_mesh("cuda", (world,), mesh_dim_names=("dp",))
-    mp = MixedPrecisionPolicy(param_dtype=torch.bfloat16, reduce_dtype=torch.float32)
+    # bf16 parameters AND bf16 gradient reduction: what the repo arm does, and what the reference's own FSDP
+    # mixed-precision recipe sets (scripts/02_fully_sharded_fsdp/resnet_fsdp_training.py:200-203)
+    mp = MixedPrecisionPolicy(param_dtype=torch.bfloat16,
+                              reduce_dtype=torch.float32 if a.ref_reduce_fp32 else torch.bfloat16)
     if a.ref_wrap == "block":
         for layer in model.layers:
             fully_shard(layer, mesh=mesh, mp_policy=mp)

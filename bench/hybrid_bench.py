@@ -84,10 +84,11 @@ def main():
             opt.step()
             return loss
     else:
-        ref_root = ROOT / "baseline" / "_ref"
-        if not (ref_root / "reference_src" / "fsdp_tp" / "llama2_model.py").exists():
+        from baseline.install_ref import ensure_reference, why_unavailable
+        ref_root = ensure_reference()
+        if ref_root is None:
             if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing"}))
+                print(json.dumps({"impl": "reference", "unavailable": why_unavailable()}))
             dist.destroy_process_group(); return
         sys.path.insert(0, str(ref_root / "reference_src" / "fsdp_tp"))
         import torch.nn.functional as F

@@ -73,10 +73,11 @@ def main():
         opt = FusedAdamW(stage.parameters(), lr=3e-4, betas=(0.9, 0.95), weight_decay=0.1)
         is_first, is_last = stage.is_first, stage.is_last
     else:
-        ref_root = ROOT / "baseline" / "_ref"
-        if not (ref_root / "reference_src" / "fsdp_tp" / "llama2_model.py").exists():
+        from baseline.install_ref import ensure_reference, why_unavailable
+        ref_root = ensure_reference()
+        if ref_root is None:
             if rank == 0:
-                print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing"}))
+                print(json.dumps({"impl": "reference", "unavailable": why_unavailable()}))
             dist.destroy_process_group(); return
         sys.path.insert(0, str(ref_root / "reference_src" / "fsdp_tp"))
         import torch.nn.functional as F

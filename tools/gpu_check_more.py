@@ -304,33 +304,41 @@ def group_models(results):
     from b200dist.ops import FusedAdamW, FusedSGD
     _check, _time = _h()
     dev = "cuda"
-    ref_dir = "/root/repo/baseline/_ref/reference_src/fsdp_tp"
-    sys.path.insert(0, ref_dir)
-    import llama2_model as ref
-    a = dict(dim=256, n_layers=2, n_heads=4, vocab_size=1024, max_seq_len=256)
-    torch.manual_seed(0)
-    r = ref.Transformer.from_model_args(ref.ModelArgs(**a)).to(dev)
-    m = Transformer(ModelArgs(**a)).to(dev)
-    m.load_state_dict(r.state_dict())
-    m = m.to(torch.bfloat16)
-    ro = torch.optim.AdamW(r.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
-    mo = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
-    g = torch.Generator(device="cpu").manual_seed(1)
-    lr_, lm_ = [], []
-    for step in range(8):
-        tok = torch.randint(0, 1024, (4, 129), generator=g).to(dev)
-        x, y = tok[:, :-1], tok[:, 1:]
-        ro.zero_grad()
-        with torch.autocast("cuda", dtype=torch.bfloat16):
-            out = r(x)
-        l = torch.nn.functional.cross_entropy(out.float().view(-1, 1024), y.reshape(-1)); l.backward(); ro.step()
-        mo.zero_grad()
-        l2 = ops.cross_entropy(m(x), y); l2.backward(); mo.step()
-        lr_.append(float(l)); lm_.append(float(l2))
-    print("ref  losses", [round(v, 4) for v in lr_], flush=True)
-    print("ours losses", [round(v, 4) for v in lm_], flush=True)
-    _check("llama loss curve vs reference (bf16)", torch.tensor(lm_), torch.tensor(lr_), 0.08, 0.01, results)
-    assert lm_[-1] < lm_[0]
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root))
+    from baseline.install_ref import ensure_reference, reference_path, why_unavailable
+    if ensure_reference() is None:
+        print(f"[SKIP] llama loss curve vs reference: {why_unavailable()}", flush=True)
+        ref = None
+    else:
+        sys.path.insert(0, str(reference_path("fsdp_tp")))
+        import llama2_model as ref
+    if ref is not None:
+        a = dict(dim=256, n_layers=2, n_heads=4, vocab_size=1024, max_seq_len=256)
+        torch.manual_seed(0)
+        r = ref.Transformer.from_model_args(ref.ModelArgs(**a)).to(dev)
+        m = Transformer(ModelArgs(**a)).to(dev)
+        m.load_state_dict(r.state_dict())
+        m = m.to(torch.bfloat16)
+        ro = torch.optim.AdamW(r.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+        mo = FusedAdamW(m.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+        g = torch.Generator(device="cpu").manual_seed(1)
+        lr_, lm_ = [], []
+        for step in range(8):
+            tok = torch.randint(0, 1024, (4, 129), generator=g).to(dev)
+            x, y = tok[:, :-1], tok[:, 1:]
+            ro.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = r(x)
+            l = torch.nn.functional.cross_entropy(out.float().view(-1, 1024), y.reshape(-1)); l.backward(); ro.step()
+            mo.zero_grad()
+            l2 = ops.cross_entropy(m(x), y); l2.backward(); mo.step()
+            lr_.append(float(l)); lm_.append(float(l2))
+        print("ref  losses", [round(v, 4) for v in lr_], flush=True)
+        print("ours losses", [round(v, 4) for v in lm_], flush=True)
+        _check("llama loss curve vs reference (bf16)", torch.tensor(lm_), torch.tensor(lr_), 0.08, 0.01, results)
+        assert lm_[-1] < lm_[0]
     # ResNet-18 vs torchvision, SGD
     torch.manual_seed(0)
     tv = torchvision.models.resnet18(num_classes=100).to(dev)

@@ -7,7 +7,12 @@ import torch
 import torch.nn.functional as F
 
 ROOT = Path(__file__).resolve().parent.parent
-sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "baseline/_ref/reference_src/fsdp_tp"))
+sys.path.insert(0, str(ROOT))
+from baseline.install_ref import ensure_reference, reference_path, why_unavailable  # noqa: E402
+
+if ensure_reference() is None:
+    raise SystemExit(f"loss_parity needs the reference model: {why_unavailable()}")
+sys.path.insert(0, str(reference_path("fsdp_tp")))
 from llama2_model import ModelArgs as RA, Transformer as RT  # noqa: E402
 
 from b200dist import ops  # noqa: E402
