@@ -38,6 +38,15 @@ class Communicator:
         use_cuda = torch.cuda.is_available() and not force_fallback
         self.native = bool(use_cuda and self.world <= 8 and L.available())
         self.device = device or (torch.device("cuda", torch.cuda.current_device()) if use_cuda else torch.device("cpu"))
+        self.native_refused = ""
+        if self.native and self.initialized and self.world > 1:
+            # the peer-memory data plane needs every rank of the group on ONE box with peer access between all
+            # pairs of their GPUs (CUDA-IPC handles mean nothing on another host): agree on that before any buffer is
+            # exchanged, and send the whole group through torch.distributed (NCCL) otherwise - multi-node jobs,
+            # sub-groups that span nodes (HYBRID_SHARD replicas, PP x DP across nodes) keep working, as in the reference
+            self.native, self.native_refused = _agree_single_box(group, self.device, self.world)
+        if self.native:
+            _apply_peer_timeout(self.device)
         self.max_ctas = 0
         self.oneshot_threshold = 256 << 10
         self._seq = [0] * N_CHANNELS
@@ -407,6 +416,66 @@ class Communicator:
         buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
         L.call("comm_alltoall", *self._ctx(buf, channel), L.ptr(out), LL(0), LL(per), I(self.max_ctas), self._s())
         return out
+
+
+def _host_identity() -> str:
+    """Same string on every process of one OS instance (boot id survives containers sharing a kernel; the hostname is the
+    fallback)."""
+    try:
+        with open("/proc/sys/kernel/random/boot_id") as f:
+            return f.read().strip()
+    except OSError:
+        import socket
+
+        return socket.gethostname()
+
+
+def _agree_single_box(group, device: torch.device, world: int):
+    """Collective (object all-gather on the control plane).  Returns (ok, reason) - identical on every rank."""
+    dev = device.index if device.index is not None else (torch.cuda.current_device() if torch.cuda.is_available() else 0)
+    mine = {"host": _host_identity(), "dev": int(dev)}
+    if os.environ.get("B200DIST_FAKE_HOST"):   # test hook: pretend this rank runs elsewhere
+        mine["host"] = os.environ["B200DIST_FAKE_HOST"]
+    infos = [None] * world
+    dist.all_gather_object(infos, mine, group=group)
+    reason = ""
+    if len({i["host"] for i in infos}) != 1:
+        reason = "ranks of the group run on different hosts"
+    else:
+        # every rank checks the devices of the others it can see; processes with a restricted CUDA_VISIBLE_DEVICES
+        # cannot index their peers, the IPC import then decides (NVSwitch boxes give all-to-all access)
+        n_vis = torch.cuda.device_count() if torch.cuda.is_available() else 0
+        for i in infos:
+            d = i["dev"]
+            if d != mine["dev"] and d < n_vis and os.environ.get("CUDA_VISIBLE_DEVICES") is None:
+                if not torch.cuda.can_device_access_peer(mine["dev"], d):
+                    reason = f"no peer access between GPU {mine['dev']} and GPU {d}"
+                    break
+    verdicts = [None] * world
+    dist.all_gather_object(verdicts, reason, group=group)
+    bad = [v for v in verdicts if v]
+    return (not bad), (bad[0] if bad else "")
+
+
+_timeout_applied = set()
+
+
+def _apply_peer_timeout(device: torch.device) -> None:
+    """B200DIST_PEER_TIMEOUT_S (default 600, 0 = off) and B200DIST_PEER_TIMEOUT_ACTION (trap | report) -> the device-side
+    limit on cross-rank waits (csrc/common.cuh PeerWatchdog).  Once per device."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx in _timeout_applied:
+        return
+    _timeout_applied.add(idx)
+    secs = float(os.environ.get("B200DIST_PEER_TIMEOUT_S", "600"))
+    trap = os.environ.get("B200DIST_PEER_TIMEOUT_ACTION", "trap").lower() != "report"
+    with torch.cuda.device(device):
+        L.check(L.load().b200_set_peer_timeout(C.c_double(secs), I(1 if trap else 0)), "set_peer_timeout")
+
+
+def peer_timeouts_reported() -> int:
+    """How many cross-rank waits have exceeded the limit so far in this process (0 when the library is absent)."""
+    return int(L.load().b200_peer_timeout_count()) if L.available() else 0
 
 
 _default: Optional[Communicator] = None

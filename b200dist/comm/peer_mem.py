@@ -66,6 +66,8 @@ class PeerBuffer:
         item = torch.empty((), dtype=dtype).element_size()
         if numel is None:
             numel = (self.nbytes - offset_bytes) // item
+        if offset_bytes < 0 or offset_bytes + numel * item > self.nbytes:
+            raise ValueError(f"view of {numel} x {dtype} at byte {offset_bytes} exceeds the {self.nbytes}-byte buffer")
         return self._local[offset_bytes:offset_bytes + numel * item].view(dtype)
 
     def close(self):
@@ -183,6 +185,8 @@ class MulticastBuffer:
         item = torch.empty((), dtype=dtype).element_size()
         if numel is None:
             numel = (self.nbytes - offset_bytes) // item
+        if offset_bytes < 0 or offset_bytes + numel * item > self.nbytes:
+            raise ValueError(f"view of {numel} x {dtype} at byte {offset_bytes} exceeds the {self.nbytes}-byte buffer")
         return self._local[offset_bytes:offset_bytes + numel * item].view(dtype)
 
     def close(self):

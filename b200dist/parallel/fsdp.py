@@ -141,7 +141,8 @@ class FSDP(nn.Module):
             self._init_unit(u)
         max_total = max(u.total for u in self.exec_units)
         if self.native and self.world > 1:
-            self.grad_stage = [self.comm.symmetric_buffer(max_total * 2) for _ in range(2)]
+            esize = torch.empty((), dtype=self.dtype).element_size()
+            self.grad_stage = [self.comm.symmetric_buffer(max_total * esize) for _ in range(2)]
             self._stage_events = [None, None]
         self._stage_idx = 0
         self._register_hooks()
@@ -334,7 +335,8 @@ class FSDP(nn.Module):
             ev.record(cur)
             with torch.cuda.stream(self.rs_stream):
                 self.rs_stream.wait_event(ev)
-                if self.fused_optimizer and hp is not None and hp["kind"] == "adamw":
+                # the fused kernel writes a bf16 compute copy next to the fp32 master: bf16 models only
+                if self.fused_optimizer and hp is not None and hp["kind"] == "adamw" and self.dtype == torch.bfloat16:
                     self._ensure_state(u)
                     self.comm.rs_adamw_from(stage, 0, self.dtype, u.shard_numel, 1.0 / self.world, u.master, u.shard,
                                             u.m, u.v, lr=hp["lr"], beta1=hp["betas"][0], beta2=hp["betas"][1],
@@ -568,17 +570,67 @@ class ShardedOptimizer:
             u.grad_shard = None
 
     def state_dict(self):
+        """THIS rank's optimizer shards (the per-rank payload of a sharded checkpoint).  Tagged with rank / world so that
+        it can only be loaded back into the same position; a single-file checkpoint uses ``full_state_dict`` instead."""
         f = self.fsdp
-        return {"step": f._step_t, "hp": {k: v for k, v in self.hp.items()},
+        return {"format": "shards", "rank": f.rank, "world": f.world, "step": f._step_t,
+                "hp": {k: v for k, v in self.hp.items()},
                 "shards": {u.name: {"master": u.master, "m": u.m, "v": u.v} for u in f.exec_units}}
+
+    def full_state_dict(self, rank0_only: bool = True):
+        """Collective.  fp32 master weights and AdamW moments gathered unit by unit into UNSHARDED flat tensors (CPU),
+        keyed by unit name, independent of the world size that wrote them: what a consolidated single-file checkpoint
+        stores, so that any rank of any world size can cut its own slice back out (``load_state_dict``)."""
+        f = self.fsdp
+        f.finish_backward()
+        keep = (f.rank == 0) or not rank0_only
+        units = {}
+        for u in f.exec_units:
+            f._ensure_state(u)
+            entry = {"numel": u.offsets[-1] + u.params[-1].numel() if u.params else 0}
+            for key, t in (("master", u.master), ("m", u.m), ("v", u.v)):
+                if f.world == 1:
+                    full = t
+                else:
+                    full = torch.empty(u.total, dtype=torch.float32, device=t.device)
+                    dist.all_gather_into_tensor(full, t.contiguous(), group=f.comm.group)
+                if keep:
+                    entry[key] = full[:entry["numel"]].detach().cpu().clone()
+            if keep:
+                units[u.name] = entry
+        if not keep:
+            return {}
+        return {"format": "full", "step": f._step_t, "hp": {k: v for k, v in self.hp.items()}, "units": units}
 
     def load_state_dict(self, sd) -> None:
         f = self.fsdp
+        fmt = sd.get("format", "shards")
+        if fmt == "full":
+            for u in f.exec_units:
+                e = sd["units"].get(u.name)
+                if e is None:
+                    continue
+                numel = u.offsets[-1] + u.params[-1].numel() if u.params else 0
+                if int(e["numel"]) != numel:
+                    raise ValueError(f"optimizer state of unit {u.name}: {e['numel']} elements, the model has {numel}")
+                lo, hi = f.rank * u.shard_numel, min((f.rank + 1) * u.shard_numel, numel)
+                f._ensure_state(u)
+                for key, dst in (("master", u.master), ("m", u.m), ("v", u.v)):
+                    dst.zero_()
+                    if hi > lo:
+                        dst[:hi - lo].copy_(e[key][lo:hi].to(dst.device))
+            f._step_t = int(sd.get("step", 0))
+            return
+        if int(sd.get("world", f.world)) != f.world or int(sd.get("rank", f.rank)) != f.rank:
+            raise ValueError(f"per-rank optimizer shards written by rank {sd.get('rank')} of {sd.get('world')} cannot be "
+                             f"loaded on rank {f.rank} of {f.world}; use a consolidated (full_state_dict) checkpoint")
         f._step_t = int(sd.get("step", 0))
         for u in f.exec_units:
             s = sd.get("shards", {}).get(u.name)
             if s is None:
                 continue
+            if s["master"].numel() != u.master.numel():
+                raise ValueError(f"optimizer shard of unit {u.name} has {s['master'].numel()} elements, expected {u.master.numel()}")
             u.master.copy_(s["master"].to(u.master.device))
             if s.get("m") is not None:
                 f._ensure_state(u)

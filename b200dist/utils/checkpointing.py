@@ -74,10 +74,14 @@ def save_checkpoint(model, optimizer, epoch: int, path: str, rank: Optional[int]
     if rank is None:
         rank = _rank()
     state = full_state_dict(model)  # collective for sharded wrappers: all ranks enter
+    # a sharded optimizer (FSDP) gathers its fp32 master / moments into unsharded tensors - also a collective - so the
+    # single file never holds ONE rank's shards (which every rank would then load as its own)
+    gather_opt = getattr(optimizer, "full_state_dict", None)
+    opt_full = gather_opt() if callable(gather_opt) else None
     if rank == 0:
         d = os.path.dirname(os.path.abspath(path))
         os.makedirs(d, exist_ok=True)
-        opt_state = optimizer.state_dict() if optimizer is not None else {}
+        opt_state = opt_full if opt_full is not None else (optimizer.state_dict() if optimizer is not None else {})
         tmp = path + ".tmp"
         torch.save({"model_state_dict": state, "optimizer_state_dict": opt_state, "epoch": epoch}, tmp)
         os.replace(tmp, path)

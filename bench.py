@@ -109,6 +109,7 @@ def parse():
     ap.add_argument("--fsdp-ctas", type=int, default=64, help="CTAs per peer-memory collective kernel (FSDP)")
     ap.add_argument("--kernel-gather", action="store_true", help="FSDP all-gather with the SM pull kernel instead of DMA peer copies")
     ap.add_argument("--kernel-reduce", action="store_true", help="FSDP reduce-scatter+AdamW pulling over NVLink from the SMs instead of DMA staging")
+    ap.add_argument("--no-overlap-optimizer", action="store_true", help="1 GPU: run AdamW after backward instead of from the gradient hooks")
     ap.add_argument("--no-reshard", action="store_true", help="keep parameters gathered between forward and backward (ZeRO-2 style)")
     return ap.parse_args()
 
@@ -208,7 +209,9 @@ def run_b200dist(a, rank, world, local):
                      copy_engine_gather=not a.kernel_gather, copy_engine_reduce=not a.kernel_reduce)
         opt = model.build_optimizer("adamw", lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1)
     else:
-        opt = FusedAdamW(model.parameters(), lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1)
+        # one GPU: every parameter is updated from its gradient hook on a side stream while backward continues
+        opt = FusedAdamW(model.parameters(), lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1,
+                         overlap_backward=not a.no_overlap_optimizer)
     trainer = Trainer(model, opt)
     n_batches = a.steps + a.warmup
     xs, ys = make_batches(n_batches, a.batch_per_gpu, a.seq_len, vocab, rank, pinned=True)

@@ -48,17 +48,7 @@ __device__ __forceinline__ uint32_t* flag_row(const CommCtx& c, int owner, int w
 __device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t seq, const char* what) {
   uint64_t t0 = 0;
   uint32_t spins = 0;
-  while ((int32_t)(ld_acquire_sys(p) - seq) < 0) {
-    if ((++spins & 0xfffu) == 0) {
-      const uint64_t now = globaltimer_ns();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 5 * B200_WATCHDOG_NS) {
-        printf("b200dist watchdog: peer %s flag stuck (block %d thread %d want %u have %u)\n", what,
-               blockIdx.x, threadIdx.x, seq, *p);
-        __trap();
-      }
-    }
-  }
+  while ((int32_t)(ld_acquire_sys(p) - seq) < 0) peer_spin_check(t0, spins, what, seq, p);
 }
 
 // Steps 1+2.  Must be called by all threads of every block.
@@ -608,6 +598,8 @@ __global__ void __launch_bounds__(512, 1) comm_alltoall_kernel(CommCtx c, uint4*
 }  // namespace b200
 
 using namespace b200;
+
+B200_DEFINE_PEER_WD_SETTER(b200_peer_wd_set_comm)
 
 // ------------------------------------------------------------------ peer memory (CUDA IPC)
 B200_API int b200_peer_alloc(size_t bytes, void** out) {

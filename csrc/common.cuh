@@ -213,6 +213,45 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
+// ---------------------------------------------------------------------------
+// Cross-rank waits (flags another GPU raises).  Unlike an mbarrier inside one kernel, how long a peer takes
+// to arrive is not bounded by this kernel: a rank may be logging, evaluating, building a kernel or waiting for its
+// data loader.  The limit is therefore a RUN-TIME value (b200_set_peer_timeout; default 10 min, 0 = wait for ever)
+// and on expiry the waiter reports (device printf + a host-visible flag the host can poll while the kernel
+// still spins) and only traps if asked to.  One copy of the settings per translation unit, all set together by
+// b200_set_peer_timeout (runtime.cu) for the current device.
+// ---------------------------------------------------------------------------
+struct PeerWatchdog {
+  unsigned long long timeout_ns;   // 0 = never expire
+  int trap;                        // 1 = __trap() after reporting, 0 = report and keep waiting
+  unsigned int* host_flag;         // mapped pinned host word, incremented on every expiry (may be null)
+};
+static __device__ PeerWatchdog g_peer_wd = {600000000000ull, 1, nullptr};
+
+// Call once per spin iteration of a cross-rank wait.
+__device__ __forceinline__ void peer_spin_check(uint64_t& t0, uint32_t& spins, const char* what, uint32_t want,
+                                                const uint32_t* p) {
+  if ((++spins & 0xfffu) != 0) return;
+  const unsigned long long lim = g_peer_wd.timeout_ns;
+  if (lim == 0) return;
+  const uint64_t now = globaltimer_ns();
+  if (t0 == 0) { t0 = now; return; }
+  if (now - t0 <= lim) return;
+  printf("b200dist watchdog: waited %llu s for a peer (%s; block %d thread %d want %u have %u)\n",
+         (unsigned long long)((now - t0) / 1000000000ull), what, blockIdx.x, threadIdx.x, want,
+         *reinterpret_cast<const volatile uint32_t*>(p));
+  if (g_peer_wd.host_flag != nullptr) {
+    atomicAdd_system(g_peer_wd.host_flag, 1u);
+    __threadfence_system();
+  }
+  if (g_peer_wd.trap) __trap();
+  t0 = now;   // report again after another period
+}
+#define B200_DEFINE_PEER_WD_SETTER(NAME)                                                          \
+  int NAME(const b200::PeerWatchdog* wd) {                                                        \
+    return cudaMemcpyToSymbol(b200::g_peer_wd, wd, sizeof(b200::PeerWatchdog)) == cudaSuccess ? 0 : 1; \
+  }
+
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
   asm volatile(

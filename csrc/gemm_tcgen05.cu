@@ -131,16 +131,8 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, uint32_t smem_src, uint32_t
 __device__ __forceinline__ void spin_flag(const uint32_t* p, uint32_t want, bool sys) {
   uint64_t t0 = 0;
   uint32_t spins = 0;
-  while ((int32_t)((sys ? ld_acquire_sys_u32(p) : ld_acquire_gpu_u32(p)) - want) < 0) {
-    if ((++spins & 0xfffu) == 0) {
-      const uint64_t now = globaltimer_ns();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 5 * B200_WATCHDOG_NS) {
-        printf("b200dist watchdog: fused-gemm flag stuck (block %d want %u have %u)\n", blockIdx.x, want, *p);
-        __trap();
-      }
-    }
-  }
+  while ((int32_t)((sys ? ld_acquire_sys_u32(p) : ld_acquire_gpu_u32(p)) - want) < 0)
+    peer_spin_check(t0, spins, "fused gemm flag", want, p);
 }
 
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
@@ -913,6 +905,8 @@ static int pick_config(int M, int N, int sms) {
 }
 
 }  // namespace b200
+
+B200_DEFINE_PEER_WD_SETTER(b200_peer_wd_set_gemm)
 
 // D[M,N] = act(alpha * A.B^T + bias) + residual (+ D)         (fp32 accumulation)
 //   A logical [M,K]: a_mn_major=0 -> stored row-major [M,K] (row stride lda)

@@ -97,13 +97,7 @@ __device__ __forceinline__ uint32_t* mc_flag_row(const McCtx& c, int owner, int 
 __device__ __forceinline__ void mc_spin(const uint32_t* p, uint32_t seq) {
   uint64_t t0 = 0;
   uint32_t spins = 0;
-  while ((int32_t)(mc_ld_acquire(p) - seq) < 0) {
-    if ((++spins & 0xfffu) == 0) {
-      const uint64_t now = globaltimer_ns();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 5 * B200_WATCHDOG_NS) { printf("b200dist watchdog: nvls flag stuck (want %u have %u)\n", seq, *p); __trap(); }
-    }
-  }
+  while ((int32_t)(mc_ld_acquire(p) - seq) < 0) peer_spin_check(t0, spins, "nvls flag", seq, p);
 }
 
 // In-place all-reduce of the multicast buffer: rank r reduces and re-broadcasts elements [r * slice, (r+1) * slice).
@@ -230,6 +224,8 @@ __global__ void __launch_bounds__(512, 1) nvls_broadcast_kernel(McCtx c, const u
 }  // namespace b200
 
 using namespace b200;
+
+B200_DEFINE_PEER_WD_SETTER(b200_peer_wd_set_mc)
 
 // *supported = 1 when the current device can join NVSwitch multicast teams
 B200_API int b200_mc_supported(int* supported) {

@@ -19,7 +19,46 @@ void b200_set_error(const char* fmt, ...) {
 
 B200_API const char* b200_last_error() { return g_err; }
 
-B200_API int b200_version() { return 100; }
+B200_API int b200_version() { return 101; }
+
+// ---- cross-rank wait limit (see PeerWatchdog in common.cuh) ----
+int b200_peer_wd_set_comm(const b200::PeerWatchdog*);
+int b200_peer_wd_set_mc(const b200::PeerWatchdog*);
+int b200_peer_wd_set_gemm(const b200::PeerWatchdog*);
+static unsigned int* g_wd_host_flag = nullptr;   // mapped pinned word shared by every device of the process
+
+// Applies to the CURRENT device (settings live in per-device __device__ variables): call once per device used.
+// seconds <= 0 disables the limit; trap != 0 aborts the kernel (and with it the CUDA context) on expiry, trap == 0
+// only reports - device printf plus the counter b200_peer_timeout_count() reads - and keeps waiting.
+B200_API int b200_set_peer_timeout(double seconds, int trap) {
+  if (g_wd_host_flag == nullptr) {
+    void* h = nullptr;
+    if (cudaHostAlloc(&h, sizeof(unsigned int), cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+      g_wd_host_flag = reinterpret_cast<unsigned int*>(h);
+      *g_wd_host_flag = 0;
+    } else {
+      (void)cudaGetLastError();   // no pinned memory: the report is the device printf only
+    }
+  }
+  b200::PeerWatchdog wd;
+  wd.timeout_ns = seconds > 0 ? (unsigned long long)(seconds * 1e9) : 0ull;
+  wd.trap = trap ? 1 : 0;
+  wd.host_flag = nullptr;
+  if (g_wd_host_flag != nullptr) {
+    void* d = nullptr;
+    if (cudaHostGetDevicePointer(&d, g_wd_host_flag, 0) == cudaSuccess) wd.host_flag = reinterpret_cast<unsigned int*>(d);
+    else (void)cudaGetLastError();
+  }
+  if (b200_peer_wd_set_comm(&wd) || b200_peer_wd_set_mc(&wd) || b200_peer_wd_set_gemm(&wd)) {
+    b200_set_error("set_peer_timeout: cudaMemcpyToSymbol failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return B200_ERR_CUDA;
+  }
+  return B200_OK;
+}
+// Number of expired cross-rank waits reported so far in this process (readable while a kernel is still spinning).
+B200_API int b200_peer_timeout_count() {
+  return g_wd_host_flag ? (int)*reinterpret_cast<volatile unsigned int*>(g_wd_host_flag) : 0;
+}
 
 B200_API int b200_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin) {
   int dev = 0;

@@ -189,6 +189,13 @@ B200DIST_API int b200_peer_close(void* p);
 /* copy-engine (DMA) transfer between local and imported peer memory: the FSDP parameter all-gather path, no SMs used */
 B200DIST_API int b200_peer_memcpy(void* dst, const void* src, size_t bytes, cudaStream_t stream);
 
+/* ---- Limit on cross-rank waits (arrive / depart / NVLS / fused-GEMM ready flags / p2p mailboxes).  NCCL, which the
+ * reference relies on, tolerates arbitrary rank skew; so does this library by default: 10 minutes, then report and
+ * trap.  seconds <= 0 = wait for ever; trap = 0 = report (device printf + counter) and keep waiting.  Applies to the
+ * current device; b200_peer_timeout_count() can be polled from the host while a kernel is still spinning. */
+B200DIST_API int b200_set_peer_timeout(double seconds, int trap);
+B200DIST_API int b200_peer_timeout_count(void);
+
 /* ---- Point-to-point signalling for pipeline stage boundaries (replaces dist.isend/irecv,
  * scripts/04_pipeline_parallel_pp/01_manual_model_split.py:108-125): copy with b200_peer_memcpy, then signal; the
  * receiver's stream waits on its own flag word.  Flags are 32-bit sequence numbers that only grow. */

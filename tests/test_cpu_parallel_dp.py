@@ -258,3 +258,47 @@ def _fsdp_resume_worker(rank, world, tmpdir):
 
 def test_fsdp_sharded_checkpoint_exact_resume(tmp_path):
     run_distributed(_fsdp_resume_worker, 2, args=(str(tmp_path),))
+
+
+def _fsdp_consolidated_resume_worker(rank, world, tmpdir):
+    """a single-file checkpoint of an FSDP model + sharded optimizer must resume exactly (the file used to hold
+    rank 0's optimizer shards, which every rank then loaded over its own master weights)."""
+    from b200dist import ops
+    from b200dist.parallel import FSDP
+    from b200dist.utils import checkpointing as ck
+
+    data = _batches(4)
+
+    def run(fsdp, opt, batches):
+        for t in batches:
+            shard = t.chunk(world)[rank]
+            opt.zero_grad()
+            ops.cross_entropy(fsdp(shard[:, :-1]), shard[:, 1:]).backward()
+            opt.step()
+
+    a = FSDP(_toy_llama())
+    oa = a.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    run(a, oa, data[:2])
+    ck.save_checkpoint(a, oa, 2, f"{tmpdir}/one.pt")
+    run(a, oa, data[2:])
+    want = a.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    b = FSDP(_toy_llama())
+    ob = b.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    assert ck.load_checkpoint(b, ob, f"{tmpdir}/one.pt") == 2
+    assert b._step_t == 2
+    run(b, ob, data[2:])
+    got = b.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in want.items():
+        if not v.is_complex():
+            assert torch.allclose(got[k], v, atol=1e-6, rtol=1e-5), f"rank {rank} {k}: {(got[k] - v).abs().max()}"
+    # per-rank shards must refuse to load into another position
+    other = dict(oa.state_dict(), rank=(rank + 1) % world)
+    try:
+        ob.load_state_dict(other)
+        raise AssertionError("loading another rank's optimizer shards must raise")
+    except ValueError:
+        pass
+
+
+def test_fsdp_consolidated_checkpoint_with_sharded_optimizer_resumes(tmp_path):
+    run_distributed(_fsdp_consolidated_resume_worker, 2, args=(str(tmp_path),))

@@ -341,3 +341,25 @@ def test_capturable_adamw_matches_torch_and_tracks_lr():
     t = Trainer(m, FusedAdamW(m.parameters(), capturable=True), loss_fn=torch.nn.functional.cross_entropy, cuda_graph=True)
     t.train_step(torch.randn(2, 4), torch.tensor([0, 2]))
     assert t._graph is None and t.steps_done == 1
+
+
+def _single_box_worker(rank, world):
+    import os
+
+    import torch
+
+    from b200dist.comm.collectives import _agree_single_box
+
+    ok, why = _agree_single_box(None, torch.device("cpu"), world)
+    assert ok and why == "", (ok, why)
+    if rank == 1:
+        os.environ["B200DIST_FAKE_HOST"] = "another-node"
+    ok, why = _agree_single_box(None, torch.device("cpu"), world)   # every rank must reach the SAME verdict
+    assert not ok and "different hosts" in why, (ok, why)
+
+
+def test_communicator_refuses_peer_memory_across_hosts():
+    """a group whose ranks are not on one box must not exchange CUDA-IPC handles; all ranks agree to fall back."""
+    from tests.dist_utils import run_distributed
+
+    run_distributed(_single_box_worker, 2)

@@ -384,4 +384,38 @@ def group_models(results):
               f"({B/ms_tv*1e3:.0f} img/s)", flush=True)
 
 
-GROUPS.update({"conv": group_conv, "models": group_models})
+def group_optim_overlap(results):
+    """FusedAdamW(overlap_backward=True) - updates issued from the gradient hooks on a side stream - must produce the
+    weights of the plain optimizer (same kernels, same arithmetic per parameter)."""
+    import torch
+    from b200dist import ops
+    from b200dist.models.llama2 import ModelArgs, Transformer
+    from b200dist.ops import FusedAdamW
+    _check, _time = _h()
+    dev = "cuda"
+    a = dict(dim=512, n_layers=3, n_heads=4, vocab_size=2048, max_seq_len=256)
+    torch.manual_seed(0)
+    m0 = Transformer(ModelArgs(**a)).to(dev).to(torch.bfloat16)
+    m1 = Transformer(ModelArgs(**a)).to(dev).to(torch.bfloat16)
+    m1.load_state_dict(m0.state_dict())
+    o0 = FusedAdamW(m0.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    o1 = FusedAdamW(m1.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1, overlap_backward=True)
+    g = torch.Generator(device="cpu").manual_seed(3)
+    l0, l1 = [], []
+    for step in range(6):
+        tok = torch.randint(0, 2048, (4, 257), generator=g).to(dev)
+        x, y = tok[:, :-1], tok[:, 1:]
+        for m, o, ls in ((m0, o0, l0), (m1, o1, l1)):
+            o.zero_grad()
+            l = ops.cross_entropy(m(x), y); l.backward(); o.step()
+            ls.append(float(l))
+    torch.cuda.synchronize()
+    print("plain   ", [round(v, 4) for v in l0]); print("overlap ", [round(v, 4) for v in l1], flush=True)
+    # split-K weight gradients accumulate with fp32 atomics, so two runs agree to rounding, not bit for bit
+    _check("overlap_backward losses vs plain", torch.tensor(l1), torch.tensor(l0), 5e-3, 0.0, results)
+    assert all(p.grad is None for p in m1.parameters()), "overlap hooks must consume the gradients"
+    _check("overlap_backward weights (all)", torch.cat([p.reshape(-1).float() for p in m1.parameters()]),
+           torch.cat([p.reshape(-1).float() for p in m0.parameters()]), 4e-3, 0.0, results)
+
+
+GROUPS.update({"conv": group_conv, "models": group_models, "optim_overlap": group_optim_overlap})

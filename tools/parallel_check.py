@@ -83,6 +83,25 @@ def main():
         ok &= good
         if rank == 0:
             print(f"[{'PASS' if good else 'FAIL'}] FSDP reshard={reshard} final weights: max diff {err:.4g}", flush=True)
+    # ---------------- FSDP with fp32 parameters (staging sized by the element size, unfused optimizer path) ----------------
+    m32 = toy().to(dev)
+    o32 = FusedAdamW(m32.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    ref32 = []
+    for t in data:
+        t = t.to(dev)
+        o32.zero_grad()
+        l = ops.cross_entropy(m32(t[:, :-1]), t[:, 1:]); l.backward(); o32.step()
+        ref32.append(float(l))
+    f = FSDP(toy().to(dev))
+    opt = f.build_optimizer("adamw", lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    losses = []
+    for t in data:
+        t = t.chunk(world)[rank].to(dev)
+        opt.zero_grad()
+        l = ops.cross_entropy(f(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
+        lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+    report("FSDP fp32 parameters loss curve", losses, ref32, 0.02)
+    del m32, o32, f, opt
     # ---------------- FSDP + activation checkpointing + gradient accumulation (no_sync micro-steps) ----------------
     m = toy().to(dev).to(torch.bfloat16).enable_activation_checkpointing()
     f = FSDP(m)
