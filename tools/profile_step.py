@@ -17,6 +17,7 @@ ap.add_argument("--n-layers", type=int, default=8)
 ap.add_argument("--seq", type=int, default=4096)
 ap.add_argument("--resnet", default=None, help="profile a ResNet step instead (arch name)")
 ap.add_argument("--batch", type=int, default=128)
+ap.add_argument("--no-overlap", action="store_true", help="AdamW after backward instead of from the gradient hooks")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
@@ -46,7 +47,7 @@ if a.resnet:
         print(f"{t / 2e3:9.3f} ms/step {100 * t / tot:5.1f}%  x{c // 2:<4d} {k[:110]}")
     sys.exit(0)
 m = Transformer.from_name("llama2-7b", device=dev, dtype=torch.bfloat16, n_layers=a.n_layers, max_seq_len=a.seq)
-tr = Trainer(m, FusedAdamW(m.parameters(), lr=1e-4))
+tr = Trainer(m, FusedAdamW(m.parameters(), lr=1e-4, overlap_backward=not a.no_overlap))
 tok = torch.randint(0, 32000, (1, a.seq + 1), device=dev)
 for _ in range(3):
     tr.train_step(tok[:, :-1], tok[:, 1:])

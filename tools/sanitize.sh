@@ -7,7 +7,7 @@
 # synccheck: illegal barrier usage (mbarrier, __syncthreads under divergence)
 set -euo pipefail
 TOOL=${1:-memcheck}; shift || true
-EXPR=${1:-"rmsnorm or rope or swiglu or adamw or gemm"}
+EXPR=${1:-"norms or elementwise or simt"}   # test ids are the group names of tests/test_gpu_kernels.py
 cd "$(dirname "$0")/.."
 export B200DIST_DEBUG_SYNC=1
 exec compute-sanitizer --tool "$TOOL" --error-exitcode 9 --kernel-name-exclude kns=at:: \
