@@ -58,8 +58,8 @@ class Communicator:
         self.nvls_threshold = int(os.environ.get("B200DIST_NVLS_MIN_BYTES", str(1 << 20)))
         self._nvls = None if os.environ.get("B200DIST_NVLS", "1") != "0" else False
         self._nvls_buf = [None] * N_CHANNELS
-        # broadcast through the switch (multimem.st from the root): correctness-checked, not yet timed at 8 GPUs -> opt-in
-        self.nvls_broadcast = os.environ.get("B200DIST_NVLS_BROADCAST", "0") not in ("", "0")
+        # broadcast through the switch (multimem.st from the root: one egress copy, replicated by the NVSwitch)
+        self.nvls_broadcast = os.environ.get("B200DIST_NVLS_BROADCAST", "1") not in ("", "0")
         # through the switch a GPU moves (1 + 1/W) x bytes per direction, the pull two-shot 2 (W-1)/W x bytes: NVLS wins
         # from W = 4 (1.25 vs 1.5), loses at W = 2 (1.5 vs 1.0)
         self.nvls_min_world = int(os.environ.get("B200DIST_NVLS_MIN_WORLD", "4"))
@@ -279,9 +279,60 @@ class Communicator:
             return out
         nbytes = inp.numel() * inp.element_size()
         assert nbytes % 16 == 0, "all_gather shards must be multiples of 16 bytes"
+        if self._use_nvls(nbytes * self.world) and inp.is_contiguous() and out.is_contiguous() and inp.data_ptr() % 16 == 0 \
+                and out.data_ptr() % 16 == 0:
+            mc = self._nvls_region(channel, nbytes * self.world)
+            if mc is not None:
+                # every rank streams its shard through the switch once (multimem.st); no staging copy of the input
+                self._nvls_call("comm_allgather_nvls", channel, "all_gather_nvls", nbytes, L.ptr(inp), C.c_void_p(mc.mc_ptr),
+                                C.c_void_p(mc.local_ptr), L.ptr(out), LL(nbytes), I(self.max_ctas), self._s())
+                return out
         buf = self._stage(channel, nbytes)
         buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
         return self.all_gather_from(out, buf, 0, nbytes, channel)
+
+    # ------------------------------------------------------------------ NVLS helpers
+    def _use_nvls(self, total_bytes: int) -> bool:
+        return (self.world >= self.nvls_min_world and total_bytes >= self.nvls_threshold and self._nvls_ready())
+
+    def _nvls_region(self, channel: int, nbytes: int):
+        mc = self._nvls_buf[channel]
+        if mc is None or mc.nbytes < nbytes:
+            mc = self._nvls_alloc(channel, nbytes)
+        return mc
+
+    def _nvls_call(self, entry: str, channel: int, tag: str, nbytes: int, *args) -> None:
+        self._seq[channel] += 1
+        if self._order is not None:
+            self._order.record(channel, tag, nbytes)
+        L.call(entry, self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
+               U(self._seq[channel] & 0xFFFFFFFF), *args)
+
+    def all_gather_nvls_into(self, mc, offset_bytes: int, inp: torch.Tensor, channel: int = 1) -> None:
+        """Zero-copy all-gather into multicast buffer ``mc``: afterwards bytes [offset, offset + world * len(inp)) of EVERY
+        rank's replica hold the shards in rank order.  ``inp`` is any contiguous local tensor."""
+        nbytes = inp.numel() * inp.element_size()
+        assert nbytes % 16 == 0 and offset_bytes % 16 == 0 and offset_bytes + nbytes * self.world <= mc.nbytes
+        self._nvls_call("comm_allgather_nvls", channel, "all_gather_nvls", nbytes, L.ptr(inp),
+                        C.c_void_p(mc.mc_ptr + offset_bytes), C.c_void_p(mc.local_ptr + offset_bytes), C.c_void_p(0),
+                        LL(nbytes), I(self.max_ctas), self._s())
+
+    def reduce_scatter_nvls_from(self, out: torch.Tensor, mc, offset_bytes: int, in_dtype: torch.dtype, scale: float = 1.0,
+                                 channel: int = 2) -> torch.Tensor:
+        """out = scale * sum over ranks of slice ``rank`` of the [world * out.numel()] region at ``offset_bytes`` of
+        multicast buffer ``mc`` (every rank wrote its own input into its replica): reduced inside the NVSwitch."""
+        self._nvls_call("comm_reducescatter_nvls", channel, "reduce_scatter_nvls", out.numel(),
+                        C.c_void_p(mc.mc_ptr + offset_bytes), L.ptr(out), LL(out.numel()), F(scale),
+                        I(L.dtype_code(in_dtype)), I(L.dtype_code(out.dtype)), I(self.max_ctas), self._s())
+        return out
+
+    def rs_adamw_nvls_from(self, mc, offset_bytes: int, in_dtype: torch.dtype, n: int, grad_scale: float, master, lowp, m, v,
+                           *, lr, beta1, beta2, eps, wd, step, channel: int = 2) -> None:
+        """FSDP gradient step in ONE kernel: reduce-scatter inside the switch + scale + AdamW on the local shard."""
+        bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
+        self._nvls_call("comm_rs_adamw_nvls", channel, "rs_adamw_nvls", n, C.c_void_p(mc.mc_ptr + offset_bytes), LL(n),
+                        F(grad_scale), I(L.dtype_code(in_dtype)), L.ptr(master), L.ptr(lowp), L.ptr(m), L.ptr(v), F(lr),
+                        F(beta1), F(beta2), F(eps), F(wd), F(bc1), F(bc2), I(self.max_ctas), self._s())
 
     def all_gather_from(self, out: torch.Tensor, src: PeerBuffer, offset_bytes: int, nbytes: int,
                         channel: int = 1, copy_engine: bool = False) -> torch.Tensor:
@@ -317,7 +368,14 @@ class Communicator:
             out.reshape(-1).copy_(tmp * scale if scale != 1.0 else tmp)
             return out
         assert inp.numel() == n * self.world and n % 8 == 0
-        buf = self._stage(channel, inp.numel() * inp.element_size())
+        total = inp.numel() * inp.element_size()
+        if (self._use_nvls(total) and inp.dtype in (torch.bfloat16, torch.float32)
+                and out.dtype in (torch.bfloat16, torch.float32) and out.is_contiguous() and out.data_ptr() % 16 == 0):
+            mc = self._nvls_region(channel, total)
+            if mc is not None:
+                mc.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
+                return self.reduce_scatter_nvls_from(out, mc, 0, inp.dtype, scale, channel)
+        buf = self._stage(channel, total)
         buf.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
         return self.reduce_scatter_from(out, buf, 0, inp.dtype, scale, channel)
 

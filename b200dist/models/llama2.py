@@ -24,6 +24,7 @@ import torch.utils.checkpoint
 from torch import nn
 
 from .. import ops
+from . import fused_block
 
 
 @dataclass
@@ -175,7 +176,14 @@ class TransformerBlock(nn.Module):
         else:
             self.weight_init_std = 0.02 / (2 * args.n_layers) ** 0.5
 
+    # parameter groups a sharding wrapper should lay out back to back (one GEMM per group in the fused block node)
+    adjacent_param_groups = (("attention.wq.weight", "attention.wk.weight", "attention.wv.weight"),
+                             ("feed_forward.w1.weight", "feed_forward.w3.weight"))
+    fused = True   # run the block as ONE autograd node (models/fused_block.py) whenever it applies
+
     def forward(self, x, freqs_cis, pos_offset: int = 0):
+        if self.fused and fused_block.block_supported(self, x):
+            return fused_block.run_block(self, x, freqs_cis, pos_offset)
         # residual adds are fused into the wo / w2 GEMM epilogues
         h = self.attention(self.attention_norm(x), freqs_cis, residual=x, pos_offset=pos_offset)
         return self.feed_forward(self.ffn_norm(h), residual=h)
@@ -202,6 +210,15 @@ class Transformer(nn.Module):
         self.activation_checkpointing = False
         if init:
             self.init_weights()
+
+    def fuse_blocks(self, enabled: bool = True, pack: bool = True) -> "Transformer":
+        """Run every block as one hand-scheduled autograd node (default) and, with ``pack``, re-home q|k|v and w1|w3 into
+        contiguous buffers so each group is a single GEMM.  Call after the model has reached its device / dtype."""
+        for layer in self.layers:
+            layer.fused = enabled
+            if enabled and pack:
+                fused_block.pack_block_weights(layer)
+        return self
 
     def enable_activation_checkpointing(self, enabled: bool = True) -> "Transformer":
         self.activation_checkpointing = enabled
@@ -267,10 +284,14 @@ class Transformer(nn.Module):
                 torch.set_default_dtype(dtype)
             if device is not None:
                 with torch.device(device):
-                    return cls(args)
-            return cls(args)
+                    model = cls(args)
+            else:
+                model = cls(args)
         finally:
             torch.set_default_dtype(prev)
+        if device is not None and torch.device(device).type == "cuda":
+            model.fuse_blocks(True, pack=True)
+        return model
 
     def num_params(self) -> int:
         return sum(p.numel() for p in self.parameters())

@@ -89,7 +89,7 @@ def dtype_code(dt: torch.dtype) -> int:
 _NVTX = os.environ.get("B200DIST_NVTX", "0") not in ("", "0")
 
 # entry points that launch more than one kernel
-_KERNELS_PER_CALL = {"rmsnorm_bwd": 2, "layernorm_bwd": 3, "flash_attn_bwd": 3}   # (memsets are not counted)
+_KERNELS_PER_CALL = {"rmsnorm_bwd": 2, "rmsnorm_bwd_res": 2, "layernorm_bwd": 3, "flash_attn_bwd": 3}   # (memsets are not counted)
 
 
 def call(name: str, *args) -> None:

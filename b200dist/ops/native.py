@@ -121,6 +121,28 @@ def rope(x, freqs, pos_offset=0, backward=False, out=None):
     return y
 
 
+def rope_strided(x2d, freqs, S: int, n_heads: int, hd: int, pos_offset=0, backward=False, out=None):
+    """Rotate the first ``n_heads`` heads of every row of ``x2d`` [tokens, ld] (fused QKV buffer), in place by default."""
+    assert x2d.dim() == 2 and x2d.stride(1) == 1
+    y = x2d if out is None else out
+    L.call("rope_strided", L.ptr(x2d), L.ptr(y), L.ptr(freqs), LL(x2d.shape[0]), I(S), I(n_heads), I(hd), LL(x2d.stride(0)),
+           LL(y.stride(0)), I(pos_offset), I(int(backward)), I(L.dtype_code(x2d.dtype)), _s())
+    return y
+
+
+def rmsnorm_bwd_res(dy, x, w, rstd, dres, dw_out=None, accumulate_dw=False):
+    """dx = dres + d rmsnorm / dx, dw: the residual branch of a pre-norm block folded into the norm backward."""
+    D = x.shape[-1]
+    x2, dy2, r2 = x.reshape(-1, D), dy.reshape(-1, D), dres.reshape(-1, D)
+    assert x2.is_contiguous() and dy2.is_contiguous() and r2.is_contiguous()
+    dx = torch.empty_like(x2)
+    dw = torch.empty_like(w) if dw_out is None else dw_out
+    scratch = torch.empty((norm_bwd_partials(x2.shape[0]), D), device=x.device, dtype=torch.float32)
+    L.call("rmsnorm_bwd_res", L.ptr(dy2), L.ptr(x2), L.ptr(w), L.ptr(rstd), L.ptr(r2), L.ptr(dx), L.ptr(dw), L.ptr(scratch),
+           I(x2.shape[0]), I(D), I(int(accumulate_dw)), I(L.dtype_code(x.dtype)), _s())
+    return dx.view(x.shape), dw
+
+
 def swiglu_fwd(a, b):
     F_ = a.shape[-1]
     a2, b2 = a.reshape(-1, F_) if a.is_contiguous() else a, b.reshape(-1, F_) if b.is_contiguous() else b

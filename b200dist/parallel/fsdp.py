@@ -76,11 +76,34 @@ def _default_units(module: nn.Module):
     return units
 
 
+def _ordered_named_parameters(module: nn.Module):
+    """``named_parameters()`` with the module's ``adjacent_param_groups`` (tuples of parameter names) pulled together:
+    the members of a group follow each other in the unit's flat buffer, so a consumer can address them as ONE row-stacked
+    matrix (q|k|v and w1|w3 of a Llama block -> one GEMM each, models/fused_block.py)."""
+    items = list(module.named_parameters())
+    groups = getattr(module, "adjacent_param_groups", ())
+    if not groups:
+        return items
+    by_name = dict(items)
+    member = {n: g for g in groups for n in g if all(m in by_name for m in g)}
+    out, done = [], set()
+    for n, p in items:
+        if n in done:
+            continue
+        g = member.get(n)
+        if g is None:
+            out.append((n, p)); done.add(n)
+        else:
+            for m in g:
+                out.append((m, by_name[m])); done.add(m)
+    return out
+
+
 class FSDP(nn.Module):
     def __init__(self, module: nn.Module, process_group=None, units: Optional[List] = None,
                  reshard_after_forward: bool = True, fused_optimizer: bool = True,
                  comm_max_ctas: int = 64, sync_module_states: bool = True, copy_engine_gather: bool = True,
-                 copy_engine_reduce: bool = True, replicate_group=None):
+                 copy_engine_reduce: bool = True, replicate_group=None, nvls_reduce: bool = True):
         super().__init__()
         self.module = module
         self.comm = get_communicator(process_group)
@@ -115,7 +138,7 @@ class FSDP(nn.Module):
         self.units: List[_Unit] = []
         for uname, um in unit_mods:
             ps, ns = [], []
-            for n, p in um.named_parameters():
+            for n, p in _ordered_named_parameters(um):
                 if id(p) not in claimed:
                     claimed.add(id(p)); ps.append(p); ns.append(f"{uname}.{n}")
             if ps:
@@ -142,7 +165,20 @@ class FSDP(nn.Module):
         max_total = max(u.total for u in self.exec_units)
         if self.native and self.world > 1:
             esize = torch.empty((), dtype=self.dtype).element_size()
-            self.grad_stage = [self.comm.symmetric_buffer(max_total * esize) for _ in range(2)]
+            # From nvls_min_world ranks up the two staging buffers live behind an NVSwitch multicast object: the reduce-
+            # scatter is then ONE multimem.ld_reduce pass over this rank's slice, fused with AdamW (comm_rs_adamw_nvls) -
+            # no DMA staging of the peers' slabs, no scratch traffic in HBM, one arrive / depart instead of two barriers.
+            self.grad_stage, self.nvls_grads = None, False
+            if nvls_reduce and self.dtype == torch.bfloat16 and self.world >= self.comm.nvls_min_world:
+                bufs = [self.comm.nvls_buffer(max_total * esize) for _ in range(2)]
+                if all(b is not None for b in bufs):
+                    self.grad_stage, self.nvls_grads = bufs, True
+                else:
+                    for b in bufs:
+                        if b is not None:
+                            b.close()
+            if self.grad_stage is None:
+                self.grad_stage = [self.comm.symmetric_buffer(max_total * esize) for _ in range(2)]
             self._stage_events = [None, None]
         self._stage_idx = 0
         self._register_hooks()
@@ -231,6 +267,7 @@ class FSDP(nn.Module):
                 # backward pass, so it would pin one of the two staging buffers while the blocks rotate through them)
                 if self.native and self.world > 1 and p.dim() == 2 and p.dtype == torch.bfloat16 and u is not self.root_unit:
                     p._b200_grad_sink = self._make_sink(u, i)
+                    p._b200_group_sink = self._make_group_sink(u, i)
 
     def _next_unit(self, u: _Unit, step: int) -> Optional[_Unit]:
         j = u.index + step
@@ -306,6 +343,35 @@ class FSDP(nn.Module):
             return True
         return sink
 
+    def _make_group_sink(self, u: _Unit, slot0: int):
+        """Sink for several row-stacked parameters that are adjacent in the unit layout (q|k|v, w1|w3): ONE wgrad GEMM
+        writes [sum rows, K] straight into the staging buffer.  Declines (False) unless ``params`` are exactly the unit's
+        parameters slot0, slot0 + 1, ... laid out back to back."""
+        def sink(dy2d, x2d, params) -> bool:
+            n = len(params)
+            if slot0 + n > len(u.params) or any(u.params[slot0 + j] is not params[j] for j in range(n)):
+                return False
+            if not self.require_backward_grad_sync or any(p.grad is not None for p in params):
+                return False
+            if any(u.offsets[slot0 + j] + params[j].numel() != u.offsets[slot0 + j + 1] for j in range(n - 1)):
+                return False
+            if len({u.sink_written[slot0 + j] for j in range(n)}) != 1:
+                return False
+            self._begin_backward()
+            o, K = u.offsets[slot0], params[0].shape[1]
+            rows = sum(p.shape[0] for p in params)
+            view = self._claim_stage(u).tensor(self.dtype, 0, u.total)[o:o + rows * K].view(rows, K)
+            N.gemm(dy2d, x2d, a_mn=True, b_mn=True, out=view, accumulate=u.sink_written[slot0])
+            for j in range(n):
+                u.sink_written[slot0 + j] = True
+                if not u.grad_ready[slot0 + j]:
+                    u.grad_ready[slot0 + j] = True
+                    u.pending_grads -= 1
+            if u.pending_grads == 0:
+                self._reduce_unit(u)
+            return True
+        return sink
+
     def _reduce_unit(self, u: _Unit) -> None:
         u.pending_grads = -1  # launched
         if not self.require_backward_grad_sync:
@@ -336,7 +402,20 @@ class FSDP(nn.Module):
             with torch.cuda.stream(self.rs_stream):
                 self.rs_stream.wait_event(ev)
                 # the fused kernel writes a bf16 compute copy next to the fp32 master: bf16 models only
-                if self.fused_optimizer and hp is not None and hp["kind"] == "adamw" and self.dtype == torch.bfloat16:
+                if (self.nvls_grads and self.fused_optimizer and hp is not None and hp["kind"] == "adamw"):
+                    self._ensure_state(u)
+                    self.comm.rs_adamw_nvls_from(stage, 0, self.dtype, u.shard_numel, 1.0 / self.world, u.master, u.shard,
+                                                 u.m, u.v, lr=hp["lr"], beta1=hp["betas"][0], beta2=hp["betas"][1],
+                                                 eps=hp["eps"], wd=hp["weight_decay"], step=t, channel=2)
+                elif self.nvls_grads:
+                    if u.grad_shard is None:
+                        u.grad_shard = torch.zeros(u.shard_numel, dtype=torch.float32, device=self.device)
+                        self.comm.reduce_scatter_nvls_from(u.grad_shard, stage, 0, self.dtype, 1.0 / self.world, channel=2)
+                    else:
+                        tmp = torch.empty_like(u.grad_shard)
+                        self.comm.reduce_scatter_nvls_from(tmp, stage, 0, self.dtype, 1.0 / self.world, channel=2)
+                        u.grad_shard.add_(tmp)
+                elif self.fused_optimizer and hp is not None and hp["kind"] == "adamw" and self.dtype == torch.bfloat16:
                     self._ensure_state(u)
                     self.comm.rs_adamw_from(stage, 0, self.dtype, u.shard_numel, 1.0 / self.world, u.master, u.shard,
                                             u.m, u.v, lr=hp["lr"], beta1=hp["betas"][0], beta2=hp["betas"][1],

@@ -37,6 +37,35 @@ __global__ void rope_kernel(const T* __restrict__ x, T* __restrict__ y, const fl
   }
 }
 
+// Same rotation applied IN A FUSED QKV BUFFER: x is [tokens, ld] with the first n_heads * hd columns of every token
+// row holding the heads to rotate (q heads followed by k heads; the v columns after them are left alone), so one
+// launch covers q and k and nothing is copied out of the projection output.  y may alias x.
+template <typename T>
+__global__ void rope_strided_kernel(const T* __restrict__ x, T* __restrict__ y, const float2* __restrict__ freqs,
+                                    long long tokens, int S, int n_heads, int hd, long long ldx, long long ldy,
+                                    int pos_offset, float sin_sign) {
+  const int cph = hd >> 3;               // 8-element chunks per head
+  const int cpt = n_heads * cph;         // chunks per token
+  const long long n = tokens * cpt;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long tok = i / cpt;
+    const int c = (int)(i - tok * cpt);
+    const int s = (int)(tok % S) + pos_offset;
+    float v[8], o[8];
+    Vec8<T>::load(x + tok * ldx + c * 8, v);
+    const float2* f = freqs + (long long)s * (hd >> 1) + (c % cph) * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 cs = f[j];
+      const float sn = cs.y * sin_sign;
+      o[2 * j] = v[2 * j] * cs.x - v[2 * j + 1] * sn;
+      o[2 * j + 1] = v[2 * j] * sn + v[2 * j + 1] * cs.x;
+    }
+    Vec8<T>::store(y + tok * ldy + c * 8, o);
+  }
+}
+
 // ------------------------------- SwiGLU ------------------------------------
 template <typename T>
 __global__ void swiglu_fwd_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y,
@@ -276,6 +305,18 @@ B200_API int b200_rope(const void* x, void* y, const float* freqs, long long row
   const long long n = rows * (hd >> 3);
   B200_DISPATCH_DTYPE(dtype, T, (rope_kernel<T><<<ew_grid(n, 256), 256, 0, stream>>>(
       (const T*)x, (T*)y, (const float2*)freqs, n, S, H, hd, pos_offset, backward ? -1.f : 1.f)));
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Rotates the first n_heads heads of every [tokens, ld] row (see rope_strided_kernel); tokens = B * S, position = token % S.
+B200_API int b200_rope_strided(const void* x, void* y, const float* freqs, long long tokens, int S, int n_heads, int hd,
+                               long long ldx, long long ldy, int pos_offset, int backward, int dtype, cudaStream_t stream) {
+  if (tokens <= 0 || n_heads <= 0) return B200_OK;
+  if ((hd % 8) || (ldx % 8) || (ldy % 8)) { b200_set_error("rope_strided: head_dim and row strides must be multiples of 8"); return B200_ERR_SHAPE; }
+  const long long n = tokens * n_heads * (hd >> 3);
+  B200_DISPATCH_DTYPE(dtype, T, (rope_strided_kernel<T><<<ew_grid(n, 256), 256, 0, stream>>>(
+      (const T*)x, (T*)y, (const float2*)freqs, tokens, S, n_heads, hd, ldx, ldy, pos_offset, backward ? -1.f : 1.f)));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

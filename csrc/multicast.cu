@@ -166,6 +166,148 @@ __global__ void __launch_bounds__(512, 1) nvls_allreduce_kernel(McCtx c, T* __re
   }
 }
 
+// ---- shared prologue / epilogue of the NVLS kernels ----
+__device__ __forceinline__ void mc_arrive_and_wait(const McCtx& c) {
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
+  __syncthreads();
+}
+// Last CTA of the grid tells every peer "I am done" and waits until every peer said so.
+__device__ __forceinline__ void mc_depart(const McCtx& c, int* is_last_smem) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
+    *is_last_smem = (done == gridDim.x);
+    if (*is_last_smem) c.counter[192 + c.channel] = 0;
+  }
+  __syncthreads();
+  if (*is_last_smem) {
+    if (threadIdx.x < c.world) {
+      __threadfence_system();
+      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + c.rank, c.seq);
+      mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
+    }
+    __syncthreads();
+  }
+}
+// 8 consecutive elements of the sum over all ranks' replicas, as fp32 (bf16 inputs are accumulated in fp32 by the switch
+// and arrive rounded to bf16 once; fp32 inputs take two 16-byte requests).
+template <typename TIn>
+__device__ __forceinline__ void mm_ldred8(const TIn* p, float (&v)[8]) {
+  if constexpr (sizeof(TIn) == 2) {
+    const uint4 r = mm_ldred_bf16(p);
+    v[0] = bf16lo(r.x); v[1] = bf16hi(r.x); v[2] = bf16lo(r.y); v[3] = bf16hi(r.y);
+    v[4] = bf16lo(r.z); v[5] = bf16hi(r.z); v[6] = bf16lo(r.w); v[7] = bf16hi(r.w);
+  } else {
+    float a[4], b[4];
+    mm_ldred_f32(p, a);
+    mm_ldred_f32(p + 4, b);
+    v[0] = a[0]; v[1] = a[1]; v[2] = a[2]; v[3] = a[3]; v[4] = b[0]; v[5] = b[1]; v[6] = b[2]; v[7] = b[3];
+  }
+}
+
+// Reduce-scatter through the switch: every rank's input [world * n] sits at `mc` (multicast address of the region);
+// rank r reads slice r with multimem.ld_reduce - ONE read per element answered by the NVSwitch with the sum over all
+// replicas - scales and writes it to its ordinary output tensor.  The SMs never see the peers' partial values and each GPU
+// receives n elements instead of (world - 1) * n.
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(512, 1) nvls_reducescatter_kernel(McCtx c, const TIn* __restrict__ mc, TOut* __restrict__ out,
+                                                                   long long n, float scale) {
+  __shared__ int is_last;
+  mc_arrive_and_wait(c);
+  const long long n8 = n >> 3;
+  const TIn* base = mc + (long long)c.rank * n;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kU = sizeof(TIn) == 2 ? 8 : 4;   // 128 bytes of switch requests in flight per thread
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
+    float v[kU][8];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) if (i + u * stride < n8) mm_ldred8<TIn>(base + (i + u * stride) * 8, v[u]);
+#pragma unroll
+    for (int u = 0; u < kU; ++u)
+      if (i + u * stride < n8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[u][j] *= scale;
+        Vec8<TOut>::store(out + (i + u * stride) * 8, v[u]);
+      }
+  }
+  mc_depart(c, &is_last);   // the region may be refilled only after every rank has read its slice
+}
+
+// The FSDP gradient step as ONE kernel: reduce-scatter in the switch + 1/world scale + AdamW on this rank's shard
+// (fp32 master, moments) + bf16 write-back of the updated shard.  The summed gradient never exists in memory.
+template <typename TIn>
+__global__ void __launch_bounds__(512, 1) nvls_rs_adamw_kernel(McCtx c, const TIn* __restrict__ mc, long long n, float grad_scale,
+                                                              float* __restrict__ master, __nv_bfloat16* __restrict__ lowp,
+                                                              float* __restrict__ m, float* __restrict__ v, float lr,
+                                                              float beta1, float beta2, float eps, float wd, float bc1,
+                                                              float bc2_sqrt) {
+  __shared__ int is_last;
+  mc_arrive_and_wait(c);
+  const long long n8 = n >> 3;
+  const TIn* base = mc + (long long)c.rank * n;
+  const float step_size = lr / bc1, decay = 1.f - lr * wd;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int kU = 4;
+  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n8; i0 += stride * kU) {
+    float g[kU][8];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) if (i0 + u * stride < n8) mm_ldred8<TIn>(base + (i0 + u * stride) * 8, g[u]);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= n8) continue;
+      float pv[8], mv[8], vv[8];
+      Vec8<float>::load(master + i * 8, pv);
+      Vec8<float>::load(m + i * 8, mv);
+      Vec8<float>::load(v + i * 8, vv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float gj = g[u][j] * grad_scale;
+        mv[j] = beta1 * mv[j] + (1.f - beta1) * gj;
+        vv[j] = beta2 * vv[j] + (1.f - beta2) * gj * gj;
+        pv[j] = pv[j] * decay - step_size * (mv[j] / (sqrtf(vv[j]) / bc2_sqrt + eps));
+      }
+      Vec8<float>::store(master + i * 8, pv);
+      Vec8<float>::store(m + i * 8, mv);
+      Vec8<float>::store(v + i * 8, vv);
+      if (lowp) Vec8<__nv_bfloat16>::store(lowp + i * 8, pv);
+    }
+  }
+  mc_depart(c, &is_last);
+}
+
+// All-gather through the switch: rank r streams its shard (any local pointer) ONCE with multimem.st into slot r of the
+// region; the NVSwitch replicates it into every rank's replica, so a GPU sends `bytes` instead of (world - 1) * bytes.
+// When the kernel completes every replica holds all shards (the host entry point then copies the replica out if asked).
+__global__ void __launch_bounds__(512, 1) nvls_allgather_kernel(McCtx c, const uint4* __restrict__ src, uint4* __restrict__ mc,
+                                                               long long n16) {
+  __shared__ int is_last;
+  mc_arrive_and_wait(c);   // everybody has left the previous collective on this channel: the region is free
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  uint4* dst = mc + (long long)c.rank * n16;
+  constexpr int kU = 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride * kU) {
+    uint4 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) if (i + u * stride < n16) v[u] = src[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < kU; ++u)
+      if (i + u * stride < n16)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(dst + i + u * stride), "f"(__uint_as_float(v[u].x)), "f"(__uint_as_float(v[u].y)),
+                        "f"(__uint_as_float(v[u].z)), "f"(__uint_as_float(v[u].w)) : "memory");
+  }
+  // all ranks' stores have been issued and fenced: once the last CTA has seen every peer's depart flag - i.e. when this
+  // kernel completes - every replica is complete.  (The copy-out is a separate stream-ordered copy: CTAs that spun here
+  // for the peers' LAST CTA would hold their SM slots while those peers' unlaunched CTAs may be waiting for one.)
+  mc_depart(c, &is_last);
+}
+
 // Broadcast through the switch: the root streams its payload with multimem.st (one egress copy, replicated by the
 // NVSwitch into every rank's buffer), then releases a flag; the other ranks copy their local replica out.
 //   row 0 arrive/wait (all ranks): everybody has left the previous collective on this channel, the buffer is free
@@ -388,5 +530,85 @@ B200_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* counte
   nvls_broadcast_kernel<<<(int)g, 512, 0, stream>>>(c, (const uint4*)src, (uint4*)mc_ptr, (const uint4*)replica_ptr,
                                                      (uint4*)out, n16, root);
   B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+static int mc_fill_ctx(McCtx& c, const void* const* flag_ptrs, void* counter, int rank, int world, int channel, unsigned seq,
+                       const char* what) {
+  if (world < 2 || world > 8) { b200_set_error("%s: world %d out of range", what, world); return B200_ERR_LIMIT; }
+  memset(&c, 0, sizeof(c));
+  for (int r = 0; r < world; ++r) c.flags[r] = reinterpret_cast<uint32_t*>(const_cast<void*>(flag_ptrs[r]));
+  c.counter = reinterpret_cast<uint32_t*>(counter);
+  c.rank = rank; c.world = world; c.channel = channel; c.seq = seq;
+  return B200_OK;
+}
+static int mc_grid(long long items, int per_thread, int max_ctas) {
+  long long g = (items + 512LL * per_thread - 1) / (512LL * per_thread);
+  const int cap = max_ctas > 0 ? max_ctas : b200_sm_count();
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : (int)g;
+}
+
+// Reduce-scatter: every rank's input [world * n] (in_dtype) lies at mc_ptr inside the multicast buffer; out[n] (out_dtype)
+// = scale * sum over ranks of slice `rank`.  n % 8 == 0, mc_ptr 16-byte aligned.
+// Replaces dist.reduce_scatter_tensor (the collective FSDP issues for gradients).
+B200_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                          unsigned seq, const void* mc_ptr, void* out, long long n, float scale,
+                                          int in_dtype, int out_dtype, int max_ctas, cudaStream_t stream) {
+  McCtx c;
+  if (int rc = mc_fill_ctx(c, flag_ptrs, counter, rank, world, channel, seq, "reducescatter_nvls")) return rc;
+  if ((n & 7) || ((uintptr_t)mc_ptr & 15) || ((uintptr_t)out & 15)) {
+    b200_set_error("reducescatter_nvls: n %% 8 == 0 and 16-byte aligned pointers required"); return B200_ERR_SHAPE;
+  }
+  const int g = mc_grid(n >> 3, in_dtype == 0 ? 8 : 4, max_ctas);
+#define RSN(TI, TO) nvls_reducescatter_kernel<TI, TO><<<g, 512, 0, stream>>>(c, (const TI*)mc_ptr, (TO*)out, n, scale)
+  if (in_dtype == 0 && out_dtype == 0) RSN(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == 0 && out_dtype == 1) RSN(__nv_bfloat16, float);
+  else if (in_dtype == 1 && out_dtype == 1) RSN(float, float);
+  else if (in_dtype == 1 && out_dtype == 0) RSN(float, __nv_bfloat16);
+  else { b200_set_error("reducescatter_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+#undef RSN
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Fused FSDP gradient step through the switch (see nvls_rs_adamw_kernel): gradients [world * n] of in_dtype at mc_ptr.
+B200_API int b200_comm_rs_adamw_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                     unsigned seq, const void* mc_ptr, long long n, float grad_scale, int in_dtype,
+                                     float* master, void* lowp, float* m, float* v, float lr, float beta1, float beta2,
+                                     float eps, float wd, float bc1, float bc2, int max_ctas, cudaStream_t stream) {
+  McCtx c;
+  if (int rc = mc_fill_ctx(c, flag_ptrs, counter, rank, world, channel, seq, "rs_adamw_nvls")) return rc;
+  if ((n & 7) || ((uintptr_t)mc_ptr & 15)) { b200_set_error("rs_adamw_nvls: n %% 8 == 0 and a 16-byte aligned buffer required"); return B200_ERR_SHAPE; }
+  const int g = mc_grid(n >> 3, 4, max_ctas);
+  const float bc2s = sqrtf(bc2);
+  if (in_dtype == 0)
+    nvls_rs_adamw_kernel<__nv_bfloat16><<<g, 512, 0, stream>>>(c, (const __nv_bfloat16*)mc_ptr, n, grad_scale, master,
+                                                                (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
+  else if (in_dtype == 1)
+    nvls_rs_adamw_kernel<float><<<g, 512, 0, stream>>>(c, (const float*)mc_ptr, n, grad_scale, master, (__nv_bfloat16*)lowp,
+                                                        m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
+  else { b200_set_error("rs_adamw_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// All-gather: src = this rank's shard (`bytes`, multiple of 16, any local pointer); mc_ptr / replica_ptr = multicast
+// address and local replica of a [world * bytes] region; out = destination or NULL (use the replica in place).
+// Replaces dist.all_gather_into_tensor (FSDP parameter gathers, SP activation gathers).
+B200_API int b200_comm_allgather_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                      unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
+                                      long long bytes, int max_ctas, cudaStream_t stream) {
+  McCtx c;
+  if (int rc = mc_fill_ctx(c, flag_ptrs, counter, rank, world, channel, seq, "allgather_nvls")) return rc;
+  if ((bytes & 15) || ((uintptr_t)src & 15) || ((uintptr_t)out & 15) || ((uintptr_t)mc_ptr & 15)) {
+    b200_set_error("allgather_nvls: bytes %% 16 == 0 and 16-byte aligned pointers required"); return B200_ERR_SHAPE;
+  }
+  const long long n16 = bytes >> 4;
+  const int g = mc_grid(n16, 8, max_ctas);
+  nvls_allgather_kernel<<<g, 512, 0, stream>>>(c, (const uint4*)src, (uint4*)mc_ptr, n16);
+  B200_LAUNCH_CHECK();
+  if (out != nullptr)
+    B200_CUDA_CHECK(cudaMemcpyAsync(out, replica_ptr, (size_t)bytes * world, cudaMemcpyDeviceToDevice, stream));
   return B200_OK;
 }

@@ -54,7 +54,7 @@ template <typename T>
 __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                    const T* __restrict__ w, const float* __restrict__ rstd_in,
                                    T* __restrict__ dx, float* __restrict__ dw_partial, int rows, int D,
-                                   int add_to_dx) {
+                                   const T* addsrc) {   // addsrc: optional [rows, D] added to dx (may alias dx)
   __shared__ float red[33];
   const int nchunks = D >> 3;
   float dwacc[kMaxChunks][8];
@@ -96,9 +96,9 @@ __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = gv[i][j] * rstd - xv[i][j] * coef;
-        if (add_to_dx) {
+        if (addsrc != nullptr) {
           float prev[8];
-          Vec8<T>::load(dxr + c * 8, prev);
+          Vec8<T>::load(addsrc + (long long)row * D + c * 8, prev);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += prev[j];
         }
@@ -117,16 +117,36 @@ __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict
   }
 }
 
-// out[c] (+)= sum_p partial[p][c]
+// out[c] (+)= sum_p partial[p][c].  One CTA owns 64 columns: 16 float4 column groups x 16 partial-row lanes, each lane
+// strides over the partial rows with several independent loads in flight, then the 16 lanes meet in shared memory
+// (a single thread walking all ~450 partial rows was a chain of dependent L2 round trips: 15-70 us per call).
+constexpr int kColsumCols = 64;
 template <typename T>
-__global__ void colsum_partials_kernel(const float* __restrict__ partial, T* __restrict__ out,
-                                       int nparts, int D, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= D) return;
-  float s = 0.f;
-  for (int p = 0; p < nparts; ++p) s += partial[(long long)p * D + c];
-  if (accumulate) s += to_f<T>(out[c]);
-  out[c] = from_f<T>(s);
+__global__ void __launch_bounds__(256) colsum_partials_kernel(const float* __restrict__ partial, T* __restrict__ out,
+                                                              int nparts, int D, int accumulate) {
+  __shared__ float4 red[16][17];
+  const int cg = threadIdx.x & 15, pl = threadIdx.x >> 4;
+  const int c = (blockIdx.x * 16 + cg) * 4;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c < D) {
+#pragma unroll 4
+    for (int p = pl; p < nparts; p += 16) {
+      const float4 v = *reinterpret_cast<const float4*>(partial + (long long)p * D + c);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  }
+  red[pl][cg] = s;
+  __syncthreads();
+  if (pl == 0 && c < D) {
+#pragma unroll
+    for (int i = 1; i < 16; ++i) { const float4 v = red[i][cg]; s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+    float r[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (accumulate) r[j] += to_f<T>(out[c + j]);
+      out[c + j] = from_f<T>(r[j]);
+    }
+  }
 }
 
 // ------------------------------- LayerNorm ---------------------------------
@@ -292,9 +312,27 @@ B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, cons
   const int grid = b200_norm_bwd_partials(rows);
   B200_DISPATCH_DTYPE(dtype, T, {
     rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
-                                                        (T*)dx, scratch, rows, D, add_to_dx);
-    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
+                                                        (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
                                                                     accumulate_dw);
+  });
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Same, with the residual branch of a pre-norm block folded in: dx = dres + d/dx (dres: [rows, D], may alias dx).
+// Saves the separate elementwise add autograd would otherwise run for x -> {norm, residual}.
+B200_API int b200_rmsnorm_bwd_res(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                                  void* dx, void* dw, float* scratch, int rows, int D, int accumulate_dw, int dtype,
+                                  cudaStream_t stream) {
+  if (rows <= 0) return B200_OK;
+  int threads;
+  if (int rc = norm_threads(D, &threads)) return rc;
+  const int grid = b200_norm_bwd_partials(rows);
+  B200_DISPATCH_DTYPE(dtype, T, {
+    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                        (T*)dx, scratch, rows, D, (const T*)dres);
+    colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D, accumulate_dw);
   });
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -326,9 +364,9 @@ B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, co
   B200_DISPATCH_DTYPE(dtype, T, {
     layernorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w,
                                                           mean, rstd, (T*)dx, pw, pb, rows, D);
-    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(pw, (T*)dw, grid, D, accumulate);
+    colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(pw, (T*)dw, grid, D, accumulate);
     if (db)
-      colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(pb, (T*)db, grid, D, accumulate);
+      colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(pb, (T*)db, grid, D, accumulate);
   });
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -398,8 +436,8 @@ B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void*
   const int grid = rows < kNoAllocMaxPartials ? rows : kNoAllocMaxPartials;  // grid * D <= array size
   B200_DISPATCH_DTYPE(dtype, T, {
     rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
-                                                        (T*)dx, scratch, rows, D, add_to_dx);
-    colsum_partials_kernel<T><<<ceil_div(D, 256), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
+                                                        (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
                                                                     accumulate_dw);
   });
   B200_LAUNCH_CHECK();

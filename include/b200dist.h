@@ -86,6 +86,10 @@ B200DIST_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* 
 B200DIST_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
                               void* dx, void* dw, float* scratch, int rows, int D, int add_to_dx,
                               int accumulate_dw, int dtype, cudaStream_t stream);
+/* dx = dres + d/dx: the residual branch of a pre-norm transformer block folded into the norm backward (dres may alias dx) */
+B200DIST_API int b200_rmsnorm_bwd_res(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                                      void* dx, void* dw, float* scratch, int rows, int D, int accumulate_dw, int dtype,
+                                      cudaStream_t stream);
 /* No counterpart in the reference.  Same result as b200_rmsnorm_bwd, but the partial-sum scratch is a fixed
  * 4.6 MiB array inside the library instead of a caller buffer, for hosts that cannot allocate device memory
  * (no allocator of their own, HBM fully pre-partitioned, or cudaMalloc banned from the hot loop).  Calls
@@ -106,6 +110,11 @@ B200DIST_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w
  * RoPE llama2_model.py:73-100; SwiGLU :266-267; nn.Embedding :374,440; CrossEntropyLoss scripts/main.py:308 */
 B200DIST_API int b200_rope(const void* x, void* y, const float* freqs, long long rows, int S, int H,
                        int hd, int pos_offset, int backward, int dtype, cudaStream_t stream);
+/* the same rotation inside a fused QKV projection output: rotates the first n_heads heads (q then k) of every
+ * [tokens, ld] row in one launch, in place if y == x (apply_rotary_emb on xq and xk, llama2_model.py:73-100) */
+B200DIST_API int b200_rope_strided(const void* x, void* y, const float* freqs, long long tokens, int S, int n_heads, int hd,
+                                   long long ldx, long long ldy, int pos_offset, int backward, int dtype,
+                                   cudaStream_t stream);
 B200DIST_API int b200_swiglu_fwd(const void* a, const void* b, void* y, long long rows, int F,
                              long long lda, long long ldb, long long ldy, int dtype,
                              cudaStream_t stream);
@@ -262,5 +271,18 @@ B200DIST_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* co
 B200DIST_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                       unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
                                       long long bytes, int root, int max_ctas, cudaStream_t stream);
+/* reduce-scatter / fused reduce-scatter + AdamW / all-gather through the NVSwitch (multimem.ld_reduce, multimem.st):
+ * the region at mc_ptr is [world * n] elements (resp. [world * bytes]) inside a buffer from b200_mc_bind_map; replace
+ * dist.reduce_scatter_tensor / dist.all_gather_into_tensor and FSDP's gradient + optimizer step */
+B200DIST_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                              unsigned seq, const void* mc_ptr, void* out, long long n, float scale,
+                                              int in_dtype, int out_dtype, int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_rs_adamw_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                         unsigned seq, const void* mc_ptr, long long n, float grad_scale, int in_dtype,
+                                         float* master, void* lowp, float* m, float* v, float lr, float beta1, float beta2,
+                                         float eps, float wd, float bc1, float bc2, int max_ctas, cudaStream_t stream);
+B200DIST_API int b200_comm_allgather_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
+                                          unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
+                                          long long bytes, int max_ctas, cudaStream_t stream);
 
 #endif  /* B200DIST_H_ */

@@ -125,6 +125,57 @@ def main():
         ref = src.clone(); dist.all_reduce(ref)
         xr.copy_(src); comm.all_reduce(xr, algo=4)
         check("all_reduce NVLS registered tensor (in place, zero copy)", xr, ref)
+    # ---- reduce-scatter / all-gather through the switch (multimem.ld_reduce / multimem.st), forced on at any world size ----
+    prev_nv = (comm.nvls_min_world, comm.nvls_threshold)
+    comm.nvls_min_world, comm.nvls_threshold = 2, 0
+    if comm._nvls_ready():
+        for dt in (torch.float32, torch.bfloat16):
+            for n in (8 * 33, 1 << 18, (1 << 20) + 8 * 5):
+                for rep in range(2):    # back-to-back calls reuse the multicast region: the depart handshake must hold
+                    xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+                    r = torch.empty(n, device=dev, dtype=dt); dist.reduce_scatter_tensor(r, xin)
+                    o = torch.empty(n, device=dev, dtype=dt); comm.reduce_scatter(o, xin)
+                    check(f"reduce_scatter NVLS {dt} n={n} call {rep}", o, r)
+                    o32 = torch.empty(n, device=dev, dtype=torch.float32); comm.reduce_scatter(o32, xin, scale=0.5)
+                    check(f"reduce_scatter NVLS scale+cast {dt} n={n} call {rep}", o32, r.float() * 0.5)
+                    x = torch.randint(-8, 8, (n,), device=dev).to(dt)
+                    ref = torch.empty(n * world, device=dev, dtype=dt); dist.all_gather_into_tensor(ref, x)
+                    out = torch.empty(n * world, device=dev, dtype=dt); comm.all_gather(out, x)
+                    check(f"all_gather NVLS {dt} n={n} call {rep}", out, ref)
+        # zero-copy forms on a dedicated multicast buffer (what FSDP uses for its gradient staging)
+        n = 1 << 16
+        mcb = comm.nvls_buffer(n * world * 4)
+        if mcb is not None:
+            gi = torch.randint(-8, 8, (n * world,), device=dev).to(torch.bfloat16)
+            r = torch.empty(n, device=dev, dtype=torch.float32); dist.reduce_scatter_tensor(r, gi.float())
+            mcb.tensor(torch.bfloat16, 0, n * world).copy_(gi)
+            o = torch.empty(n, device=dev, dtype=torch.float32)
+            comm.reduce_scatter_nvls_from(o, mcb, 0, torch.bfloat16, 1.0)
+            check("reduce_scatter NVLS zero-copy bf16 -> fp32", o, r)
+            sh = torch.randint(-8, 8, (n,), device=dev).to(torch.bfloat16)
+            ref = torch.empty(n * world, device=dev, dtype=torch.bfloat16); dist.all_gather_into_tensor(ref, sh)
+            comm.all_gather_nvls_into(mcb, 0, sh)
+            torch.cuda.synchronize()
+            check("all_gather NVLS zero-copy (replica in place)", mcb.tensor(torch.bfloat16, 0, n * world), ref)
+            # fused reduce-scatter (in the switch) + AdamW vs the pull kernel on the same gradients
+            g2 = torch.randn(n * world, device=dev).bfloat16()
+            p0 = torch.randn(n, device=dev)
+            pb = comm.symmetric_buffer(g2.numel() * 2); pb.tensor(torch.bfloat16).copy_(g2)
+            ms0, mm0, vv0 = p0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+            lp0 = torch.empty(n, device=dev, dtype=torch.bfloat16)
+            comm.rs_adamw_from(pb, 0, torch.bfloat16, n, 1.0 / world, ms0, lp0, mm0, vv0, lr=1e-2, beta1=0.9, beta2=0.95,
+                               eps=1e-8, wd=0.1, step=1)
+            mcb.tensor(torch.bfloat16, 0, n * world).copy_(g2)
+            ms1, mm1, vv1 = p0.clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+            lp1 = torch.empty(n, device=dev, dtype=torch.bfloat16)
+            comm.rs_adamw_nvls_from(mcb, 0, torch.bfloat16, n, 1.0 / world, ms1, lp1, mm1, vv1, lr=1e-2, beta1=0.9,
+                                    beta2=0.95, eps=1e-8, wd=0.1, step=1)
+            # the switch rounds the fp32 sum to bf16 once; step 1 of Adam is sign-like, so compare the moments
+            check("rs_adamw NVLS exp_avg vs pull kernel", mm1, mm0, 2e-2 * float(mm0.abs().max()))
+            check("rs_adamw NVLS master vs pull kernel", ms1, ms0, 2.5e-2)
+    elif rank == 0:
+        print("[INFO] NVLS unavailable: reduce-scatter / all-gather through the switch not checked", flush=True)
+    comm.nvls_min_world, comm.nvls_threshold = prev_nv
     # fused reduce-scatter + AdamW vs (NCCL reduce-scatter, torch AdamW)
     n = 1 << 16
     g = torch.randn(n * world, device=dev).bfloat16()

@@ -418,4 +418,50 @@ def group_optim_overlap(results):
            torch.cat([p.reshape(-1).float() for p in m0.parameters()]), 4e-3, 0.0, results)
 
 
-GROUPS.update({"conv": group_conv, "models": group_models, "optim_overlap": group_optim_overlap})
+def group_fused_block(results):
+    """models/fused_block.py (one autograd node per Llama block: fused q|k|v and w1|w3 GEMMs, in-place strided RoPE,
+    residual gradient folded into the RMSNorm backward) against the module-by-module path on the same weights: loss,
+    logits and every parameter gradient, for packed weights, unpacked weights (accumulate epilogues) and GQA."""
+    import torch
+    from b200dist import ops
+    from b200dist.models.llama2 import ModelArgs, Transformer
+    _check, _time = _h()
+    dev = "cuda"
+    for name, cfg, pack in (("packed", dict(dim=512, n_layers=2, n_heads=4, vocab_size=1024, max_seq_len=512), True),
+                            ("unpacked", dict(dim=512, n_layers=2, n_heads=4, vocab_size=1024, max_seq_len=512), False),
+                            ("gqa hd64", dict(dim=512, n_layers=2, n_heads=8, n_kv_heads=2, vocab_size=1024, max_seq_len=512), True)):
+        torch.manual_seed(0)
+        ref = Transformer(ModelArgs(**cfg)).to(dev).to(torch.bfloat16).fuse_blocks(False)
+        fus = Transformer(ModelArgs(**cfg)).to(dev).to(torch.bfloat16)
+        fus.load_state_dict(ref.state_dict())
+        fus.fuse_blocks(True, pack=pack)
+        tok = torch.randint(0, 1024, (2, 385), device=dev)
+        x, y = tok[:, :-1], tok[:, 1:]
+        lo_r = ref(x); l_r = ops.cross_entropy(lo_r, y); l_r.backward()
+        lo_f = fus(x); l_f = ops.cross_entropy(lo_f, y); l_f.backward()
+        torch.cuda.synchronize()
+        _check(f"fused block [{name}] logits", lo_f, lo_r, 3e-2, 2e-2, results)
+        _check(f"fused block [{name}] loss", l_f.detach().reshape(1), l_r.detach().reshape(1), 2e-3, 0.0, results)
+        for (n, pf), (_, pr) in zip(fus.named_parameters(), ref.named_parameters()):
+            assert pf.grad is not None, n
+            g_abs = float(pr.grad.float().abs().max())
+            _check(f"fused block [{name}] grad {n}", pf.grad, pr.grad, 0.02 * g_abs + 1e-6, 3e-2, results)
+    # timing of one 7B-shape block, forward + backward, both paths
+    cfg = dict(dim=4096, n_layers=1, n_heads=32, vocab_size=1024, max_seq_len=4096)
+    for fused in (False, True):
+        torch.manual_seed(0)
+        m = Transformer(ModelArgs(**cfg)).to(dev).to(torch.bfloat16).fuse_blocks(fused, pack=True)
+        h = torch.randn(1, 4096, 4096, device=dev, dtype=torch.bfloat16, requires_grad=True)
+        blk = m.layers[0]
+
+        def step():
+            out = blk(h, m.freqs_cis)
+            out.backward(out)
+            for p in blk.parameters():
+                p.grad = None
+        ms = _time(step, iters=10, warmup=3)
+        print(f"[TIME] llama-7b block fwd+bwd S4096 {'fused node' if fused else 'module-by-module'}: {ms:.3f} ms", flush=True)
+
+
+GROUPS.update({"conv": group_conv, "models": group_models, "optim_overlap": group_optim_overlap,
+               "fused_block": group_fused_block})
