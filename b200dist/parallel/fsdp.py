@@ -128,6 +128,7 @@ class FSDP(nn.Module):
             self.ag_stream = torch.cuda.Stream(self.device)
             self.rs_stream = torch.cuda.Stream(self.device)
         self._opt = None
+        self.nvls_grads = False
         self._step_t = 0
         self._in_backward = False
         self._bwd_seen = 0

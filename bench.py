@@ -110,6 +110,8 @@ def parse():
     ap.add_argument("--kernel-gather", action="store_true", help="FSDP all-gather with the SM pull kernel instead of DMA peer copies")
     ap.add_argument("--kernel-reduce", action="store_true", help="FSDP reduce-scatter+AdamW pulling over NVLink from the SMs instead of DMA staging")
     ap.add_argument("--no-overlap-optimizer", action="store_true", help="1 GPU: run AdamW after backward instead of from the gradient hooks")
+    ap.add_argument("--no-nvls-reduce", action="store_true", help="FSDP: keep the gradient staging in plain peer memory (DMA / pull reduce) instead of NVSwitch multicast memory")
+    ap.add_argument("--nvls-min-world", type=int, default=None, help="smallest world size that uses the NVSwitch (multimem) paths (default 4)")
     ap.add_argument("--no-reshard", action="store_true", help="keep parameters gathered between forward and backward (ZeRO-2 style)")
     return ap.parse_args()
 
@@ -203,9 +205,12 @@ def run_b200dist(a, rank, world, local):
     model = Transformer.from_name(a.model, device=dev, dtype=torch.bfloat16, **overrides)
     vocab = model.vocab_size
     if world > 1:
+        from b200dist.comm import get_communicator
         from b200dist.parallel.fsdp import FSDP
 
-        model = FSDP(model, comm_max_ctas=a.fsdp_ctas, reshard_after_forward=not a.no_reshard, sync_module_states=False,
+        if a.nvls_min_world is not None:
+            get_communicator(None).nvls_min_world = a.nvls_min_world
+        model = FSDP(model, nvls_reduce=not a.no_nvls_reduce, comm_max_ctas=a.fsdp_ctas, reshard_after_forward=not a.no_reshard, sync_module_states=False,
                      copy_engine_gather=not a.kernel_gather, copy_engine_reduce=not a.kernel_reduce)
         opt = model.build_optimizer("adamw", lr=a.lr, betas=(0.9, 0.95), weight_decay=0.1)
     else:

@@ -113,6 +113,8 @@ def main():
     ap.add_argument("--kernel-gather", action="store_true")
     ap.add_argument("--kernel-reduce", action="store_true")
     ap.add_argument("--fsdp-ctas", type=int, default=64)
+    ap.add_argument("--nvls-min-world", type=int, default=None)
+    ap.add_argument("--no-nvls-reduce", action="store_true")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -127,9 +129,12 @@ def main():
     torch.manual_seed(0)
     model = Transformer.from_name("llama2-7b", device=dev, dtype=torch.bfloat16, n_layers=a.n_layers, max_seq_len=a.seq)
     if world > 1:
+        from b200dist.comm import get_communicator
         from b200dist.parallel.fsdp import FSDP
 
-        model = FSDP(model, comm_max_ctas=a.fsdp_ctas, sync_module_states=False, copy_engine_gather=not a.kernel_gather,
+        if a.nvls_min_world is not None:
+            get_communicator(None).nvls_min_world = a.nvls_min_world
+        model = FSDP(model, nvls_reduce=not a.no_nvls_reduce, comm_max_ctas=a.fsdp_ctas, sync_module_states=False, copy_engine_gather=not a.kernel_gather,
                      copy_engine_reduce=not a.kernel_reduce)
         opt = model.build_optimizer("adamw", lr=3e-4, betas=(0.9, 0.95), weight_decay=0.1)
     else:
@@ -152,7 +157,7 @@ def main():
         out_dir.mkdir(exist_ok=True)
         with open(out_dir / f"fsdp_timeline_{world}gpu.txt", "w") as f:
             print(f"# llama2-7b shape, {a.n_layers} layers, seq {a.seq}, world {world}, rank 0; "
-                  f"gather={'kernel' if a.kernel_gather else 'copy-engine'} reduce={'kernel' if a.kernel_reduce else 'copy-engine'}",
+                  f"gather={'kernel' if a.kernel_gather else 'copy-engine'} reduce={'nvls' if getattr(model, 'nvls_grads', False) else ('kernel' if a.kernel_reduce else 'copy-engine')}",
                   file=f)
             summarise(path, a.steps, f)
         print((out_dir / f"fsdp_timeline_{world}gpu.txt").read_text())

@@ -83,6 +83,23 @@ def main():
         ok &= good
         if rank == 0:
             print(f"[{'PASS' if good else 'FAIL'}] FSDP reshard={reshard} final weights: max diff {err:.4g}", flush=True)
+    # ---------------- FSDP with the gradient staging in NVSwitch multicast memory (default from 4 ranks; forced here) ------
+    from b200dist.comm import get_communicator as _gc0
+
+    _c0 = _gc0(None); _prev0 = _c0.nvls_min_world; _c0.nvls_min_world = 2
+    m = toy().to(dev).to(torch.bfloat16)
+    f = FSDP(m)
+    _c0.nvls_min_world = _prev0
+    opt = f.build_optimizer("adamw", lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
+    losses = []
+    for t in data:
+        t = t.chunk(world)[rank].to(dev)
+        opt.zero_grad()
+        l = ops.cross_entropy(f(t[:, :-1]), t[:, 1:]); l.backward(); opt.step()
+        lt = l.detach().clone(); dist.all_reduce(lt); losses.append(float(lt) / world)
+    report(f"FSDP gradients reduced in the switch + AdamW in one kernel (NVLS staging: {f.nvls_grads}) loss curve", losses,
+           ref_losses, 0.02)
+    del f, opt, m
     # ---------------- FSDP with fp32 parameters (staging sized by the element size, unfused optimizer path) ----------------
     m32 = toy().to(dev)
     o32 = FusedAdamW(m32.parameters(), lr=1e-3, betas=(0.9, 0.95), weight_decay=0.1)
