@@ -78,11 +78,13 @@ class _Conv2dFn(Function):
         Cp = (Cc + 7) // 8 * 8
         direct = KH == 1 and KW == 1 and stride == 1 and pad == 0 and Cp == Cc
         out_dtype = torch.float32 if x.dtype == torch.float32 else _BF16
-        igemm = (_IGEMM and not direct and stride == 1 and Cc % 64 == 0 and K % 8 == 0 and out_dtype == _BF16
+        igemm = (_IGEMM and not direct and stride in (1, 2) and Cc % 64 == 0 and K % 8 == 0 and out_dtype == _BF16
                  and Ho > 0 and Wo > 0)
         if igemm:
+            # stride 2 (3x3 s2 and the 1x1 s2 shortcut of a ResNet stage transition): same kernel, the tensor map steps
+            # over every second pixel
             y = N.conv2d_igemm(xh.contiguous(), _w_matrix(w, Cc), KH, KW, pad,
-                               bias=bias.to(_BF16) if bias is not None else None)
+                               bias=bias.to(_BF16) if bias is not None else None, stride=stride)
             ctx.save_for_backward(xh, w, None)
             ctx.geom = (stride, pad, Ho, Wo, Cp, direct, x.dtype, bias is not None, K)
             ctx.igemm = True
@@ -116,7 +118,7 @@ class _Conv2dFn(Function):
         wm = _w_matrix(w, Cp)
         if Kp != K:
             wm = F.pad(wm, (0, 0, 0, Kp - K))
-        if ctx.needs_input_grad[0] and ctx.igemm and K % 64 == 0 and Cc % 8 == 0:
+        if ctx.needs_input_grad[0] and ctx.igemm and stride == 1 and K % 64 == 0 and Cc % 8 == 0:
             # input gradient = stride-1 conv of dY with the spatially flipped, channel-transposed filter, pad' = K - 1 - pad
             wflip = w.flip(2, 3).permute(1, 2, 3, 0).reshape(Cc, KH * KW * K).to(_BF16).contiguous()
             dxh = N.conv2d_igemm(dyh.view(Nn, Ho, Wo, K), wflip, KH, KW, KH - 1 - pad)
@@ -131,7 +133,7 @@ class _Conv2dFn(Function):
                        I(Ho), I(Wo), I(0), _s())
             dx = _nchw_view(dxh).to(x_dtype)
         if ctx.needs_input_grad[1] and ctx.igemm and _IGEMM_WGRAD and Nn * Ho * Wo >= 128:
-            dwm = N.conv2d_igemm_wgrad(xh.contiguous(), dyh.view(Nn, Ho, Wo, K), KH, KW, pad)     # [K, KH*KW*C] fp32
+            dwm = N.conv2d_igemm_wgrad(xh.contiguous(), dyh.view(Nn, Ho, Wo, K), KH, KW, pad, stride=stride)  # [K, KH*KW*C] fp32
             dw = dwm.view(K, KH, KW, Cc).permute(0, 3, 1, 2).to(w.dtype)
         elif ctx.needs_input_grad[1]:
             a = xh.reshape(Nn * H * W, Cc) if direct else (col if col is not None else

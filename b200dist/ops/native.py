@@ -321,20 +321,20 @@ def sgd_step(p, g, buf, *, lr, momentum, wd, first_step, grad_scale=1.0, p_lowp=
            LL(p.numel()), F(lr), F(momentum), F(wd), F(grad_scale), I(int(first_step)), _s())
 
 
-def conv2d_igemm(x_nhwc, wmat, KH: int, KW: int, pad: int, bias=None, residual=None, act: int = 0):
-    """Implicit-GEMM stride-1 convolution: x [N, H, W, C] bf16 contiguous, wmat [Cout, KH * KW * C] bf16 -> [N, Ho, Wo, Cout].
-    C % 64 == 0 and Cout % 8 == 0 (see csrc/gemm_tcgen05.cu, launch_conv_igemm)."""
+def conv2d_igemm(x_nhwc, wmat, KH: int, KW: int, pad: int, bias=None, residual=None, act: int = 0, stride: int = 1):
+    """Implicit-GEMM convolution (stride 1 or 2): x [N, H, W, C] bf16 contiguous, wmat [Cout, KH * KW * C] bf16 ->
+    [N, Ho, Wo, Cout].  C % 64 == 0 and Cout % 8 == 0 (see csrc/gemm_tcgen05.cu, launch_conv_igemm)."""
     Nn, H, W, Cc = x_nhwc.shape
     Cout = wmat.shape[0]
     assert x_nhwc.is_contiguous() and wmat.is_contiguous() and wmat.shape[1] == KH * KW * Cc
-    Ho, Wo = H + 2 * pad - KH + 1, W + 2 * pad - KW + 1
+    Ho, Wo = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
     out = torch.empty((Nn, Ho, Wo, Cout), dtype=torch.bfloat16, device=x_nhwc.device)
-    L.call("conv2d_igemm_bf16", L.ptr(x_nhwc), L.ptr(wmat), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH), I(KW),
-           I(pad), L.ptr(bias), L.ptr(residual), I(act), _s())
+    L.call("conv2d_igemm_strided_bf16", L.ptr(x_nhwc), L.ptr(wmat), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH),
+           I(KW), I(pad), I(stride), L.ptr(bias), L.ptr(residual), I(act), _s())
     return out
 
 
-def conv2d_igemm_wgrad(x_nhwc, dy_nhwc, KH: int, KW: int, pad: int, out=None, accumulate: bool = False):
+def conv2d_igemm_wgrad(x_nhwc, dy_nhwc, KH: int, KW: int, pad: int, out=None, accumulate: bool = False, stride: int = 1):
     """Implicit-GEMM weight gradient of a stride-1 convolution: x [N, H, W, C], dy [N, Ho, Wo, Cout] bf16 contiguous ->
     fp32 [Cout, KH * KW * C] in (kh, kw, c) column order.  C % 64 == 0, Cout % 8 == 0."""
     Nn, H, W, Cc = x_nhwc.shape
@@ -342,6 +342,6 @@ def conv2d_igemm_wgrad(x_nhwc, dy_nhwc, KH: int, KW: int, pad: int, out=None, ac
     assert x_nhwc.is_contiguous() and dy_nhwc.is_contiguous()
     if out is None:
         out = torch.empty((Cout, KH * KW * Cc), dtype=torch.float32, device=x_nhwc.device)
-    L.call("conv2d_igemm_wgrad", L.ptr(x_nhwc), L.ptr(dy_nhwc), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH), I(KW),
-           I(pad), I(int(accumulate)), _s())
+    L.call("conv2d_igemm_wgrad_strided", L.ptr(x_nhwc), L.ptr(dy_nhwc), L.ptr(out), I(Nn), I(H), I(W), I(Cc), I(Cout), I(KH),
+           I(KW), I(pad), I(stride), I(int(accumulate)), _s())
     return out

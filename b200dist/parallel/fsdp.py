@@ -33,6 +33,7 @@ CPU tensors (gloo unit tests) run the same control flow on torch.distributed col
 from __future__ import annotations
 
 import contextlib
+import os
 
 import math
 from typing import Dict, List, Optional
@@ -166,11 +167,11 @@ class FSDP(nn.Module):
         max_total = max(u.total for u in self.exec_units)
         if self.native and self.world > 1:
             esize = torch.empty((), dtype=self.dtype).element_size()
-            # From nvls_min_world ranks up the two staging buffers live behind an NVSwitch multicast object: the reduce-
+            # When the platform offers NVSwitch multicast, the two staging buffers live behind a multicast object: the reduce-
             # scatter is then ONE multimem.ld_reduce pass over this rank's slice, fused with AdamW (comm_rs_adamw_nvls) -
             # no DMA staging of the peers' slabs, no scratch traffic in HBM, one arrive / depart instead of two barriers.
             self.grad_stage, self.nvls_grads = None, False
-            if nvls_reduce and self.dtype == torch.bfloat16 and self.world >= self.comm.nvls_min_world:
+            if nvls_reduce and self.dtype == torch.bfloat16 and self.world >= int(os.environ.get("B200DIST_FSDP_NVLS_MIN_WORLD", "2")):
                 bufs = [self.comm.nvls_buffer(max_total * esize) for _ in range(2)]
                 if all(b is not None for b in bufs):
                     self.grad_stage, self.nvls_grads = bufs, True

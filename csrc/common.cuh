@@ -504,4 +504,7 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn_m
 int b200_make_tmap(CUtensorMap* out, const void* base, int elem_bytes, int rank,
                    const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                    int swizzle_128b);
+int b200_make_tmap_strided(CUtensorMap* out, const void* base, int elem_bytes, int rank,
+                   const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
+                   int swizzle_128b);
 int b200_sm_count();

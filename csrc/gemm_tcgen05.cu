@@ -74,6 +74,7 @@ struct FusedParams {
   int c_hbox, c_wbox, c_nbox;   // output-pixel box of one m-block (c_nbox * c_hbox * c_wbox <= 128 rows)
   int c_tiles_h, c_tiles_w;
   int c_KW, c_pad, c_cblocks;   // kernel width, padding, C / 64
+  int c_stride;                 // convolution stride (1 or 2): input coordinate = output coordinate * stride + tap - pad
   int c_box_bytes;              // bytes one box load delivers (the rest of the 128-row A stage stays stale: rows unused)
 };
 
@@ -316,7 +317,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 const int col = n0 + j * 64;
                 const int tap = col / fp.c_C, c0 = col - tap * fp.c_C;
                 const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
-                tma_load_4d(sb + j * 8192, &tmap_b, fb, c0, pw + kw - fp.c_pad, ph + kh - fp.c_pad, pn);
+                tma_load_4d(sb + j * 8192, &tmap_b, fb, c0, pw * fp.c_stride + kw - fp.c_pad, ph * fp.c_stride + kh - fp.c_pad, pn);
               }
               if (++stage == kStages) { stage = 0; phase ^= 1u; }
               continue;
@@ -328,7 +329,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
               const int tn = m_blk / (fp.c_tiles_w * fp.c_tiles_h);
               const int tap = kb / fp.c_cblocks, cb = kb - tap * fp.c_cblocks;
               const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
-              tma_load_4d(sa, &tmap_a, fb, cb * 64, tw * fp.c_wbox + kw - fp.c_pad, th * fp.c_hbox + kh - fp.c_pad,
+              tma_load_4d(sa, &tmap_a, fb, cb * 64, tw * fp.c_wbox * fp.c_stride + kw - fp.c_pad,
+                          th * fp.c_hbox * fp.c_stride + kh - fp.c_pad,
                           tn * fp.c_nbox);
               a_done = true;
             }
@@ -741,10 +743,12 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
 // Implicit-GEMM convolution launcher (stride 1): out[n, ho, wo, :] = sum_{kh, kw, c} x[n, ho + kh - pad, wo + kw - pad, c] *
 // wmat[:, (kh, kw, c)]  (+ bias, + residual, activation) with x NHWC bf16 and wmat [Cout, KH * KW * C] K-major.
 static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nimg, int H, int W, int C, int Cout, int KH,
-                             int KW, int pad, const void* bias, const void* residual, int act, cudaStream_t stream) {
+                             int KW, int pad, int stride, const void* bias, const void* residual, int act,
+                             cudaStream_t stream) {
   constexpr int CG = 1, BN = 128;
   using Cfg = GemmCfg<CG, BN>;
-  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  if (stride < 1 || stride > 2) { b200_set_error("conv_igemm: stride %d not supported (1 or 2)", stride); return B200_ERR_UNSUPPORTED; }
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   if (Ho <= 0 || Wo <= 0 || (C % 64) || (Cout % 8) || Nimg <= 0) {
     b200_set_error("conv_igemm: needs C %% 64 == 0, Cout %% 8 == 0 and a non-empty output (C=%d Cout=%d Ho=%d Wo=%d)", C, Cout, Ho, Wo);
     return B200_ERR_SHAPE;
@@ -760,7 +764,7 @@ static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nim
   }
   fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
   fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
-  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64;
+  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64; fp.c_stride = stride;
   fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
   GemmParams p = {};
   p.M = Nimg * Ho * Wo; p.N = Cout; p.K = KH * KW * C;
@@ -777,8 +781,10 @@ static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nim
   {
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
     const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
-    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
-    if (int rc = b200_make_tmap(&ta, x, 2, 4, dims, str, box, 1)) return rc;
+    // stride 2: the box spans 2 x as many input pixels and the tensor map steps over every second one
+    const uint32_t box[4] = {64u, (uint32_t)(fp.c_wbox * stride), (uint32_t)(fp.c_hbox * stride), (uint32_t)fp.c_nbox};
+    const uint32_t est[4] = {1u, (uint32_t)stride, (uint32_t)stride, 1u};
+    if (int rc = b200_make_tmap_strided(&ta, x, 2, 4, dims, str, box, est, 1)) return rc;
   }
   {
     const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N};
@@ -811,10 +817,11 @@ static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nim
 // Implicit-GEMM weight gradient (stride 1): dW[co, (kh, kw, c)] (fp32, [Cout, KH*KW*C]) = sum over n, ho, wo of
 // dY[n, ho, wo, co] * X[n, ho + kh - pad, wo + kw - pad, c].  Split-K over pixel boxes with fp32 red.add.
 static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg, int H, int W, int C, int Cout, int KH,
-                             int KW, int pad, int accumulate, cudaStream_t stream) {
+                             int KW, int pad, int stride, int accumulate, cudaStream_t stream) {
   constexpr int CG = 1, BN = 128;
   using Cfg = GemmCfg<CG, BN>;
-  const int Ho = H + 2 * pad - KH + 1, Wo = W + 2 * pad - KW + 1;
+  if (stride < 1 || stride > 2) { b200_set_error("conv_wgrad: stride %d not supported (1 or 2)", stride); return B200_ERR_UNSUPPORTED; }
+  const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
   if (Ho <= 0 || Wo <= 0 || (C % 64) || (Cout % 8) || Nimg <= 0) {
     b200_set_error("conv_wgrad: needs C %% 64 == 0, Cout %% 8 == 0 and a non-empty output (C=%d Cout=%d)", C, Cout);
     return B200_ERR_SHAPE;
@@ -831,7 +838,7 @@ static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg,
   }
   fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
   fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
-  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64;
+  fp.c_KW = KW; fp.c_pad = pad; fp.c_cblocks = C / 64; fp.c_stride = stride;
   fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
   GemmParams p = {};
   p.M = Cout; p.N = KH * KW * C;
@@ -864,8 +871,9 @@ static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg,
   {
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)Nimg};
     const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
-    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
-    if (int rc = b200_make_tmap(&tb, x, 2, 4, dims, str, box, 1)) return rc;
+    const uint32_t box[4] = {64u, (uint32_t)(fp.c_wbox * stride), (uint32_t)(fp.c_hbox * stride), (uint32_t)fp.c_nbox};
+    const uint32_t est[4] = {1u, (uint32_t)stride, (uint32_t)stride, 1u};
+    if (int rc = b200_make_tmap_strided(&tb, x, 2, 4, dims, str, box, est, 1)) return rc;
   }
   auto kern = gemm_tcgen05_kernel<CG, BN, true, true, float, true>;
   static bool attr_set = false;
@@ -1040,12 +1048,23 @@ B200_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* 
 B200_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
                                     int KH, int KW, int pad, const void* bias, const void* residual, int act,
                                     cudaStream_t stream) {
-  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, bias, residual, act, stream);
+  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, 1, bias, residual, act, stream);
+}
+// Same with a convolution stride of 1 or 2 (ResNet stage transitions: 3x3 s2 and the 1x1 s2 shortcut): the activation
+// tensor map traverses every `stride`-th pixel, so the strided taps still arrive as one TMA box per k-block.
+B200_API int b200_conv2d_igemm_strided_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
+                                            int KH, int KW, int pad, int stride, const void* bias, const void* residual,
+                                            int act, cudaStream_t stream) {
+  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, stride, bias, residual, act, stream);
 }
 
 // Implicit-GEMM weight gradient of a stride-1 convolution (wgrad): x [N, H, W, C] and
 // dy [N, Ho, Wo, Cout] NHWC bf16 -> dw [Cout, KH * KW * C] fp32 (zeroed first unless accumulate).  C % 64 == 0.
 B200_API int b200_conv2d_igemm_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
                                      int KH, int KW, int pad, int accumulate, cudaStream_t stream) {
-  return b200::launch_conv_wgrad(x, dy, dw, N, H, W, C, Cout, KH, KW, pad, accumulate, stream);
+  return b200::launch_conv_wgrad(x, dy, dw, N, H, W, C, Cout, KH, KW, pad, 1, accumulate, stream);
+}
+B200_API int b200_conv2d_igemm_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
+                                             int KH, int KW, int pad, int stride, int accumulate, cudaStream_t stream) {
+  return b200::launch_conv_wgrad(x, dy, dw, N, H, W, C, Cout, KH, KW, pad, stride, accumulate, stream);
 }

@@ -105,6 +105,15 @@ static EncodeTiledFn get_encode_fn() {
 int b200_make_tmap(CUtensorMap* out, const void* base, int elem_bytes, int rank,
                    const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                    int swizzle_128b) {
+  return b200_make_tmap_strided(out, base, elem_bytes, rank, dims, strides_bytes, box, nullptr, swizzle_128b);
+}
+
+// elem_strides (may be null = all 1): traversal stride per dimension.  With a stride s > 1 a box of extent b covers b
+// tensor elements and delivers ceil(b / s) of them - every s-th one - packed in shared memory: a strided convolution reads
+// exactly its taps through it.
+int b200_make_tmap_strided(CUtensorMap* out, const void* base, int elem_bytes, int rank,
+                           const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                           const uint32_t* elem_strides, int swizzle_128b) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     b200_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
@@ -117,7 +126,7 @@ int b200_make_tmap(CUtensorMap* out, const void* base, int elem_bytes, int rank,
   for (int i = 0; i < rank; ++i) {
     gdim[i] = dims[i];
     gbox[i] = box[i];
-    estr[i] = 1;
+    estr[i] = elem_strides ? elem_strides[i] : 1;
   }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
   CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16

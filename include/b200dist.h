@@ -60,6 +60,13 @@ B200DIST_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* o
                                     cudaStream_t stream);
 B200DIST_API int b200_conv2d_igemm_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
                                      int KH, int KW, int pad, int accumulate, cudaStream_t stream);
+/* stride 1 or 2 (torchvision ResNet stage transitions, /root/reference/scripts/main.py:249): the activation tensor map
+ * steps over every `stride`-th pixel, so strided forward and weight-gradient convolutions need no patch matrix either */
+B200DIST_API int b200_conv2d_igemm_strided_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
+                                                int KH, int KW, int pad, int stride, const void* bias, const void* residual,
+                                                int act, cudaStream_t stream);
+B200DIST_API int b200_conv2d_igemm_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
+                                                 int KH, int KW, int pad, int stride, int accumulate, cudaStream_t stream);
 
 /* ---- Attention (tcgen05 flash attention) ----
  * replaces F.scaled_dot_product_attention: fsdp_tp/llama2_model.py:218-223; explicit softmax attention: scripts/03_tensor_parallel_tp/tensor_parallel_vit.py:120-122 */

@@ -79,5 +79,50 @@ for (B, C, H, W, K, ks, pad) in [(2, 64, 56, 56, 64, 3, 1), (3, 128, 28, 28, 128
         t_cudnn = ev(lambda: F.conv2d(xc, w, padding=pad))
         msg += f" | time igemm {t_ig:.0f} us, im2col+GEMM {t_old:.0f} us, cuDNN {t_cudnn:.0f} us"
     print(msg, flush=True)
+# ---- stride-2 forward and weight gradient (tensor map with element strides): ResNet stage transitions, odd extents ----
+for (B, C, H, W, K, ks, pad) in [(2, 128, 56, 56, 128, 3, 1), (2, 256, 56, 56, 512, 1, 0), (3, 64, 29, 41, 72, 3, 1),
+                                 (2, 512, 14, 14, 512, 3, 1), (4, 1024, 14, 14, 2048, 1, 0), (64, 128, 56, 56, 128, 3, 1)]:
+    x = torch.randn(B, C, H, W, device=dev).bfloat16()
+    w = (torch.randn(K, C, ks, ks, device=dev) * (1.0 / (C * ks * ks) ** 0.5)).bfloat16()
+    xh = x.permute(0, 2, 3, 1).contiguous()
+    wm = w.permute(0, 2, 3, 1).reshape(K, ks * ks * C).contiguous()
+    y = N.conv2d_igemm(xh, wm, ks, ks, pad, stride=2)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float(), w.float(), stride=2, padding=pad).permute(0, 2, 3, 1)
+    ok = tuple(y.shape) == tuple(ref.shape)
+    err = float((y.float() - ref).abs().max()) if ok else float("inf"); scale = float(ref.abs().max())
+    ok = ok and err <= 0.02 * scale + 0.02
+    fails += (not ok)
+    msg = f"[{'PASS' if ok else 'FAIL'}] igemm fprop STRIDE 2 B{B} C{C} {H}x{W} -> K{K} k{ks} p{pad}: max_err={err:.4g} (|ref| {scale:.3g})"
+    dyw = torch.randn_like(ref).bfloat16().contiguous()
+    if B * ref.shape[1] * ref.shape[2] >= 128:
+        dwm = N.conv2d_igemm_wgrad(xh, dyw, ks, ks, pad, stride=2)
+        torch.cuda.synchronize()
+        wr = w.float().requires_grad_(True)
+        F.conv2d(x.float(), wr, stride=2, padding=pad).backward(dyw.float().permute(0, 3, 1, 2))
+        wref = wr.grad.permute(0, 2, 3, 1).reshape(K, -1)
+        e3 = float((dwm - wref).abs().max()); s3 = float(wref.abs().max())
+        ok3 = e3 <= 0.02 * s3 + 0.02
+        fails += (not ok3)
+        msg += f" | wgrad max_err={e3:.4g} (|ref| {s3:.3g}) {'PASS' if ok3 else 'FAIL'}"
+    # the autograd op end to end (forward igemm, dgrad = GEMM + col2im, wgrad igemm) vs F.conv2d
+    xa = x.clone().requires_grad_(True); wa = w.clone().requires_grad_(True)
+    ya = cops.conv2d(xa, wa, None, 2, pad)
+    ya.backward(dyw.permute(0, 3, 1, 2))
+    xr = x.float().requires_grad_(True); wr2 = w.float().requires_grad_(True)
+    F.conv2d(xr, wr2, stride=2, padding=pad).backward(dyw.float().permute(0, 3, 1, 2))
+    e4 = float((xa.grad.float() - xr.grad).abs().max()); s4 = float(xr.grad.abs().max())
+    e5 = float((wa.grad.float() - wr2.grad).abs().max()); s5 = float(wr2.grad.abs().max())
+    ok4 = e4 <= 0.03 * s4 + 0.02 and e5 <= 0.03 * s5 + 0.02
+    fails += (not ok4)
+    msg += f" | autograd dx err {e4:.3g} dw err {e5:.3g} {'PASS' if ok4 else 'FAIL'}"
+    if B >= 64:
+        t_ig = ev(lambda: N.conv2d_igemm(xh, wm, ks, ks, pad, stride=2))
+        xc = x.contiguous(memory_format=torch.channels_last)
+        t_cudnn = ev(lambda: F.conv2d(xc, w, stride=2, padding=pad))
+        Ho, Wo = ref.shape[1], ref.shape[2]
+        t_im = ev(lambda: cops._im2col(xh, ks, ks, 2, pad, Ho, Wo, C))
+        msg += f" | time igemm {t_ig:.0f} us, im2col alone {t_im:.0f} us, cuDNN {t_cudnn:.0f} us"
+    print(msg, flush=True)
 print(f"== conv igemm: failures {fails}")
 sys.exit(1 if fails else 0)
