@@ -1,5 +1,5 @@
 """Tiny launcher for ncu captures: runs ONE kernel family a few times.
-    python tools/ncu_targets.py gemm|attn_fwd|attn_bwd|rmsnorm|adamw"""
+    python tools/ncu_targets.py gemm|gemm_wgrad|attn_fwd|attn_bwd|rmsnorm|adamw|conv|conv_s2|conv_wgrad"""
 import sys
 from pathlib import Path
 
@@ -36,5 +36,17 @@ elif what == "adamw":
     lp = torch.empty(n, device=dev, dtype=torch.bfloat16)
     for _ in range(4):
         N.adamw_step(p, g, m, v, lr=1e-3, beta1=0.9, beta2=0.95, eps=1e-8, wd=0.1, step=3, p_lowp=lp)
+elif what in ("conv", "conv_wgrad", "conv_s2"):
+    stride = 2 if what == "conv_s2" else 1
+    C, K, H = (128, 128, 56) if stride == 2 else (64, 64, 56)
+    x = torch.randn(256, H, H, C, device=dev).bfloat16()
+    wm = (torch.randn(K, 9 * C, device=dev) * 0.05).bfloat16()
+    Ho = (H + 2 - 3) // stride + 1
+    dy = torch.randn(256, Ho, Ho, K, device=dev).bfloat16()
+    for _ in range(3):
+        if what == "conv_wgrad":
+            N.conv2d_igemm_wgrad(x, dy, 3, 3, 1)
+        else:
+            N.conv2d_igemm(x, wm, 3, 3, 1, stride=stride)
 torch.cuda.synchronize()
 print("done", what)
