@@ -459,6 +459,40 @@ class Communicator:
             t.reshape(-1).view(torch.uint8).copy_(tmp[:nbytes])
         return t
 
+    def neighbor_exchange(self, to_prev: torch.Tensor, to_next: torch.Tensor, channel: int = 5):
+        """Chain halo exchange: returns (from_prev, from_next) = (rank-1's ``to_next``, rank+1's ``to_prev``), zeros at the
+        two ends.  Every rank moves two strips regardless of the world size (an all-gather of the edges would move
+        2 * world)."""
+        assert to_prev.shape == to_next.shape and to_prev.dtype == to_next.dtype
+        from_prev, from_next = torch.zeros_like(to_prev), torch.zeros_like(to_next)
+        if self.world == 1:
+            return from_prev, from_next
+        if not self.native or not to_prev.is_cuda:
+            ops = []
+            g = self.group
+            gr = (lambda r: dist.get_global_rank(g, r)) if g is not None else (lambda r: r)
+            tp, tn = to_prev.contiguous(), to_next.contiguous()
+            if self.rank > 0:
+                ops += [dist.P2POp(dist.isend, tp, gr(self.rank - 1), group=g), dist.P2POp(dist.irecv, from_prev, gr(self.rank - 1), group=g)]
+            if self.rank + 1 < self.world:
+                ops += [dist.P2POp(dist.isend, tn, gr(self.rank + 1), group=g), dist.P2POp(dist.irecv, from_next, gr(self.rank + 1), group=g)]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            return from_prev, from_next
+        nbytes = to_prev.numel() * to_prev.element_size()
+        pad = (nbytes + 15) // 16 * 16
+        buf = self._stage(channel, 2 * pad)
+        buf.tensor(to_prev.dtype, 0, to_prev.numel()).copy_(to_prev.reshape(-1))
+        buf.tensor(to_next.dtype, pad, to_next.numel()).copy_(to_next.reshape(-1))
+        if pad == nbytes:
+            op, on = from_prev, from_next
+        else:
+            op = torch.empty(pad, dtype=torch.uint8, device=to_prev.device); on = torch.empty_like(op)
+        L.call("comm_neighbor_exchange", *self._ctx(buf, channel), L.ptr(op), L.ptr(on), LL(0), LL(pad), I(self.max_ctas), self._s())
+        if pad != nbytes:
+            from_prev.reshape(-1).view(torch.uint8).copy_(op[:nbytes]); from_next.reshape(-1).view(torch.uint8).copy_(on[:nbytes])
+        return from_prev, from_next
+
     def all_to_all(self, out: torch.Tensor, inp: torch.Tensor, channel: int = 4) -> torch.Tensor:
         """out chunk r = rank r's inp chunk [this rank]; equal-size chunks along the flat dimension."""
         if self.world == 1:

@@ -3,7 +3,8 @@
 Docs-only in the reference (/root/reference/docs/guide/10_domain_parallel.md:45-149: splitting the height dimension
 breaks a 3x3 convolution at the cut unless each rank first receives a one-row halo from its neighbours; the guide points
 to PhysicsNeMo ShardTensor).  Here the input is sharded along H; ``halo_exchange`` attaches ``halo`` boundary rows of
-the neighbouring ranks (zeros at the global border) through ONE small peer-memory all-gather of boundary rows, and its
+the neighbouring ranks (zeros at the global border) with one neighbour exchange - each rank reads two strips from its two
+neighbours over peer memory, whatever the number of ranks - and its
 backward returns the halo gradients to their owners.  ``halo_conv2d`` then equals the corresponding rows of the
 unsharded convolution exactly.
 """
@@ -16,15 +17,11 @@ from ..ops import conv as cops
 
 
 def _exchange(x, comm, halo):
-    """-> (top, bottom): halo rows received from rank-1 / rank+1 (zeros at the domain border)."""
-    P, r = comm.world, comm.rank
-    edges = torch.stack([x[:, :, :halo, :], x[:, :, -halo:, :]]).contiguous()       # [2, N, C, halo, W]: my top / bottom rows
-    allb = torch.empty((P,) + tuple(edges.shape), dtype=x.dtype, device=x.device)
-    comm.all_gather(allb, edges, channel=5)
-    zeros = torch.zeros_like(edges[0])
-    top = allb[r - 1, 1] if r > 0 else zeros            # neighbour above contributes ITS bottom rows
-    bottom = allb[r + 1, 0] if r < P - 1 else zeros     # neighbour below contributes ITS top rows
-    return top, bottom
+    """-> (top, bottom): halo rows received from rank-1 / rank+1 (zeros at the domain border).  Two neighbour transfers
+    per rank (``Communicator.neighbor_exchange``), independent of the number of ranks."""
+    my_top, my_bottom = x[:, :, :halo, :].contiguous(), x[:, :, -halo:, :].contiguous()
+    # the rank above needs my top rows as ITS bottom halo; the rank below needs my bottom rows as ITS top halo
+    return comm.neighbor_exchange(my_top, my_bottom)
 
 
 class _HaloExchange(Function):
@@ -37,16 +34,12 @@ class _HaloExchange(Function):
     @staticmethod
     def backward(ctx, g):
         comm, h = ctx.comm, ctx.halo
-        P, r = comm.world, comm.rank
         core = g[:, :, h:-h, :].clone()
-        # gradient of my top halo belongs to rank-1's bottom rows; of my bottom halo to rank+1's top rows
-        send = torch.stack([g[:, :, :h, :], g[:, :, -h:, :]]).contiguous()          # [2(top, bottom), N, C, h, W]
-        allg = torch.empty((P,) + tuple(send.shape), dtype=g.dtype, device=g.device)
-        comm.all_gather(allg, send, channel=5)
-        if r < P - 1:
-            core[:, :, -h:, :] += allg[r + 1, 0]   # rank+1's top-halo gradient lands on my bottom rows
-        if r > 0:
-            core[:, :, :h, :] += allg[r - 1, 1]    # rank-1's bottom-halo gradient lands on my top rows
+        # the gradient of my top halo belongs to rank-1's bottom rows, that of my bottom halo to rank+1's top rows:
+        # the same neighbour exchange, with the halo gradients as payload
+        from_prev, from_next = comm.neighbor_exchange(g[:, :, :h, :].contiguous(), g[:, :, -h:, :].contiguous())
+        core[:, :, :h, :] += from_prev      # rank-1's bottom-halo gradient lands on my top rows (zeros on rank 0)
+        core[:, :, -h:, :] += from_next     # rank+1's top-halo gradient lands on my bottom rows (zeros on the last rank)
         return core, None, None
 
 

@@ -595,6 +595,27 @@ __global__ void __launch_bounds__(512, 1) comm_alltoall_kernel(CommCtx c, uint4*
   comm_depart(c);
 }
 
+// ------------------------------ neighbour (halo) exchange -------------------
+// Each rank has placed its two edge strips in its symmetric buffer: slot 0 = what the PREVIOUS rank needs (my first rows),
+// slot 1 = what the NEXT rank needs (my last rows), n16 16-byte elements each.  After the arrive handshake a rank reads
+// only its two neighbours: from_prev <- rank-1's slot 1, from_next <- rank+1's slot 0 (zeros at the ends of the chain).
+// Payload per rank is two strips whatever the world size (domain-parallel halo exchange, docs/guide/10_domain_parallel.md
+// of the reference :69-103).
+__global__ void __launch_bounds__(512, 1) comm_neighbor_kernel(CommCtx c, uint4* __restrict__ from_prev,
+                                                              uint4* __restrict__ from_next, long long in_off16,
+                                                              long long n16) {
+  comm_arrive_and_wait(c);
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  const uint4* prev = c.rank > 0 ? reinterpret_cast<const uint4*>(c.data[c.rank - 1]) + in_off16 + n16 : nullptr;
+  const uint4* next = c.rank + 1 < c.world ? reinterpret_cast<const uint4*>(c.data[c.rank + 1]) + in_off16 : nullptr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
+       i += (long long)gridDim.x * blockDim.x) {
+    from_prev[i] = prev ? ld_peer_v4(prev + i) : zero;
+    from_next[i] = next ? ld_peer_v4(next + i) : zero;
+  }
+  comm_depart(c);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -876,6 +897,19 @@ B200_API int b200_comm_alltoall(COMM_ARGS, void* out, long long in_off_bytes, lo
   if ((bytes_per_peer | in_off_bytes) & 15) { b200_set_error("alltoall: sizes must be multiples of 16 bytes"); return B200_ERR_SHAPE; }
   comm_alltoall_kernel<<<comm_grid((bytes_per_peer >> 4) * world, 512, max_ctas), 512, 0, stream>>>(
       COMM_CTX, (uint4*)out, in_off_bytes >> 4, bytes_per_peer >> 4);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Halo exchange along a chain of ranks (see comm_neighbor_kernel).  data_ptrs: symmetric buffer holding, at in_off_bytes,
+// [slot 0: strip for rank-1][slot 1: strip for rank+1], `bytes` (multiple of 16) each.
+B200_API int b200_comm_neighbor_exchange(COMM_ARGS, void* from_prev, void* from_next, long long in_off_bytes, long long bytes,
+                                         int max_ctas, cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if ((bytes & 15) || (in_off_bytes & 15)) { b200_set_error("neighbor_exchange: sizes must be multiples of 16 bytes"); return B200_ERR_SHAPE; }
+  const long long n16 = bytes >> 4;
+  const int grid = comm_grid(n16, 512, max_ctas);
+  comm_neighbor_kernel<<<grid, 512, 0, stream>>>(COMM_CTX, (uint4*)from_prev, (uint4*)from_next, in_off_bytes >> 4, n16);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -289,49 +289,75 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             fence_proxy_async_all();
           }
         }
+        // Implicit-GEMM convolution: everything that depends only on the tile is computed here, once, and the k loop
+        // walks (channel block, kw, kh) resp. (w tile, h tile, image tile) with counters.  This loop runs on ONE thread
+        // and feeds the whole CTA: with the divisions inside it, a k-block took ~1200 cycles to issue (ncu: the MMA
+        // issuer spun on the full barriers while the producer never waited for a free stage).
+        int cv_mode = 0, cv_w0 = 0, cv_h0 = 0, cv_n0 = 0, cv_a = 0, cv_b = 0, cv_c = 0;
+        int cv_colc[kLoadN / 64 > 0 ? kLoadN / 64 : 1], cv_colw[kLoadN / 64 > 0 ? kLoadN / 64 : 1],
+            cv_colh[kLoadN / 64 > 0 ? kLoadN / 64 : 1];
+        uint32_t cv_tx = (uint32_t)Cfg::kStageBytes;
+        if constexpr (FUSED && CG == 1) {
+          cv_mode = fp.conv_on;
+          if (cv_mode == 1) {
+            const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
+            cv_n0 = (m_blk / (fp.c_tiles_w * fp.c_tiles_h)) * fp.c_nbox;
+            cv_w0 = tw * fp.c_wbox * fp.c_stride - fp.c_pad;
+            cv_h0 = th * fp.c_hbox * fp.c_stride - fp.c_pad;
+            const int tap = kb0 / fp.c_cblocks;
+            cv_a = kb0 - tap * fp.c_cblocks;          // channel block
+            cv_c = tap / fp.c_KW;                     // kh
+            cv_b = tap - cv_c * fp.c_KW;              // kw
+            cv_tx = (uint32_t)(fp.c_box_bytes + Cfg::kBBytes);
+          } else if (cv_mode == 2) {
+            cv_a = kb0 % fp.c_tiles_w;                                  // w tile
+            cv_b = (kb0 / fp.c_tiles_w) % fp.c_tiles_h;                 // h tile
+            cv_c = kb0 / (fp.c_tiles_w * fp.c_tiles_h);                 // image tile
+#pragma unroll
+            for (int j = 0; j < kLoadN / 64; ++j) {
+              const int col = n0 + j * 64;
+              const int tap = col / fp.c_C;
+              const int kh = tap / fp.c_KW;
+              cv_colc[j] = col - tap * fp.c_C;
+              cv_colw[j] = tap - kh * fp.c_KW - fp.c_pad;
+              cv_colh[j] = kh - fp.c_pad;
+            }
+            cv_tx = (uint32_t)((kBlockM / 64 + kLoadN / 64) * fp.c_box_bytes);
+          }
+        }
+        const int cv_wbox = FUSED ? fp.c_wbox : 0, cv_hbox = FUSED ? fp.c_hbox : 0, cv_nbox = FUSED ? fp.c_nbox : 0;
+        const int cv_stride = FUSED ? fp.c_stride : 1, cv_cblocks = FUSED ? fp.c_cblocks : 1, cv_KW = FUSED ? fp.c_KW : 1;
+        const int cv_tiles_w = FUSED ? fp.c_tiles_w : 1, cv_tiles_h = FUSED ? fp.c_tiles_h : 1;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint32_t sb = sa + Cfg::kABytes;
           const uint32_t fb = full0 + 8u * stage;
           if constexpr (FUSED && CG == 1) {
-            uint32_t tx = (uint32_t)Cfg::kStageBytes;
-            if (fp.conv_on == 1) tx = (uint32_t)(fp.c_box_bytes + Cfg::kBBytes);
-            else if (fp.conv_on == 2) tx = (uint32_t)((kBlockM / 64 + kLoadN / 64) * fp.c_box_bytes);
-            mbar_expect_tx(full_bar(stage), tx);
+            mbar_expect_tx(full_bar(stage), cv_tx);
           } else {
             if (is_leader) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
           }
           const int k0 = kb * kBlockK;
           bool a_done = false;
           if constexpr (FUSED && CG == 1 && A_MN && B_MN) {
-            if (fp.conv_on == 2) {
-              // k-block = box of output pixels (w fastest, then h, then image)
-              const int tw = kb % fp.c_tiles_w, th = (kb / fp.c_tiles_w) % fp.c_tiles_h;
-              const int tn = kb / (fp.c_tiles_w * fp.c_tiles_h);
-              const int pw = tw * fp.c_wbox, ph = th * fp.c_hbox, pn = tn * fp.c_nbox;
+            if (cv_mode == 2) {
+              // k-block = box of output pixels (w fastest, then h, then image): counters cv_a / cv_b / cv_c
+              const int pw = cv_a * cv_wbox, ph = cv_b * cv_hbox, pn = cv_c * cv_nbox;
 #pragma unroll
               for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
 #pragma unroll
-              for (int j = 0; j < kLoadN / 64; ++j) {
-                const int col = n0 + j * 64;
-                const int tap = col / fp.c_C, c0 = col - tap * fp.c_C;
-                const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
-                tma_load_4d(sb + j * 8192, &tmap_b, fb, c0, pw * fp.c_stride + kw - fp.c_pad, ph * fp.c_stride + kh - fp.c_pad, pn);
-              }
+              for (int j = 0; j < kLoadN / 64; ++j)
+                tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
+              if (++cv_a == cv_tiles_w) { cv_a = 0; if (++cv_b == cv_tiles_h) { cv_b = 0; ++cv_c; } }
               if (++stage == kStages) { stage = 0; phase ^= 1u; }
               continue;
             }
           }
           if constexpr (FUSED && CG == 1 && !A_MN) {
-            if (fp.conv_on == 1) {
-              const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
-              const int tn = m_blk / (fp.c_tiles_w * fp.c_tiles_h);
-              const int tap = kb / fp.c_cblocks, cb = kb - tap * fp.c_cblocks;
-              const int kh = tap / fp.c_KW, kw = tap - kh * fp.c_KW;
-              tma_load_4d(sa, &tmap_a, fb, cb * 64, tw * fp.c_wbox * fp.c_stride + kw - fp.c_pad,
-                          th * fp.c_hbox * fp.c_stride + kh - fp.c_pad,
-                          tn * fp.c_nbox);
+            if (cv_mode == 1) {
+              tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
+              if (++cv_a == cv_cblocks) { cv_a = 0; if (++cv_b == cv_KW) { cv_b = 0; ++cv_c; } }
               a_done = true;
             }
           }
@@ -742,10 +768,11 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
 
 // Implicit-GEMM convolution launcher (stride 1): out[n, ho, wo, :] = sum_{kh, kw, c} x[n, ho + kh - pad, wo + kw - pad, c] *
 // wmat[:, (kh, kw, c)]  (+ bias, + residual, activation) with x NHWC bf16 and wmat [Cout, KH * KW * C] K-major.
+template <int BN>
 static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nimg, int H, int W, int C, int Cout, int KH,
                              int KW, int pad, int stride, const void* bias, const void* residual, int act,
                              cudaStream_t stream) {
-  constexpr int CG = 1, BN = 128;
+  constexpr int CG = 1;
   using Cfg = GemmCfg<CG, BN>;
   if (stride < 1 || stride > 2) { b200_set_error("conv_igemm: stride %d not supported (1 or 2)", stride); return B200_ERR_UNSUPPORTED; }
   const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
@@ -1045,17 +1072,23 @@ B200_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* 
 // out [N, Ho, Wo, Cout]; bias [Cout] and residual [N, Ho, Wo, Cout] optional; act as in b200_gemm_bf16.
 // C % 64 == 0, Cout % 8 == 0.  Replaces the cuDNN convolution behind torchvision's ResNet (scripts/main.py:249) without
 // materialising the im2col patch matrix.
+B200_API int b200_conv2d_igemm_strided_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
+                                            int KH, int KW, int pad, int stride, const void* bias, const void* residual,
+                                            int act, cudaStream_t stream);
 B200_API int b200_conv2d_igemm_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
                                     int KH, int KW, int pad, const void* bias, const void* residual, int act,
                                     cudaStream_t stream) {
-  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, 1, bias, residual, act, stream);
+  return b200_conv2d_igemm_strided_bf16(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, 1, bias, residual, act, stream);
 }
 // Same with a convolution stride of 1 or 2 (ResNet stage transitions: 3x3 s2 and the 1x1 s2 shortcut): the activation
 // tensor map traverses every `stride`-th pixel, so the strided taps still arrive as one TMA box per k-block.
 B200_API int b200_conv2d_igemm_strided_bf16(const void* x, const void* wmat, void* out, int N, int H, int W, int C, int Cout,
                                             int KH, int KW, int pad, int stride, const void* bias, const void* residual,
                                             int act, cudaStream_t stream) {
-  return b200::launch_conv_igemm(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, stride, bias, residual, act, stream);
+  // 64-wide output tiles for the 64-channel layers (ResNet layer1): a 128-wide tile would spend half its MMAs and half
+  // its weight loads on columns that do not exist
+  if (Cout <= 64) return b200::launch_conv_igemm<64>(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, stride, bias, residual, act, stream);
+  return b200::launch_conv_igemm<128>(x, wmat, out, N, H, W, C, Cout, KH, KW, pad, stride, bias, residual, act, stream);
 }
 
 // Implicit-GEMM weight gradient of a stride-1 convolution (wgrad): x [N, H, W, C] and

@@ -256,6 +256,11 @@ B200DIST_API int b200_comm_broadcast(const void* const* data_ptrs, const void* c
 B200DIST_API int b200_comm_alltoall(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes_per_peer,
                                 int max_ctas, cudaStream_t stream);
+/* neighbour (halo) exchange along a chain of ranks: every rank reads two strips - from rank-1 and rank+1 - whatever the
+ * world size (domain-parallel convolution; the reference only describes it, docs/guide/10_domain_parallel.md:69-103) */
+B200DIST_API int b200_comm_neighbor_exchange(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                                             int world, int channel, unsigned seq, void* from_prev, void* from_next,
+                                             long long in_off_bytes, long long bytes, int max_ctas, cudaStream_t stream);
 B200DIST_API int b200_comm_slab_reduce(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, void* out, const void* residual, long long n, int max_ctas,
                                    cudaStream_t stream);
