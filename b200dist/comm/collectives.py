@@ -45,6 +45,11 @@ class Communicator:
             # exchanged, and send the whole group through torch.distributed (NCCL) otherwise - multi-node jobs,
             # sub-groups that span nodes (HYBRID_SHARD replicas, PP x DP across nodes) keep working, as in the reference
             self.native, self.native_refused = _agree_single_box(group, self.device, self.world)
+            if not self.native and self.rank == 0:
+                import logging
+
+                logging.getLogger("b200dist").warning("peer-memory data plane refused: %s; this group uses "
+                                                      "torch.distributed (NCCL) collectives", self.native_refused)
         if self.native:
             _apply_peer_timeout(self.device)
         self.max_ctas = 0

@@ -190,6 +190,21 @@ __device__ __forceinline__ void fence_mbar_init() {
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// One lane of a CONVERGED warp (the lowest active one); all lanes must call it together.  The single-thread roles
+// of the tcgen05 / TMA kernels (load issue, MMA issue) run their loops with the whole warp and put only the issuing
+// instruction under `if (elect_one_sync())`: address / descriptor arithmetic then stays warp-uniform and the compiler keeps
+// it in uniform registers.  Inside `if (lane == 0) { loop }` the same arithmetic is "divergent" to the compiler and every
+// UTCHMMA / UTMALDG gets wrapped in an ELECT + 5 x R2UR.BROADCAST + branch sequence (~20 extra instructions per issue).
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                :: "r"(bar), "r"(bytes) : "memory");

@@ -165,7 +165,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
   const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 4);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
   const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
   const bool is_leader = cta_rank == 0;
   const int n_comm = FUSED ? fp.n_comm : 0;
@@ -265,8 +265,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     __syncwarp();
   } else if (warp == 0) {
-    if (lane == 0) {
+    {
       // ===================== TMA producer =====================
+      // (the whole warp walks the loop; only the elected lane issues - see elect_one_sync)
       int stage = 0;
       uint32_t phase = 0;
       const uint32_t full0 = (CG == 2) ? mapa(full_bar(0), 0) : full_bar(0);
@@ -330,13 +331,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int cv_tiles_w = FUSED ? fp.c_tiles_w : 1, cv_tiles_h = FUSED ? fp.c_tiles_h : 1;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
+          const bool el = elect_one_sync();   // the lane that issues; every lane computes the (uniform) operands
           const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
           const uint32_t sb = sa + Cfg::kABytes;
           const uint32_t fb = full0 + 8u * stage;
           if constexpr (FUSED && CG == 1) {
-            mbar_expect_tx(full_bar(stage), cv_tx);
+            if (el) mbar_expect_tx(full_bar(stage), cv_tx);
           } else {
-            if (is_leader) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
+            if (is_leader && el) mbar_expect_tx(full_bar(stage), Cfg::kStageBytes * CG);
           }
           const int k0 = kb * kBlockK;
           bool a_done = false;
@@ -344,11 +346,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             if (cv_mode == 2) {
               // k-block = box of output pixels (w fastest, then h, then image): counters cv_a / cv_b / cv_c
               const int pw = cv_a * cv_wbox, ph = cv_b * cv_hbox, pn = cv_c * cv_nbox;
+              if (el) {
 #pragma unroll
-              for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
+                for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
 #pragma unroll
-              for (int j = 0; j < kLoadN / 64; ++j)
-                tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
+                for (int j = 0; j < kLoadN / 64; ++j)
+                  tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
+              }
               if (++cv_a == cv_tiles_w) { cv_a = 0; if (++cv_b == cv_tiles_h) { cv_b = 0; ++cv_c; } }
               if (++stage == kStages) { stage = 0; phase ^= 1u; }
               continue;
@@ -356,30 +360,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           if constexpr (FUSED && CG == 1 && !A_MN) {
             if (cv_mode == 1) {
-              tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
+              if (el) tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
               if (++cv_a == cv_cblocks) { cv_a = 0; if (++cv_b == cv_KW) { cv_b = 0; ++cv_c; } }
               a_done = true;
             }
           }
-          if (a_done) {
-          } else if constexpr (!A_MN) {
-            if constexpr (CG == 2) tma_load_2d_2sm(sa, &tmap_a, fb, k0, m0);
-            else tma_load_2d(sa, &tmap_a, fb, k0, m0);
-          } else {
+          if (el) {
+            if (a_done) {
+            } else if constexpr (!A_MN) {
+              if constexpr (CG == 2) tma_load_2d_2sm(sa, &tmap_a, fb, k0, m0);
+              else tma_load_2d(sa, &tmap_a, fb, k0, m0);
+            } else {
 #pragma unroll
-            for (int j = 0; j < kBlockM / 64; ++j) {
-              if constexpr (CG == 2) tma_load_2d_2sm(sa + j * 8192, &tmap_a, fb, m0 + j * 64, k0);
-              else tma_load_2d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, k0);
+              for (int j = 0; j < kBlockM / 64; ++j) {
+                if constexpr (CG == 2) tma_load_2d_2sm(sa + j * 8192, &tmap_a, fb, m0 + j * 64, k0);
+                else tma_load_2d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, k0);
+              }
             }
-          }
-          if constexpr (!B_MN) {
-            if constexpr (CG == 2) tma_load_2d_2sm(sb, &tmap_b, fb, k0, n0);
-            else tma_load_2d(sb, &tmap_b, fb, k0, n0);
-          } else {
+            if constexpr (!B_MN) {
+              if constexpr (CG == 2) tma_load_2d_2sm(sb, &tmap_b, fb, k0, n0);
+              else tma_load_2d(sb, &tmap_b, fb, k0, n0);
+            } else {
 #pragma unroll
-            for (int j = 0; j < kLoadN / 64; ++j) {
-              if constexpr (CG == 2) tma_load_2d_2sm(sb + j * 8192, &tmap_b, fb, n0 + j * 64, k0);
-              else tma_load_2d(sb + j * 8192, &tmap_b, fb, n0 + j * 64, k0);
+              for (int j = 0; j < kLoadN / 64; ++j) {
+                if constexpr (CG == 2) tma_load_2d_2sm(sb + j * 8192, &tmap_b, fb, n0 + j * 64, k0);
+                else tma_load_2d(sb + j * 8192, &tmap_b, fb, n0 + j * 64, k0);
+              }
             }
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -387,9 +393,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && is_leader) {
+    if (is_leader) {
       // ===================== MMA issuer =====================
+      // Whole warp in the loop, elected lane issues (see elect_one_sync).  The shared-memory descriptors differ between
+      // stages and k-steps only in their 14-bit address field, so they are ONE add away from two per-kernel bases.
       constexpr uint32_t idesc = umma_idesc_bf16(kBlockM * CG, BN, A_MN, B_MN);
+      const uint64_t adesc0 = A_MN ? umma_smem_desc_sw128(smem_base, kBlockK * 128, 1024) : umma_smem_desc_sw128(smem_base, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? umma_smem_desc_sw128(smem_base + Cfg::kABytes, kBlockK * 128, 1024)
+                                   : umma_smem_desc_sw128(smem_base + Cfg::kABytes, 16, 1024);
+      constexpr uint32_t kAStep = (A_MN ? kUmmaK * 128 : kUmmaK * 2) >> 4;   // address-field increment per k-step
+      constexpr uint32_t kBStep = (B_MN ? kUmmaK * 128 : kUmmaK * 2) >> 4;
+      constexpr uint32_t kStageStep = Cfg::kStageBytes >> 4;
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -403,23 +417,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
-          const uint32_t sb = sa + Cfg::kABytes;
+          const uint64_t ad = adesc0 + (uint64_t)(stage * kStageStep);
+          const uint64_t bd = bdesc0 + (uint64_t)(stage * kStageStep);
+          const uint32_t acc0 = kb != kb0 ? 1u : 0u;
+          if (elect_one_sync()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            const uint64_t adesc = A_MN ? umma_smem_desc_sw128(sa + k * kUmmaK * 128, kBlockK * 128, 1024)
-                                        : umma_smem_desc_sw128(sa + k * kUmmaK * 2, 16, 1024);
-            const uint64_t bdesc = B_MN ? umma_smem_desc_sw128(sb + k * kUmmaK * 128, kBlockK * 128, 1024)
-                                        : umma_smem_desc_sw128(sb + k * kUmmaK * 2, 16, 1024);
-            umma_f16_ss<CG>(tmem_d, adesc, bdesc, idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kBlockK / kUmmaK; ++k)
+              umma_f16_ss<CG>(tmem_d, ad + (uint64_t)(k * kAStep), bd + (uint64_t)(k * kBStep), idesc, k == 0 ? acc0 : 1u);
+            // frees this smem stage (in both CTAs for cta_group::2) once the MMAs retire
+            if constexpr (CG == 2) umma_commit_2sm(empty_bar(stage), 0x3);
+            else umma_commit(empty_bar(stage));
           }
-          // frees this smem stage (in both CTAs for cta_group::2) once the MMAs retire
-          if constexpr (CG == 2) umma_commit_2sm(empty_bar(stage), 0x3);
-          else umma_commit(empty_bar(stage));
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        if constexpr (CG == 2) umma_commit_2sm(tfull_bar(as), 0x3);
-        else umma_commit(tfull_bar(as));
+        if (elect_one_sync()) {
+          if constexpr (CG == 2) umma_commit_2sm(tfull_bar(as), 0x3);
+          else umma_commit(tfull_bar(as));
+        }
         if (++as == 2) { as = 0; aphase ^= 1u; }
       }
     }
