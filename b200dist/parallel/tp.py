@@ -369,25 +369,19 @@ def enable_fused_tp(model, tp_mesh: DeviceMesh):
     from . import tp_fused
     from .. import ops as _ops
 
+    from ..models import fused_block
+
     comm = tp_mesh.communicator()
 
     for blk in model.layers:
-        att, ffn = blk.attention, blk.feed_forward
+        # q|k|v and w1|w3 shards back to back in memory: each group is ONE fused all-gather GEMM (and one fused
+        # GEMM -> reduce-scatter in backward).  An FSDP wrapper applied afterwards keeps them adjacent in its flat buffer.
+        fused_block.pack_block_weights(blk)
 
-        def block_forward(x, freqs_cis, pos_offset: int = 0, _blk=blk, _att=att, _ffn=ffn):
-            if not tp_fused.fusable(x, comm):
+        def block_forward(x, freqs_cis, pos_offset: int = 0, _blk=blk):
+            if not tp_fused.block_tp_supported(_blk, x, comm):
                 return _blk._unfused_forward(x, freqs_cis, pos_offset)
-            hd = _att.head_dim
-            xn = _blk.attention_norm(x)                                            # local sequence shard
-            q, k, v = tp_fused.ag_linear(comm, xn, [_att.wq.weight, _att.wk.weight, _att.wv.weight])
-            S = q.shape[1]
-            q = _ops.rope(q.view(1, S, -1, hd), freqs_cis, pos_offset)
-            k = _ops.rope(k.view(1, S, -1, hd), freqs_cis, pos_offset)
-            o = _ops.attention(q, k, v.view(1, S, -1, hd), causal=True)
-            h = tp_fused.linear_rs(comm, o.reshape(1, S, -1), _att.wo.weight, residual=x)
-            hn = _blk.ffn_norm(h)
-            a, b = tp_fused.ag_linear(comm, hn, [_ffn.w1.weight, _ffn.w3.weight])
-            return tp_fused.linear_rs(comm, _ops.swiglu(a, b), _ffn.w2.weight, residual=h)
+            return tp_fused.run_block_tp(_blk, x, freqs_cis, pos_offset, comm)
 
         blk._unfused_forward = blk.forward
         blk.forward = block_forward

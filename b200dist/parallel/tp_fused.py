@@ -190,6 +190,113 @@ class _LinearAR(Function):
         return None, dx.view(*dy.shape[:-1], dx.shape[-1]), dw, db
 
 
+class LlamaBlockTPFn(Function):
+    """One tensor-parallel + sequence-parallel Llama block as a single autograd node on the fused kernels.
+
+    Input / output: this rank's sequence shard [1, S/T, D].  Per block, forward and backward together, the node issues
+
+    * 4 all-gather -> GEMM kernels: ``[q|k|v]`` (ONE GEMM over the row-stacked wq|wk|wv shard), ``[w1|w3]`` (one GEMM over
+      the stacked w1|w3 shard), and in backward the two row-parallel input gradients (gather dY, multiply by W);
+    * 4 GEMM -> reduce-scatter kernels: wo and w2 (+ residual) forward, and the input gradients of the two stacked
+      column-parallel projections (K = 3 D / T resp. 2 F / T: the partial products of q, k, v accumulate in TMEM);
+    * RoPE in place inside the gathered projection output, attention on the local heads, SwiGLU on the two halves of
+      the stacked output, RMSNorm on the sequence shard with the residual gradient folded into its backward.
+
+    Reference plan: /root/reference/scripts/06_hybrid_parallelism/01_fsdp_tp_hybrid.py:126-152 (SequenceParallel norms,
+    ColwiseParallel wq/wk/wv/w1/w3, RowwiseParallel wo/w2 with Shard(1) outputs); model llama2_model.py:207,267.
+    """
+
+    @staticmethod
+    def forward(ctx, comm, x, freqs_real, pos_offset, eps, n_heads_local, n_kv_local, w_an, wq, wk, wv, wo, w_fn, w1, w2, w3):
+        from ..models.fused_block import adjacent_rows
+
+        S_loc, D = x.shape[1], x.shape[2]
+        T = comm.world
+        S = S_loc * T
+        hd = wq.shape[0] // n_heads_local
+        Nq, Nkv, Ffn = n_heads_local * hd, n_kv_local * hd, w1.shape[0]
+        x2 = x.reshape(S_loc, D)
+        wqkv, w13 = adjacent_rows((wq, wk, wv)), adjacent_rows((w1, w3))
+        assert wqkv is not None and w13 is not None, "fused TP block: pack the weight shards first (enable_fused_tp does)"
+        n1, rstd1 = N.rmsnorm_fwd(x2, w_an if w_an.dtype == x.dtype else w_an.to(x.dtype), eps)
+        qkv, xg = _ag_gemm(comm, n1, wqkv)                                   # [S, Nq + 2 Nkv], gathered n1 [S, D]
+        xg1 = xg.clone()                                                     # the workspace is reused by the next gather
+        N.rope_strided(qkv, freqs_real, S, n_heads_local + n_kv_local, hd, pos_offset)
+        q4 = qkv[:, :Nq].view(1, S, n_heads_local, hd)
+        k4 = qkv[:, Nq:Nq + Nkv].view(1, S, n_kv_local, hd)
+        v4 = qkv[:, Nq + Nkv:].view(1, S, n_kv_local, hd)
+        scale = float(hd) ** -0.5
+        o4, lse = N.flash_attn_fwd(q4, k4, v4, True, scale, 0, 0)
+        h = _gemm_rs(comm, o4.view(S, Nq), wo, residual=x2)                  # [S/T, D] = x + attn(x), my rows
+        n2, rstd2 = N.rmsnorm_fwd(h, w_fn if w_fn.dtype == x.dtype else w_fn.to(x.dtype), eps)
+        ab, xg = _ag_gemm(comm, n2, w13)                                     # [S, 2 F/T]
+        xg2 = xg.clone()
+        s = N.swiglu_fwd(ab[:, :Ffn], ab[:, Ffn:])
+        y = _gemm_rs(comm, s, w2, residual=h)
+        ctx.comm = comm
+        ctx.save_for_backward(x2, rstd1, xg1, qkv, o4, lse, h, rstd2, xg2, ab, s, freqs_real, w_an, wqkv, wo, w_fn, w13, w2)
+        ctx.meta = (S_loc, S, D, hd, n_heads_local, n_kv_local, Ffn, pos_offset, scale, eps)
+        ctx.params = (w_an, wq, wk, wv, wo, w_fn, w1, w2, w3)
+        return y.view(1, S_loc, D)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from ..models.fused_block import _wgrad
+
+        comm = ctx.comm
+        (x2, rstd1, xg1, qkv, o4, lse, h, rstd2, xg2, ab, s, freqs_real, w_an, wqkv, wo, w_fn, w13, w2) = ctx.saved_tensors
+        S_loc, S, D, hd, Hq, Hkv, Ffn, pos_offset, scale, eps = ctx.meta
+        p_an, p_wq, p_wk, p_wv, p_wo, p_fn, p_w1, p_w2, p_w3 = ctx.params
+        Nq, Nkv = Hq * hd, Hkv * hd
+        dy2 = dy.reshape(S_loc, D)
+        dy2 = dy2 if (dy2.is_contiguous() and dy2.dtype == torch.bfloat16) else dy2.to(torch.bfloat16).contiguous()
+        wan = w_an if w_an.dtype == x2.dtype else w_an.to(x2.dtype)
+        wfn = w_fn if w_fn.dtype == x2.dtype else w_fn.to(x2.dtype)
+        # ---- feed-forward half ----
+        ds, dyg = _ag_gemm(comm, dy2, w2, b_mn=True)                         # gather dY rows, ds = dY @ W2_shard  [S, F/T]
+        (dw2,) = _wgrad(dyg, s, (p_w2,))                                     # uses the gathered dY before the next gather
+        dab = torch.empty_like(ab)
+        N.swiglu_bwd(ds, ab[:, :Ffn], ab[:, Ffn:], da=dab[:, :Ffn], db=dab[:, Ffn:])
+        dn2 = _gemm_rs(comm, dab, w13, b_mn=True)                            # [S/T, D]: sum over ranks of dab @ W13_shard
+        dw1, dw3 = _wgrad(dab, xg2, (p_w1, p_w3))
+        dh, dw_fn = N.rmsnorm_bwd_res(dn2, h, wfn, rstd2, dy2)
+        # ---- attention half ----
+        do, dhg = _ag_gemm(comm, dh, wo, b_mn=True)                          # [S, Nq]
+        (dwo,) = _wgrad(dhg, o4.view(S, Nq), (p_wo,))
+        q4 = qkv[:, :Nq].view(1, S, Hq, hd)
+        k4 = qkv[:, Nq:Nq + Nkv].view(1, S, Hkv, hd)
+        v4 = qkv[:, Nq + Nkv:].view(1, S, Hkv, hd)
+        dqkv = torch.empty_like(qkv)
+        N.flash_attn_bwd(q4, k4, v4, o4, do.view(1, S, Hq, hd), lse, True, scale, 0, 0,
+                         dq=dqkv[:, :Nq].view(1, S, Hq, hd), dk=dqkv[:, Nq:Nq + Nkv].view(1, S, Hkv, hd),
+                         dv=dqkv[:, Nq + Nkv:].view(1, S, Hkv, hd))
+        N.rope_strided(dqkv, freqs_real, S, Hq + Hkv, hd, pos_offset, backward=True)
+        dn1 = _gemm_rs(comm, dqkv, wqkv, b_mn=True)
+        dwq, dwk, dwv = _wgrad(dqkv, xg1, (p_wq, p_wk, p_wv))
+        dx, dw_an = N.rmsnorm_bwd_res(dn1, x2, wan, rstd1, dh)
+        return (None, dx.view(1, S_loc, D), None, None, None, None, None,
+                dw_an.to(p_an.dtype), dwq, dwk, dwv, dwo, dw_fn.to(p_fn.dtype), dw1, dw2, dw3)
+
+
+def block_tp_supported(blk, x, comm) -> bool:
+    att, ffn = blk.attention, blk.feed_forward
+    hd = att.head_dim
+    return (fusable(x, comm) and hd in (64, 128) and all(l.bias is None for l in (att.wq, att.wk, att.wv, att.wo, ffn.w1, ffn.w2, ffn.w3))
+            and att.wq.weight.shape[0] % hd == 0 and att.wk.weight.shape[0] % hd == 0)
+
+
+def run_block_tp(blk, x, freqs_cis, pos_offset, comm):
+    """x: this rank's sequence shard [1, S/T, D] of a block that went through ``llama_tp_plan(sequence_parallel=True)``."""
+    att, ffn = blk.attention, blk.feed_forward
+    hd = att.head_dim
+    fr = torch.view_as_real(freqs_cis) if freqs_cis.is_complex() else freqs_cis
+    if not fr.is_contiguous():
+        fr = fr.contiguous()
+    return LlamaBlockTPFn.apply(comm, x, fr, pos_offset, blk.attention_norm.eps, att.wq.weight.shape[0] // hd,
+                                att.wk.weight.shape[0] // hd, blk.attention_norm.weight, att.wq.weight, att.wk.weight,
+                                att.wv.weight, att.wo.weight, blk.ffn_norm.weight, ffn.w1.weight, ffn.w2.weight, ffn.w3.weight)
+
+
 def linear_ar(comm, x, w, bias: Optional[torch.Tensor] = None):
     """Row-parallel linear with an all-reduced (replicated) output; rows of ``x`` must be divisible by the TP degree."""
     return _LinearAR.apply(comm, x, w, bias)
