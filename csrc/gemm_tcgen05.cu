@@ -14,6 +14,7 @@
 // All three operand-major combinations run on the same kernel through the UMMA
 // descriptor major-ness bits, so no transposes are ever materialised.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -85,16 +86,20 @@ constexpr int kGroupM = 8;     // rasterisation group
 constexpr int kGemmThreads = 192;
 constexpr int kSmemBudget = 232448 - 2048;  // 227 KB minus alignment slack and barriers
 
-template <int CG, int BN>
+// EPI = 1: the epilogue stages the bf16 output tile in shared memory (128-byte-swizzled 64-column slabs) and writes it with
+// TMA tensor stores - used by the GEMM -> reduce-scatter variant, whose destination is the OWNER rank's slab over NVLink:
+// full 128-byte lines leave the SM as bulk transfers instead of one 16-byte peer store per thread and row.
+template <int CG, int BN, int EPI = 0>
 struct GemmCfg {
   static constexpr int kLoadN = BN / CG;  // B rows loaded by each CTA
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBBytes = kLoadN * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagesRaw = kSmemBudget / kStageBytes;
+  static constexpr int kEpiBytes = EPI ? kBlockM * BN * 2 : 0;   // [BN / 64 slabs][128 rows][128 bytes]
+  static constexpr int kStagesRaw = (kSmemBudget - kEpiBytes) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulators
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 + 256;
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -146,18 +151,21 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_blk = in_group / gsz;
 }
 
-template <int CG, int BN, bool A_MN, bool B_MN, typename OutT, bool FUSED = false>
+struct ScatterMaps { CUtensorMap d[8]; };   // EPI = 1: tensor map over each rank's staging slab set [world * chunk_rows, N]
+
+template <int CG, int BN, bool A_MN, bool B_MN, typename OutT, bool FUSED = false, int EPI = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b, const GemmParams p,
-                    const __grid_constant__ FusedParams fp) {
-  using Cfg = GemmCfg<CG, BN>;
+                    const __grid_constant__ FusedParams fp, const __grid_constant__ ScatterMaps smaps) {
+  using Cfg = GemmCfg<CG, BN, EPI>;
   constexpr int kStages = Cfg::kStages;
   constexpr int kLoadN = Cfg::kLoadN;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  const uint32_t epi_base = smem_base + kStages * Cfg::kStageBytes;   // EPI = 1: output staging (1024-byte aligned)
+  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   // barrier layout (8 bytes each): full[S] | empty[S] | tmem_full[2] | tmem_empty[2] | tmem_ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
@@ -474,6 +482,69 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
       const __nv_bfloat16* rrow = p.residual ? p.residual + row * p.ldr : nullptr;
+      if constexpr (EPI == 1) {
+        // ===== staged epilogue (GEMM -> reduce-scatter): TMEM -> registers -> 128-byte-swizzled shared-memory slabs of
+        // 64 columns -> TMA tensor stores straight into the OWNER rank's slab (peer memory over NVLink) =====
+        const int r_loc = quarter * 32 + lane;                          // row inside this CTA's 128-row tile
+        const long long row0 = (long long)(m_blk * CG + (int)cta_rank) * kBlockM;
+        // the previous tile's stores must have finished READING the staging buffer before it is rewritten
+        if (warp == 2 && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int n0 = n_tile0 + c * 32;
+          if (n0 >= p.N) break;  // warp-uniform
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + c * 32, r);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+          if (rrow && row_ok) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              if (n0 + g * 8 < p.N) {
+                const uint4 b = ld_v4(rrow + n0 + g * 8);
+                v[g * 8 + 0] += bf16lo(b.x); v[g * 8 + 1] += bf16hi(b.x);
+                v[g * 8 + 2] += bf16lo(b.y); v[g * 8 + 3] += bf16hi(b.y);
+                v[g * 8 + 4] += bf16lo(b.z); v[g * 8 + 5] += bf16hi(b.z);
+                v[g * 8 + 6] += bf16lo(b.w); v[g * 8 + 7] += bf16hi(b.w);
+              }
+            }
+          }
+          const uint32_t slab_row = epi_base + (uint32_t)(c >> 1) * 16384u + (uint32_t)r_loc * 128u;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t chunk = (uint32_t)((c & 1) * 4 + g) ^ (uint32_t)(r_loc & 7);   // SWIZZLE_128B: 16-byte chunk ^ (row % 8)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                         :: "r"(slab_row + (chunk << 4)), "r"(pack_bf16(v[g * 8 + 0], v[g * 8 + 1])),
+                            "r"(pack_bf16(v[g * 8 + 2], v[g * 8 + 3])), "r"(pack_bf16(v[g * 8 + 4], v[g * 8 + 5])),
+                            "r"(pack_bf16(v[g * 8 + 6], v[g * 8 + 7])) : "memory");
+          }
+        }
+        // the accumulator now lives in shared memory: hand the TMEM stage back to the MMA issuer
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CG == 2) mbar_arrive_cluster(tempty_remote + 8u * as);
+          else mbar_arrive(tempty_bar(as));
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy smem writes -> visible to the TMA unit
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) {
+          const long long owner = row0 / fp.d_chunk_rows;
+          const int dest_row = (int)((long long)fp.rank * fp.d_chunk_rows + (row0 - owner * fp.d_chunk_rows));
+#pragma unroll 1
+          for (int j = 0; j < BN / 64; ++j) {
+            const int col = n_tile0 + j * 64;
+            if (col >= p.N) break;
+            tma_store_2d(&smaps.d[owner], epi_base + (uint32_t)j * 16384u, col, dest_row);
+          }
+          tma_store_commit();
+        }
+        if (++as == 2) { as = 0; aphase ^= 1u; }
+        continue;
+      }
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int n0 = n_tile0 + c * 32;
@@ -566,6 +637,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   }
 
   // ---------------- teardown ----------------
+  if constexpr (EPI == 1) {
+    if (warp == 2 && lane == 0) {   // every tensor store of this CTA has been written (not merely read out of smem)
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      __threadfence_system();
+    }
+  }
   tc_fence_before();
   if constexpr (CG == 2) { __syncthreads(); cluster_sync(); } else __syncthreads();
   if (warp == 0) {
@@ -700,7 +777,8 @@ static int launch_gemm(const void* A, const void* B, const GemmParams& p0, long 
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   FusedParams nofuse = {};
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, nofuse));
+  static const ScatterMaps no_maps = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, nofuse, no_maps));
   return B200_OK;
 }
 
@@ -725,11 +803,11 @@ static int dispatch_cfg(int config, int a_mn, int b_mn, const void* A, const voi
 }
 
 // Fused variants always use the 2-CTA 256x256 configuration, bf16 output.
-template <bool B_MN>
+template <bool B_MN, int EPI = 0>
 static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0, long long lda, long long ldb,
                              const FusedParams& fp, cudaStream_t stream) {
   constexpr int CG = 2, BN = 256;
-  using Cfg = GemmCfg<CG, BN>;
+  using Cfg = GemmCfg<CG, BN, EPI>;
   GemmParams p = p0;
   p.num_m_blocks = ceil_div(p.M, kBlockM * CG);
   p.num_n_blocks = ceil_div(p.N, BN);
@@ -755,7 +833,17 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
     const uint32_t box[2] = {64u, (uint32_t)kBlockK};
     if (int rc = b200_make_tmap(&tb, B, 2, 2, dims, str, box, 1)) return rc;
   }
-  auto kern = gemm_tcgen05_kernel<CG, BN, false, B_MN, __nv_bfloat16, true>;
+  ScatterMaps maps = {};
+  if constexpr (EPI == 1) {
+    // one tensor map per destination rank: its staging buffer [world * chunk_rows, N] bf16, 64-column x 128-row boxes
+    for (int o = 0; o < fp.world; ++o) {
+      const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)((long long)fp.world * fp.d_chunk_rows)};
+      const uint64_t str[1] = {(uint64_t)p.ldd * 2};
+      const uint32_t box[2] = {64u, (uint32_t)kBlockM};
+      if (int rc = b200_make_tmap(&maps.d[o], fp.d_ptrs[o], 2, 2, dims, str, box, 1)) return rc;
+    }
+  }
+  auto kern = gemm_tcgen05_kernel<CG, BN, false, B_MN, __nv_bfloat16, true, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -776,7 +864,7 @@ static int launch_gemm_fused(const void* A, const void* B, const GemmParams& p0,
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp, maps));
   return B200_OK;
 }
 
@@ -851,7 +939,8 @@ static int launch_conv_igemm(const void* x, const void* wmat, void* out, int Nim
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  static const ScatterMaps no_maps = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp, no_maps));
   return B200_OK;
 }
 
@@ -934,7 +1023,8 @@ static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg,
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp));
+  static const ScatterMaps no_maps = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp, no_maps));
   return B200_OK;
 }
 
@@ -1077,6 +1167,14 @@ B200_API int b200_gemm_rs_bf16(const void* A, const void* B, const void* const* 
   fp.d_chunk_rows = M / world;
   const int blocks_per_chunk = ceil_div(M / world, kBlockM * 2);
   fp.m_rot = ((rank + 1) % world) * blocks_per_chunk;  // first the neighbour's rows, own rows last
+  // Scatter through shared memory + TMA tensor stores when every 256-row tile lies inside one owner's chunk (the normal
+  // case: local sequence % 256 == 0); the per-thread peer-store epilogue remains for ragged chunks and as a reference
+  // (B200DIST_GEMM_RS_DIRECT=1).
+  static const bool direct = getenv("B200DIST_GEMM_RS_DIRECT") != nullptr && getenv("B200DIST_GEMM_RS_DIRECT")[0] == '1';
+  if (!direct && world > 1 && (M / world) % (kBlockM * 2) == 0) {
+    if (b_mn_major) return launch_gemm_fused<true, 1>(A, B, p, lda, ldb, fp, stream);
+    return launch_gemm_fused<false, 1>(A, B, p, lda, ldb, fp, stream);
+  }
   if (b_mn_major) return launch_gemm_fused<true>(A, B, p, lda, ldb, fp, stream);
   return launch_gemm_fused<false>(A, B, p, lda, ldb, fp, stream);
 }
