@@ -68,6 +68,57 @@ _IGEMM = os.environ.get("B200DIST_CONV_IGEMM", "1") not in ("", "0")
 _IGEMM_WGRAD = os.environ.get("B200DIST_CONV_IGEMM_WGRAD", "1") not in ("", "0")   # implicit-GEMM weight gradient
 
 
+_STEM = os.environ.get("B200DIST_CONV_STEM_IGEMM", "1") not in ("", "0")
+
+
+def _stem_pad(xh: torch.Tensor, pad: int, Ho: int, Wo: int, KH: int) -> torch.Tensor:
+    """[N, H, W, C<=8] -> zero-padded [N, Hp, Wp, 8] bf16: `pad` border rows / columns plus what the 8-wide tap window and
+    the last filter row reach (see csrc/gemm_tcgen05.cu, launch_conv_stem)."""
+    Nn, H, W, Cc = xh.shape
+    Hp = max(H + 2 * pad, 2 * (Ho - 1) + KH + 1)
+    Wp = max(W + 2 * pad, 2 * (Wo - 1) + 8)
+    xp = torch.zeros((Nn, Hp, Wp, 8), dtype=_BF16, device=xh.device)
+    xp[:, pad:pad + H, pad:pad + W, :Cc] = xh
+    return xp
+
+
+def _stem_wmat(w: torch.Tensor) -> torch.Tensor:
+    """[K, C, KH, KW<=8] -> bf16 [K, KH * 64] in (kh, kw 0..7, c 0..7) order, zero where kw >= KW or c >= C."""
+    K, Cc, KH, KW = w.shape
+    wm = torch.zeros((K, KH, 8, 8), dtype=_BF16, device=w.device)
+    wm[:, :, :KW, :Cc] = w.permute(0, 2, 3, 1)
+    return wm.reshape(K, KH * 64)
+
+
+class _StemConvFn(Function):
+    """Stride-2 KxK convolution on <= 8 input channels (ResNet conv1) as an implicit GEMM; no input gradient."""
+
+    @staticmethod
+    def forward(ctx, x, w, pad):
+        xh = _nhwc(x if x.dtype == _BF16 else x.to(_BF16))
+        Nn, H, W, Cc = xh.shape
+        K, _, KH, KW = w.shape
+        Ho, Wo = _conv_geom(H, W, KH, KW, 2, pad)
+        xp = _stem_pad(xh, pad, Ho, Wo, KH)
+        y = N.conv2d_stem(xp, _stem_wmat(w), Ho, Wo, KH)
+        ctx.save_for_backward(xp, w)
+        ctx.x_dtype = x.dtype
+        return _nchw_view(y)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xp, w = ctx.saved_tensors
+        K, Cc, KH, KW = w.shape
+        dyh = _nhwc(dy if dy.dtype == _BF16 else dy.to(_BF16)).contiguous()
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dwm = N.conv2d_stem_wgrad(xp, dyh, KH)                               # [K, KH * 64] fp32
+            dw = dwm.view(K, KH, 8, 8)[:, :, :KW, :Cc].permute(0, 3, 1, 2).to(w.dtype)
+        if ctx.needs_input_grad[0]:
+            raise NotImplementedError("stem convolution: input gradients are not implemented (images need none)")
+        return None, dw, None
+
+
 class _Conv2dFn(Function):
     @staticmethod
     def forward(ctx, x, w, bias, stride, pad):
@@ -148,6 +199,12 @@ class _Conv2dFn(Function):
 def conv2d(x, weight, bias=None, stride: int = 1, padding: int = 0):
     if not x.is_cuda:
         return F.conv2d(x, weight, bias, stride, padding)
+    K, Cc, KH, KW = weight.shape
+    if (_STEM and int(stride) == 2 and Cc <= 8 and KH == KW and 3 <= KW <= 8 and K <= 64 and K % 8 == 0 and bias is None
+            and not x.requires_grad and x.dtype in (_BF16, torch.float32) and x.shape[-1] // 2 <= 256
+            and x.shape[0] * (x.shape[-2] // 2) * (x.shape[-1] // 2) >= 128):
+        y = _StemConvFn.apply(x, weight, int(padding))
+        return y if x.dtype == _BF16 else y.float()
     return _Conv2dFn.apply(x, weight, bias, int(stride), int(padding))
 
 

@@ -334,6 +334,26 @@ def conv2d_igemm(x_nhwc, wmat, KH: int, KW: int, pad: int, bias=None, residual=N
     return out
 
 
+def conv2d_stem(xp_nhwc, wmat, Ho: int, Wo: int, KH: int):
+    """Small-channel stride-2 stem convolution: xp [N, Hp, Wp, 8] bf16 (zero-padded channels + border), wmat [Cout, KH * 64]."""
+    Nn, Hp, Wp, Cc = xp_nhwc.shape
+    assert Cc == 8 and xp_nhwc.is_contiguous() and wmat.is_contiguous() and wmat.shape[1] == KH * 64
+    Cout = wmat.shape[0]
+    out = torch.empty((Nn, Ho, Wo, Cout), dtype=torch.bfloat16, device=xp_nhwc.device)
+    L.call("conv2d_stem_bf16", L.ptr(xp_nhwc), L.ptr(wmat), L.ptr(out), I(Nn), I(Hp), I(Wp), I(Ho), I(Wo), I(Cout), I(KH), _s())
+    return out
+
+
+def conv2d_stem_wgrad(xp_nhwc, dy_nhwc, KH: int):
+    """fp32 [Cout, KH * 64] weight gradient of ``conv2d_stem`` in (kh, kw 0..7, c 0..7) column order."""
+    Nn, Hp, Wp, Cc = xp_nhwc.shape
+    _, Ho, Wo, Cout = dy_nhwc.shape
+    assert Cc == 8 and xp_nhwc.is_contiguous() and dy_nhwc.is_contiguous()
+    dw = torch.empty((Cout, KH * 64), dtype=torch.float32, device=xp_nhwc.device)
+    L.call("conv2d_stem_wgrad", L.ptr(xp_nhwc), L.ptr(dy_nhwc), L.ptr(dw), I(Nn), I(Hp), I(Wp), I(Ho), I(Wo), I(Cout), I(KH), _s())
+    return dw
+
+
 def conv2d_igemm_wgrad(x_nhwc, dy_nhwc, KH: int, KW: int, pad: int, out=None, accumulate: bool = False, stride: int = 1):
     """Implicit-GEMM weight gradient of a stride-1 convolution: x [N, H, W, C], dy [N, Ho, Wo, Cout] bf16 contiguous ->
     fp32 [Cout, KH * KW * C] in (kh, kw, c) column order.  C % 64 == 0, Cout % 8 == 0."""

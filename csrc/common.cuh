@@ -340,6 +340,15 @@ __device__ __forceinline__ void tma_load_4d(uint32_t smem_dst, const void* desc,
       :: "r"(smem_dst), "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(hint)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_5d(uint32_t smem_dst, const void* desc, uint32_t bar,
+                                            int c0, int c1, int c2, int c3, int c4,
+                                            uint64_t hint = kEvictNormal) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2], %8;"
+      :: "r"(smem_dst), "l"(desc), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "l"(hint)
+      : "memory");
+}
 __device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t smem_src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                :: "l"(desc), "r"(smem_src), "r"(c0), "r"(c1) : "memory");

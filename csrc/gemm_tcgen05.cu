@@ -76,6 +76,7 @@ struct FusedParams {
   int c_tiles_h, c_tiles_w;
   int c_KW, c_pad, c_cblocks;   // kernel width, padding, C / 64
   int c_stride;                 // convolution stride (1 or 2): input coordinate = output coordinate * stride + tap - pad
+  int c_stem;                   // 1: small-channel stem (see launch_conv_stem): 5-D activation boxes, k-block = one filter row
   int c_box_bytes;              // bytes one box load delivers (the rest of the 128-row A stage stays stale: rows unused)
 };
 
@@ -311,7 +312,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (cv_mode == 1) {
             const int tw = m_blk % fp.c_tiles_w, th = (m_blk / fp.c_tiles_w) % fp.c_tiles_h;
             cv_n0 = (m_blk / (fp.c_tiles_w * fp.c_tiles_h)) * fp.c_nbox;
-            cv_w0 = tw * fp.c_wbox * fp.c_stride - fp.c_pad;
+            cv_w0 = fp.c_stem ? tw * fp.c_wbox : tw * fp.c_wbox * fp.c_stride - fp.c_pad;   // stem: w in OUTPUT pixels
             cv_h0 = th * fp.c_hbox * fp.c_stride - fp.c_pad;
             const int tap = kb0 / fp.c_cblocks;
             cv_a = kb0 - tap * fp.c_cblocks;          // channel block
@@ -337,6 +338,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int cv_wbox = FUSED ? fp.c_wbox : 0, cv_hbox = FUSED ? fp.c_hbox : 0, cv_nbox = FUSED ? fp.c_nbox : 0;
         const int cv_stride = FUSED ? fp.c_stride : 1, cv_cblocks = FUSED ? fp.c_cblocks : 1, cv_KW = FUSED ? fp.c_KW : 1;
         const int cv_tiles_w = FUSED ? fp.c_tiles_w : 1, cv_tiles_h = FUSED ? fp.c_tiles_h : 1;
+        const bool cv_stem = FUSED ? fp.c_stem != 0 : false;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const bool el = elect_one_sync();   // the lane that issues; every lane computes the (uniform) operands
@@ -358,8 +360,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
                 for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
 #pragma unroll
-                for (int j = 0; j < kLoadN / 64; ++j)
-                  tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
+                for (int j = 0; j < kLoadN / 64; ++j) {
+                  if (cv_stem) tma_load_5d(sb + j * 8192, &tmap_b, fb, 0, 0, pw, ph * cv_stride + (n0 >> 6) + j, pn);  // slab = filter row
+                  else tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
+                }
               }
               if (++cv_a == cv_tiles_w) { cv_a = 0; if (++cv_b == cv_tiles_h) { cv_b = 0; ++cv_c; } }
               if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -368,7 +372,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           if constexpr (FUSED && CG == 1 && !A_MN) {
             if (cv_mode == 1) {
-              if (el) tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
+              if (el) {
+                if (cv_stem) tma_load_5d(sa, &tmap_a, fb, 0, 0, cv_w0, cv_h0 + cv_c, cv_n0);   // k-block = filter row kh
+                else tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
+              }
               if (++cv_a == cv_cblocks) { cv_a = 0; if (++cv_b == cv_KW) { cv_b = 0; ++cv_c; } }
               a_done = true;
             }
@@ -1028,6 +1035,152 @@ static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg,
   return B200_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Small-channel stem convolution (ResNet 7x7 stride-2 on RGB) as an implicit GEMM.
+//   The caller hands over xp = the input zero-padded to 8 channels AND spatially ([N, Hp, Wp, 8] bf16, Hp >= 2 (Ho-1) + KH,
+//   Wp >= 2 (Wo-1) + 8).  One output pixel and one filter row kh need the 8 consecutive input pixels
+//   w = 2 wo .. 2 wo + 7 of row h = 2 ho + kh: 8 pixels x 8 channels = 128 contiguous bytes = exactly one swizzled smem row
+//   of a k-block.  A 5-D tensor map {c: 8, kw: 8 (stride one pixel), wo: Wo (stride two pixels), h: Hp, n: N} with box
+//   {8, 8, wbox, 2 hbox (element stride 2), nbox} therefore delivers an A tile of 128 output pixels x 64 K-elements per TMA
+//   instruction; the K index is (kh, kw in 0..7, c in 0..7) with zero weights for kw == KW..7 and c >= C.  No patch matrix
+//   (the im2col path writes and re-reads 2.5 GB per step for ResNet-50 at batch 256).
+static int stem_maps(CUtensorMap* tx, const void* xp, int Nimg, int Hp, int Wp, int Wo, int wbox, int hbox, int nbox) {
+  const uint64_t dims[5] = {8u, 8u, (uint64_t)Wo, (uint64_t)Hp, (uint64_t)Nimg};
+  const uint64_t str[4] = {16u, 32u, (uint64_t)Wp * 16u, (uint64_t)Hp * Wp * 16u};
+  const uint32_t box[5] = {8u, 8u, (uint32_t)wbox, (uint32_t)(hbox * 2), (uint32_t)nbox};
+  const uint32_t est[5] = {1u, 1u, 1u, 2u, 1u};
+  return b200_make_tmap_strided(tx, xp, 2, 5, dims, str, box, est, 1);
+}
+
+static int launch_conv_stem(const void* xp, const void* wmat, void* out, int Nimg, int Hp, int Wp, int Ho, int Wo, int Cout,
+                            int KH, cudaStream_t stream) {
+  constexpr int CG = 1, BN = 64;
+  using Cfg = GemmCfg<CG, BN>;
+  if (Cout > 64 || (Cout % 8) || Hp < 2 * (Ho - 1) + KH || Wp < 2 * (Wo - 1) + 8 || Wo > 256 || Nimg <= 0) {
+    b200_set_error("conv_stem: needs Cout <= 64, Cout %% 8 == 0 and a padded input of at least %d x %d (Cout=%d Hp=%d Wp=%d)",
+                   2 * (Ho - 1) + KH, 2 * (Wo - 1) + 8, Cout, Hp, Wp);
+    return B200_ERR_SHAPE;
+  }
+  FusedParams fp = {};
+  fp.conv_on = 1; fp.c_stem = 1;
+  fp.c_Ho = Ho; fp.c_Wo = Wo; fp.c_N = Nimg;
+  fp.c_wbox = Wo < kBlockM ? Wo : kBlockM;
+  fp.c_hbox = kBlockM / fp.c_wbox; if (fp.c_hbox > Ho) fp.c_hbox = Ho; if (fp.c_hbox < 1) fp.c_hbox = 1;
+  fp.c_nbox = 1;
+  fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
+  fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
+  fp.c_KW = 1; fp.c_pad = 0; fp.c_cblocks = 1; fp.c_stride = 2;
+  fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
+  GemmParams p = {};
+  p.M = Nimg * Ho * Wo; p.N = Cout; p.K = KH * 64;
+  p.D = out; p.ldd = Cout; p.alpha = 1.f;
+  p.num_m_blocks = Nimg * fp.c_tiles_h * fp.c_tiles_w;
+  p.num_n_blocks = 1;
+  p.num_k_blocks = KH;
+  p.num_tiles = p.num_m_blocks;
+  p.splits = 1; p.kb_per_split = p.num_k_blocks;
+  CUtensorMap ta, tb;
+  if (int rc = stem_maps(&ta, xp, Nimg, Hp, Wp, Wo, fp.c_wbox, fp.c_hbox, fp.c_nbox)) return rc;
+  {
+    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N};
+    const uint64_t str[1] = {(uint64_t)p.K * 2};
+    const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)Cfg::kLoadN};
+    if (int rc = b200_make_tmap(&tb, wmat, 2, 2, dims, str, box, 1)) return rc;
+  }
+  auto kern = gemm_tcgen05_kernel<CG, BN, false, false, __nv_bfloat16, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int ctas = b200_sm_count();
+  if (ctas > p.num_tiles) ctas = p.num_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static const ScatterMaps no_maps = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp, no_maps));
+  return B200_OK;
+}
+
+// Weight gradient of the stem: dW[co, (kh, kw8, c8)] (fp32 [Cout, KH * 64]) = sum over output pixels of dY[pixel, co] *
+// xp[n, 2 ho + kh, 2 wo + kw, c]; pixel-box split-K like launch_conv_wgrad, the B slab of filter row kh is one 5-D box.
+static int launch_conv_stem_wgrad(const void* xp, const void* dy, float* dw, int Nimg, int Hp, int Wp, int Ho, int Wo,
+                                  int Cout, int KH, cudaStream_t stream) {
+  constexpr int CG = 1, BN = 128;
+  using Cfg = GemmCfg<CG, BN>;
+  if ((Cout % 8) || Hp < 2 * (Ho - 1) + KH + 1 || Wp < 2 * (Wo - 1) + 8 || Nimg <= 0) {
+    b200_set_error("conv_stem_wgrad: padded input too small or Cout %% 8 != 0 (Cout=%d Hp=%d Wp=%d)", Cout, Hp, Wp);
+    return B200_ERR_SHAPE;
+  }
+  FusedParams fp = {};
+  fp.conv_on = 2; fp.c_stem = 1;
+  fp.c_C = 64;
+  fp.c_Ho = Ho; fp.c_Wo = Wo; fp.c_N = Nimg;
+  fp.c_wbox = Wo < kBlockK ? Wo : kBlockK;
+  fp.c_hbox = kBlockK / fp.c_wbox; if (fp.c_hbox > Ho) fp.c_hbox = Ho; if (fp.c_hbox < 1) fp.c_hbox = 1;
+  fp.c_nbox = 1;
+  fp.c_tiles_w = ceil_div(Wo, fp.c_wbox);
+  fp.c_tiles_h = ceil_div(Ho, fp.c_hbox);
+  fp.c_KW = 1; fp.c_pad = 0; fp.c_cblocks = 1; fp.c_stride = 2;
+  fp.c_box_bytes = fp.c_nbox * fp.c_hbox * fp.c_wbox * 128;
+  GemmParams p = {};
+  p.M = Cout; p.N = KH * 64;
+  p.D = dw; p.ldd = p.N; p.alpha = 1.f;
+  p.num_m_blocks = ceil_div(p.M, kBlockM);
+  p.num_n_blocks = ceil_div(p.N, BN);
+  p.num_k_blocks = Nimg * fp.c_tiles_h * fp.c_tiles_w;
+  p.K = p.num_k_blocks * kBlockK;
+  p.num_tiles = p.num_m_blocks * p.num_n_blocks;
+  int sp = b200_sm_count() / p.num_tiles; if (sp < 2) sp = 2;
+  const int max_by_k = p.num_k_blocks / 4 > 0 ? p.num_k_blocks / 4 : 1;
+  if (sp > max_by_k) sp = max_by_k;
+  if (sp < 2) sp = 2;
+  if (sp > p.num_k_blocks) sp = p.num_k_blocks;
+  if (sp < 2) { b200_set_error("conv_stem_wgrad: fewer than two pixel boxes"); return B200_ERR_UNSUPPORTED; }
+  p.kb_per_split = ceil_div(p.num_k_blocks, sp);
+  p.splits = ceil_div(p.num_k_blocks, p.kb_per_split);
+  if (p.splits < 2) { p.kb_per_split = ceil_div(p.num_k_blocks, 2); p.splits = ceil_div(p.num_k_blocks, p.kb_per_split); }
+  B200_CUDA_CHECK(cudaMemsetAsync(dw, 0, (size_t)p.M * p.N * 4, stream));
+  p.num_tiles *= p.splits;
+  CUtensorMap ta, tb;
+  {
+    const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)Nimg};
+    const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
+    const uint32_t box[4] = {64u, (uint32_t)fp.c_wbox, (uint32_t)fp.c_hbox, (uint32_t)fp.c_nbox};
+    if (int rc = b200_make_tmap(&ta, dy, 2, 4, dims, str, box, 1)) return rc;
+  }
+  if (int rc = stem_maps(&tb, xp, Nimg, Hp, Wp, Wo, fp.c_wbox, fp.c_hbox, fp.c_nbox)) return rc;
+  auto kern = gemm_tcgen05_kernel<CG, BN, true, true, float, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int ctas = b200_sm_count();
+  if (ctas > p.num_tiles) ctas = p.num_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ctas);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static const ScatterMaps no_maps = {};
+  B200_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, fp, no_maps));
+  return B200_OK;
+}
+
 // Wave-quantisation-aware choice between the three tile configurations.
 static int pick_config(int M, int N, int sms) {
   auto eff = [&](int tm, int tn, int units) {
@@ -1212,4 +1365,18 @@ B200_API int b200_conv2d_igemm_wgrad(const void* x, const void* dy, float* dw, i
 B200_API int b200_conv2d_igemm_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
                                              int KH, int KW, int pad, int stride, int accumulate, cudaStream_t stream) {
   return b200::launch_conv_wgrad(x, dy, dw, N, H, W, C, Cout, KH, KW, pad, stride, accumulate, stream);
+}
+
+// Small-channel stride-2 stem convolution (torchvision ResNet conv1: 7x7, stride 2, pad 3, 3 input channels) without a patch
+// matrix.  xp: input zero-padded to 8 channels and spatially by `pad` (+ enough columns for the 8-wide tap window),
+// [N, Hp, Wp, 8] bf16; wmat: [Cout, KH * 64] bf16 in (kh, kw 0..7, c 0..7) order, zeros where kw >= KW or c >= C;
+// out: [N, Ho, Wo, Cout] bf16.  Replaces the cuDNN stem convolution of /root/reference/scripts/main.py:249.
+B200_API int b200_conv2d_stem_bf16(const void* xp, const void* wmat, void* out, int N, int Hp, int Wp, int Ho, int Wo,
+                                   int Cout, int KH, cudaStream_t stream) {
+  return b200::launch_conv_stem(xp, wmat, out, N, Hp, Wp, Ho, Wo, Cout, KH, stream);
+}
+// dw: fp32 [Cout, KH * 64] in the same column order (the caller drops the padded taps / channels).
+B200_API int b200_conv2d_stem_wgrad(const void* xp, const void* dy, float* dw, int N, int Hp, int Wp, int Ho, int Wo, int Cout,
+                                    int KH, cudaStream_t stream) {
+  return b200::launch_conv_stem_wgrad(xp, dy, dw, N, Hp, Wp, Ho, Wo, Cout, KH, stream);
 }

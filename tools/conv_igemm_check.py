@@ -124,5 +124,31 @@ for (B, C, H, W, K, ks, pad) in [(2, 128, 56, 56, 128, 3, 1), (2, 256, 56, 56, 5
         t_im = ev(lambda: cops._im2col(xh, ks, ks, 2, pad, Ho, Wo, C))
         msg += f" | time igemm {t_ig:.0f} us, im2col alone {t_im:.0f} us, cuDNN {t_cudnn:.0f} us"
     print(msg, flush=True)
+# ---- small-channel stem (7x7 stride 2 pad 3 on RGB, 5-D tensor map): forward + weight gradient through the autograd op ----
+for (B, H, W, K, ks, pad) in [(4, 224, 224, 64, 7, 3), (3, 96, 130, 32, 7, 3), (2, 64, 64, 64, 5, 2), (128, 224, 224, 64, 7, 3)]:
+    x = torch.randn(B, 3, H, W, device=dev).bfloat16()
+    w = (torch.randn(K, 3, ks, ks, device=dev) * (1.0 / (3 * ks * ks) ** 0.5)).bfloat16()
+    wa = w.clone().requires_grad_(True)
+    y = cops.conv2d(x, wa, None, 2, pad)
+    ref = F.conv2d(x.float(), w.float(), stride=2, padding=pad)
+    ok = tuple(y.shape) == tuple(ref.shape)
+    err = float((y.float() - ref).abs().max()) if ok else float("inf"); scale = float(ref.abs().max())
+    ok = ok and err <= 0.02 * scale + 0.02
+    dy = torch.randn_like(ref).bfloat16()
+    y.backward(dy)
+    wr = w.float().requires_grad_(True)
+    F.conv2d(x.float(), wr, stride=2, padding=pad).backward(dy.float())
+    e2 = float((wa.grad.float() - wr.grad).abs().max()); s2 = float(wr.grad.abs().max())
+    ok2 = e2 <= 0.03 * s2 + 0.02
+    fails += (not ok) + (not ok2)
+    msg = (f"[{'PASS' if ok else 'FAIL'}] stem igemm B{B} 3x{H}x{W} -> K{K} k{ks} s2 p{pad}: max_err={err:.4g} (|ref| {scale:.3g}) | "
+           f"wgrad max_err={e2:.4g} (|ref| {s2:.3g}) {'PASS' if ok2 else 'FAIL'}")
+    if B >= 128:
+        xc = x.contiguous(memory_format=torch.channels_last)
+        t_st = ev(lambda: cops.conv2d(xc, w, None, 2, pad))
+        import os
+        t_cudnn = ev(lambda: F.conv2d(xc, w, stride=2, padding=pad))
+        msg += f" | time stem igemm (incl. padding copy) {t_st:.0f} us, cuDNN {t_cudnn:.0f} us"
+    print(msg, flush=True)
 print(f"== conv igemm: failures {fails}")
 sys.exit(1 if fails else 0)
