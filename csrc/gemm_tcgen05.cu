@@ -76,7 +76,7 @@ struct FusedParams {
   int c_tiles_h, c_tiles_w;
   int c_KW, c_pad, c_cblocks;   // kernel width, padding, C / 64
   int c_stride;                 // convolution stride (1 or 2): input coordinate = output coordinate * stride + tap - pad
-  int c_stem;                   // 1: small-channel stem (see launch_conv_stem): 5-D activation boxes, k-block = one filter row
+  int c_stem;                   // 1: small-channel stem (see launch_conv_stem): sliding-window activation boxes, k-block = one filter row
   int c_box_bytes;              // bytes one box load delivers (the rest of the 128-row A stage stays stale: rows unused)
 };
 
@@ -361,7 +361,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 for (int j = 0; j < kBlockM / 64; ++j) tma_load_4d(sa + j * 8192, &tmap_a, fb, m0 + j * 64, pw, ph, pn);
 #pragma unroll
                 for (int j = 0; j < kLoadN / 64; ++j) {
-                  if (cv_stem) tma_load_5d(sb + j * 8192, &tmap_b, fb, 0, 0, pw, ph * cv_stride + (n0 >> 6) + j, pn);  // slab = filter row
+                  if (cv_stem) tma_load_4d(sb + j * 8192, &tmap_b, fb, 0, pw, ph * cv_stride + (n0 >> 6) + j, pn);  // slab = filter row
                   else tma_load_4d(sb + j * 8192, &tmap_b, fb, cv_colc[j], pw * cv_stride + cv_colw[j], ph * cv_stride + cv_colh[j], pn);
                 }
               }
@@ -373,7 +373,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if constexpr (FUSED && CG == 1 && !A_MN) {
             if (cv_mode == 1) {
               if (el) {
-                if (cv_stem) tma_load_5d(sa, &tmap_a, fb, 0, 0, cv_w0, cv_h0 + cv_c, cv_n0);   // k-block = filter row kh
+                if (cv_stem) tma_load_4d(sa, &tmap_a, fb, 0, cv_w0, cv_h0 + cv_c, cv_n0);   // k-block = filter row kh
                 else tma_load_4d(sa, &tmap_a, fb, cv_a * 64, cv_w0 + cv_b, cv_h0 + cv_c, cv_n0);   // (channel block, kw, kh)
               }
               if (++cv_a == cv_cblocks) { cv_a = 0; if (++cv_b == cv_KW) { cv_b = 0; ++cv_c; } }
@@ -1040,16 +1040,19 @@ static int launch_conv_wgrad(const void* x, const void* dy, float* dw, int Nimg,
 //   The caller hands over xp = the input zero-padded to 8 channels AND spatially ([N, Hp, Wp, 8] bf16, Hp >= 2 (Ho-1) + KH,
 //   Wp >= 2 (Wo-1) + 8).  One output pixel and one filter row kh need the 8 consecutive input pixels
 //   w = 2 wo .. 2 wo + 7 of row h = 2 ho + kh: 8 pixels x 8 channels = 128 contiguous bytes = exactly one swizzled smem row
-//   of a k-block.  A 5-D tensor map {c: 8, kw: 8 (stride one pixel), wo: Wo (stride two pixels), h: Hp, n: N} with box
-//   {8, 8, wbox, 2 hbox (element stride 2), nbox} therefore delivers an A tile of 128 output pixels x 64 K-elements per TMA
+//   of a k-block.  A tensor map {window: 64 elements, wo: Wo (stride two pixels = 32 bytes, i.e. windows overlap), h: Hp, n: N}
+//   with box {64, wbox, 2 hbox (element stride 2), nbox} therefore delivers an A tile of 128 output pixels x 64 K-elements per TMA
 //   instruction; the K index is (kh, kw in 0..7, c in 0..7) with zero weights for kw == KW..7 and c >= C.  No patch matrix
 //   (the im2col path writes and re-reads 2.5 GB per step for ResNet-50 at batch 256).
 static int stem_maps(CUtensorMap* tx, const void* xp, int Nimg, int Hp, int Wp, int Wo, int wbox, int hbox, int nbox) {
-  const uint64_t dims[5] = {8u, 8u, (uint64_t)Wo, (uint64_t)Hp, (uint64_t)Nimg};
-  const uint64_t str[4] = {16u, 32u, (uint64_t)Wp * 16u, (uint64_t)Hp * Wp * 16u};
-  const uint32_t box[5] = {8u, 8u, (uint32_t)wbox, (uint32_t)(hbox * 2), (uint32_t)nbox};
-  const uint32_t est[5] = {1u, 1u, 1u, 2u, 1u};
-  return b200_make_tmap_strided(tx, xp, 2, 5, dims, str, box, est, 1);
+  // dimension 0 is the 64-element (8 pixels x 8 channels = 128 bytes) window itself, dimension 1 slides it by two pixels:
+  // the dimensions overlap in memory, which the TMA unit handles (tools/microbench/tma5d_probe.cu); a 16-byte inner box
+  // under SWIZZLE_128B does NOT work (it faults), so the window must be the innermost dimension as a whole.
+  const uint64_t dims[4] = {64u, (uint64_t)Wo, (uint64_t)Hp, (uint64_t)Nimg};
+  const uint64_t str[3] = {32u, (uint64_t)Wp * 16u, (uint64_t)Hp * Wp * 16u};
+  const uint32_t box[4] = {64u, (uint32_t)wbox, (uint32_t)(hbox * 2), (uint32_t)nbox};
+  const uint32_t est[4] = {1u, 1u, 2u, 1u};
+  return b200_make_tmap_strided(tx, xp, 2, 4, dims, str, box, est, 1);
 }
 
 static int launch_conv_stem(const void* xp, const void* wmat, void* out, int Nimg, int Hp, int Wp, int Ho, int Wo, int Cout,
@@ -1111,7 +1114,7 @@ static int launch_conv_stem(const void* xp, const void* wmat, void* out, int Nim
 }
 
 // Weight gradient of the stem: dW[co, (kh, kw8, c8)] (fp32 [Cout, KH * 64]) = sum over output pixels of dY[pixel, co] *
-// xp[n, 2 ho + kh, 2 wo + kw, c]; pixel-box split-K like launch_conv_wgrad, the B slab of filter row kh is one 5-D box.
+// xp[n, 2 ho + kh, 2 wo + kw, c]; pixel-box split-K like launch_conv_wgrad, the B slab of filter row kh is one sliding-window box.
 static int launch_conv_stem_wgrad(const void* xp, const void* dy, float* dw, int Nimg, int Hp, int Wp, int Ho, int Wo,
                                   int Cout, int KH, cudaStream_t stream) {
   constexpr int CG = 1, BN = 128;

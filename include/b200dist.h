@@ -68,7 +68,7 @@ B200DIST_API int b200_conv2d_igemm_strided_bf16(const void* x, const void* wmat,
 B200DIST_API int b200_conv2d_igemm_wgrad_strided(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int Cout,
                                                  int KH, int KW, int pad, int stride, int accumulate, cudaStream_t stream);
 /* small-channel stride-2 stem (ResNet conv1, 7x7 / 2 on RGB; /root/reference/scripts/main.py:249 via torchvision): the input
- * comes zero-padded to 8 channels and spatially, a 5-D tensor map turns (8 taps x 8 channels) into one 128-byte operand row */
+ * comes zero-padded to 8 channels and spatially, a sliding-window tensor map turns (8 taps x 8 channels) into one 128-byte operand row */
 B200DIST_API int b200_conv2d_stem_bf16(const void* xp, const void* wmat, void* out, int N, int Hp, int Wp, int Ho, int Wo,
                                        int Cout, int KH, cudaStream_t stream);
 B200DIST_API int b200_conv2d_stem_wgrad(const void* xp, const void* dy, float* dw, int N, int Hp, int Wp, int Ho, int Wo,
