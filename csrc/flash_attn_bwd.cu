@@ -110,7 +110,7 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t tmem_ptr_addr = bar + 8u * (6 + 2 * kFbStages);
 
   const AttnParams& a = p.a;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
   const int kv_blk = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
   const int kv0 = kv_blk * kFbBlock;
   const int G = a.H / a.Hkv;
@@ -165,28 +165,37 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && n_iters > 0) {
+    if (n_iters > 0) {
+      // Whole warp in the schedule, one elected lane issues; shared-memory descriptors are a 64-bit add away from six
+      // per-kernel bases (see elect_one_sync).  A 64-query step issues 24 MMAs worth ~1030 tensor cycles: with ~16
+      // instructions of descriptor building per MMA on a single lane the ISSUE was the longer path.
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, kFbSub, false, false);  // [128 keys] x [64 queries], K = hd
       constexpr uint32_t idesc_acc = umma_idesc_bf16(128, HD, false, true);     // TMEM A x MN-major B, K = 64 queries
+      const uint64_t dK0 = umma_smem_desc_sw128(sK, 16, 1024), dV0 = umma_smem_desc_sw128(sV, 16, 1024);
+      const uint64_t dQk = umma_smem_desc_sw128(sQ(0), 16, 1024), dDOk = umma_smem_desc_sw128(sDO(0), 16, 1024);          // K-major views
+      const uint64_t dQm = umma_smem_desc_sw128(sQ(0), 8192, 1024), dDOm = umma_smem_desc_sw128(sDO(0), 8192, 1024);      // MN-major views
+      constexpr uint32_t kRingStep = (uint32_t)(2 * kSub) >> 4;   // address-field distance between ring stages
       auto issue_sdp = [&](int it) {
         const int st = it % kFbStages, bb = it & 1;
         mbar_wait(qdo_full(st), (it / kFbStages) & 1);
         tc_fence_after();
+        const uint64_t q = dQk + (uint64_t)(st * kRingStep), g = dDOk + (uint64_t)(st * kRingStep);
+        const uint32_t ds_ = tS(bb), dp_ = tDP(bb);
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;   // resident 128-row tiles: 16 KB per hd half
-          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;    // streamed 64-row tiles: 8 KB per hd half
-          umma_f16_ss<1>(tS(bb), umma_smem_desc_sw128(sK + offa, 16, 1024),
-                         umma_smem_desc_sw128(sQ(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
-        }
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint32_t offa = ((kk >> 2) * 16384 + (kk & 3) * 32) >> 4;   // resident 128-row tiles: 16 KB per hd half
+            const uint32_t offb = ((kk >> 2) * 8192 + (kk & 3) * 32) >> 4;    // streamed 64-row tiles: 8 KB per hd half
+            umma_f16_ss<1>(ds_, dK0 + offa, q + offb, idesc_s, kk > 0 ? 1u : 0u);
+          }
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
-          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
-          umma_f16_ss<1>(tDP(bb), umma_smem_desc_sw128(sV + offa, 16, 1024),
-                         umma_smem_desc_sw128(sDO(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint32_t offa = ((kk >> 2) * 16384 + (kk & 3) * 32) >> 4;
+            const uint32_t offb = ((kk >> 2) * 8192 + (kk & 3) * 32) >> 4;
+            umma_f16_ss<1>(dp_, dV0 + offa, g + offb, idesc_s, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(sdp_full(bb));
         }
-        umma_commit(sdp_full(bb));
       };
       mbar_wait(kv_full, 0);
       issue_sdp(0);
@@ -195,22 +204,25 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
         const int st = it % kFbStages, bb = it & 1;
         mbar_wait(pds_ready(bb), (it >> 1) & 1);
         tc_fence_after();
+        const uint64_t qm = dQm + (uint64_t)(st * kRingStep), gm = dDOm + (uint64_t)(st * kRingStep);
+        const uint32_t ps = tS(bb), pd = tDP(bb);
+        const uint32_t acc0 = it > 0 ? 1u : 0u;
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < kFbSub / 16; ++kk) {
-          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;      // P^T / dS^T live where each half read its scores
-          umma_f16_ts<1>(tDV, tS(bb) + acol, umma_smem_desc_sw128(sDO(st) + kk * 2048, 8192, 1024), idesc_acc,
-                         (it > 0 || kk > 0) ? 1u : 0u);
-        }
+          for (int kk = 0; kk < kFbSub / 16; ++kk) {
+            const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;      // P^T / dS^T live where each half read its scores
+            umma_f16_ts<1>(tDV, ps + acol, gm + (uint64_t)(kk * (2048 >> 4)), idesc_acc, kk > 0 ? 1u : acc0);
+          }
 #pragma unroll
-        for (int kk = 0; kk < kFbSub / 16; ++kk) {
-          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
-          umma_f16_ts<1>(tDK, tDP(bb) + acol, umma_smem_desc_sw128(sQ(st) + kk * 2048, 8192, 1024), idesc_acc,
-                         (it > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < kFbSub / 16; ++kk) {
+            const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
+            umma_f16_ts<1>(tDK, pd + acol, qm + (uint64_t)(kk * (2048 >> 4)), idesc_acc, kk > 0 ? 1u : acc0);
+          }
+          umma_commit(qdo_empty(st));
         }
-        umma_commit(qdo_empty(st));
         if (it + 2 < n_iters) issue_sdp(it + 2);   // reuses buffer bb: ordered after the two MMAs above
       }
-      umma_commit(acc_done);
+      if (elect_one_sync()) umma_commit(acc_done);
     }
     __syncwarp();
   } else {
@@ -321,7 +333,7 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t tmem_ptr_addr = bar + 8u * (6 + 2 * kFbStages);
 
   const AttnParams& a = p.a;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
   const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;
   const int h = blockIdx.y, b = blockIdx.z;
   const int hk = h / (a.H / a.Hkv);
@@ -373,28 +385,35 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && n_blocks > 0) {
+    if (n_blocks > 0) {
+      // whole warp in the schedule, elected lane issues, descriptors by addition (see the dK / dV kernel)
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, kFbSub, false, false);
       constexpr uint32_t idesc_acc = umma_idesc_bf16(128, HD, false, true);
+      const uint64_t dQ0 = umma_smem_desc_sw128(sQ, 16, 1024), dDO0 = umma_smem_desc_sw128(sDO, 16, 1024);
+      const uint64_t dKk = umma_smem_desc_sw128(sK(0), 16, 1024), dVk = umma_smem_desc_sw128(sV(0), 16, 1024);
+      const uint64_t dKm = umma_smem_desc_sw128(sK(0), 8192, 1024);
+      constexpr uint32_t kRingStep = (uint32_t)(2 * kSub) >> 4;
       auto issue_sdp = [&](int j) {
         const int st = j % kFbStages, bb = j & 1;
         mbar_wait(kv_full(st), (j / kFbStages) & 1);
         tc_fence_after();
+        const uint64_t k_ = dKk + (uint64_t)(st * kRingStep), v_ = dVk + (uint64_t)(st * kRingStep);
+        const uint32_t ds_ = tS(bb), dp_ = tDP(bb);
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
-          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
-          umma_f16_ss<1>(tS(bb), umma_smem_desc_sw128(sQ + offa, 16, 1024),
-                         umma_smem_desc_sw128(sK(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
-        }
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint32_t offa = ((kk >> 2) * 16384 + (kk & 3) * 32) >> 4;
+            const uint32_t offb = ((kk >> 2) * 8192 + (kk & 3) * 32) >> 4;
+            umma_f16_ss<1>(ds_, dQ0 + offa, k_ + offb, idesc_s, kk > 0 ? 1u : 0u);
+          }
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t offa = (kk >> 2) * 16384 + (kk & 3) * 32;
-          const uint32_t offb = (kk >> 2) * 8192 + (kk & 3) * 32;
-          umma_f16_ss<1>(tDP(bb), umma_smem_desc_sw128(sDO + offa, 16, 1024),
-                         umma_smem_desc_sw128(sV(st) + offb, 16, 1024), idesc_s, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint32_t offa = ((kk >> 2) * 16384 + (kk & 3) * 32) >> 4;
+            const uint32_t offb = ((kk >> 2) * 8192 + (kk & 3) * 32) >> 4;
+            umma_f16_ss<1>(dp_, dDO0 + offa, v_ + offb, idesc_s, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(sdp_full(bb));
         }
-        umma_commit(sdp_full(bb));
       };
       mbar_wait(qdo_full, 0);
       issue_sdp(0);
@@ -403,16 +422,20 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
         const int st = j % kFbStages, bb = j & 1;
         mbar_wait(ds_ready(bb), (j >> 1) & 1);
         tc_fence_after();
+        const uint64_t km = dKm + (uint64_t)(st * kRingStep);
+        const uint32_t pd = tDP(bb);
+        const uint32_t acc0 = j > 0 ? 1u : 0u;
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < kFbSub / 16; ++kk) {
-          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
-          umma_f16_ts<1>(tDQ, tDP(bb) + acol, umma_smem_desc_sw128(sK(st) + kk * 2048, 8192, 1024), idesc_acc,
-                         (j > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < kFbSub / 16; ++kk) {
+            const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
+            umma_f16_ts<1>(tDQ, pd + acol, km + (uint64_t)(kk * (2048 >> 4)), idesc_acc, kk > 0 ? 1u : acc0);
+          }
+          umma_commit(kv_empty(st));
         }
-        umma_commit(kv_empty(st));
         if (j + 2 < n_blocks) issue_sdp(j + 2);
       }
-      umma_commit(acc_done);
+      if (elect_one_sync()) umma_commit(acc_done);
     }
     __syncwarp();
   } else {

@@ -51,7 +51,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
   auto pv_done = [&](int t) { return bar + 8u * (13 + t); };
   const uint32_t tmem_ptr_addr = bar + 8u * 15;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
   const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
   const int h = blockIdx.y, b = blockIdx.z;
   const int hk = h / (p.H / p.Hkv);
@@ -122,27 +122,39 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && n_max > 0) {
+    if (n_max > 0) {
       // ===================== MMA issuer =====================
+      // The whole warp walks this schedule and one elected lane issues (see elect_one_sync in common.cuh): descriptor
+      // arithmetic stays in uniform registers and is one 64-bit add per operand off four per-kernel bases, so the 16
+      // UTCHMMA of a QK^T + PV pair issue back to back.  (With a single-lane loop every UTCHMMA carried ~16 instructions
+      // of descriptor building plus an ELECT / branch wrapper - about as long as the 65-cycle MMA it issues.)
       constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, HD, false, true);
+      const uint64_t dq0 = umma_smem_desc_sw128(sQ(0), 16, 1024), dk0 = umma_smem_desc_sw128(sK(0), 16, 1024);
+      const uint64_t dv0 = umma_smem_desc_sw128(sV(0), 16384, 1024);
+      constexpr uint32_t kTileStep = (uint32_t)kTile >> 4;          // address-field distance between consecutive tiles
       auto issue_qk = [&](int t, int j) {
-        const int st = j & 1;
+        const uint64_t qd = dq0 + (uint64_t)(t * kTileStep), kd = dk0 + (uint64_t)((j & 1) * kTileStep);
+        const uint32_t d = tS(t);
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * 16384 + (kk & 3) * 32;
-          umma_f16_ss<1>(tS(t), umma_smem_desc_sw128(sQ(t) + off, 16, 1024),
-                         umma_smem_desc_sw128(sK(st) + off, 16, 1024), idesc_qk, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < HD / 16; ++kk) {
+            const uint32_t off = ((kk >> 2) * 16384 + (kk & 3) * 32) >> 4;
+            umma_f16_ss<1>(d, qd + off, kd + off, idesc_qk, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(s_full(t));
         }
-        umma_commit(s_full(t));
       };
       auto issue_pv = [&](int t, int j) {
-        const int st = j & 1;
+        const uint64_t vd = dv0 + (uint64_t)((j & 1) * kTileStep);
+        const uint32_t d = tO(t), a0 = tS(t);
+        const uint32_t acc0 = j > 0 ? 1u : 0u;
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int kk = 0; kk < kFaBlock / 16; ++kk)
-          umma_f16_ts<1>(tO(t), tS(t) + kk * 8, umma_smem_desc_sw128(sV(st) + kk * 2048, 16384, 1024), idesc_pv,
-                         (j > 0 || kk > 0) ? 1u : 0u);
-        umma_commit(pv_done(t));
+          for (int kk = 0; kk < kFaBlock / 16; ++kk)
+            umma_f16_ts<1>(d, a0 + kk * 8, vd + (uint64_t)(kk * (2048 >> 4)), idesc_pv, kk > 0 ? 1u : acc0);
+          umma_commit(pv_done(t));
+        }
       };
       mbar_wait(q_full, 0);
       mbar_wait(k_full(0), 0);
@@ -150,7 +162,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #pragma unroll
       for (int t = 0; t < kFaTiles; ++t)
         if (n_blk[t] > 0) issue_qk(t, 0);
-      umma_commit(k_empty(0));
+      if (elect_one_sync()) umma_commit(k_empty(0));
       for (int j = 0; j < n_max; ++j) {
         const int st = j & 1;
         const bool more = j + 1 < n_max;
@@ -167,8 +179,10 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
             if (j + 1 < n_blk[t]) issue_qk(t, j + 1);   // overwrites S_t/P_t only after PV_t(j) (in-order pipe)
           }
         }
-        umma_commit(v_empty(st));
-        if (more) umma_commit(k_empty((j + 1) & 1));
+        if (elect_one_sync()) {
+          umma_commit(v_empty(st));
+          if (more) umma_commit(k_empty((j + 1) & 1));
+        }
       }
     }
     __syncwarp();
