@@ -42,3 +42,47 @@ def test_stage_slices_compose_to_the_full_model():
     # uneven split: the last stage takes the remainder
     odd = [TransformerStage(ModelArgs(**{**CFG, "n_layers": 5}), i, 2, init=False).layer_ids for i in range(2)]
     assert odd == [[0, 1, 2], [3, 4]]
+
+
+def test_pack_block_weights_makes_qkv_and_w13_adjacent_and_keeps_values():
+    """models/fused_block.py: packing re-homes q|k|v and w1|w3 into contiguous buffers (values unchanged) so the fused
+    block node can address each group as one row-stacked matrix."""
+    import torch
+
+    from b200dist.models import fused_block
+    from b200dist.models.llama2 import ModelArgs, Transformer
+
+    torch.manual_seed(0)
+    m = Transformer(ModelArgs(dim=32, n_layers=1, n_heads=4, vocab_size=64, max_seq_len=16, multiple_of=16))
+    blk = m.layers[0]
+    before = {n: p.detach().clone() for n, p in blk.named_parameters()}
+    assert fused_block.adjacent_rows((blk.attention.wq.weight, blk.attention.wk.weight, blk.attention.wv.weight)) is None
+    fused_block.pack_block_weights(blk)
+    qkv = fused_block.adjacent_rows((blk.attention.wq.weight, blk.attention.wk.weight, blk.attention.wv.weight))
+    w13 = fused_block.adjacent_rows((blk.feed_forward.w1.weight, blk.feed_forward.w3.weight))
+    assert qkv is not None and tuple(qkv.shape) == (96, 32) and w13 is not None
+    assert torch.equal(qkv[32:64], blk.attention.wk.weight) and torch.equal(w13[w13.shape[0] // 2:], blk.feed_forward.w3.weight)
+    for n, p in blk.named_parameters():
+        assert torch.equal(p, before[n]), n
+    # an in-place update of one parameter is visible through the stacked view (same storage)
+    with torch.no_grad():
+        blk.attention.wv.weight.add_(1.0)
+    assert torch.equal(qkv[64:], blk.attention.wv.weight)
+    # CPU tensors keep the module-by-module path: the fused node never runs here
+    x = torch.randn(1, 8, 32)
+    assert not fused_block.block_supported(blk, x)
+    y = m(torch.randint(0, 64, (1, 8)))
+    assert y.shape == (1, 8, 64)
+
+
+def test_fsdp_unit_layout_pulls_adjacent_groups_together():
+    from b200dist.models.llama2 import ModelArgs, Transformer
+    from b200dist.parallel.fsdp import _ordered_named_parameters
+
+    m = Transformer(ModelArgs(dim=32, n_layers=1, n_heads=4, vocab_size=64, max_seq_len=16, multiple_of=16))
+    names = [n for n, _ in _ordered_named_parameters(m.layers[0])]
+    i = names.index("attention.wq.weight")
+    assert names[i:i + 3] == ["attention.wq.weight", "attention.wk.weight", "attention.wv.weight"]
+    j = names.index("feed_forward.w1.weight")
+    assert names[j + 1] == "feed_forward.w3.weight"
+    assert sorted(names) == sorted(n for n, _ in m.layers[0].named_parameters())

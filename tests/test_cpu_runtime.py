@@ -363,3 +363,18 @@ def test_communicator_refuses_peer_memory_across_hosts():
     from tests.dist_utils import run_distributed
 
     run_distributed(_single_box_worker, 2)
+
+
+@pytest.mark.skipif(not REF.exists(), reason="reference tree not mounted")
+def test_reference_arm_provisions_itself():
+    """baseline/install_ref.py creates baseline/_ref (pip --target + verbatim recipe trees) on demand and is idempotent."""
+    import filecmp
+
+    from baseline import install_ref as ir
+
+    root = ir.ensure_reference()
+    assert root is not None, ir.why_unavailable()
+    assert (root / "utils" / "__init__.py").exists()
+    for rel in ("fsdp_tp/llama2_model.py", "scripts/main.py", "tests/torch_comm_bench.py"):
+        assert filecmp.cmp(REF / rel, ir.reference_path(*rel.split("/")), shallow=False), rel
+    assert ir.ensure_reference() == root
