@@ -3,9 +3,11 @@ results are merged with their log-sum-exp.
 
 Docs-only in the reference (/root/reference/docs/guide/08_sequence_parallel.md:82-143: P steps of isend/irecv to the ring
 neighbour overlapped with ``flash_attention_with_lse`` and an online-softmax merge).  On an NVSwitch box every peer is
-one hop away, so the "ring" is only a schedule: at step t each rank PULLS the K/V chunk of rank (r - t) mod P straight
-out of that rank's symmetric buffer (one peer-memory kernel, prefetched on a side stream while the tcgen05 flash
-kernel works on the current chunk).  Causality is handled by the kernel's ``q_offset`` / ``k_offset`` arguments, so
+one hop away, so the "ring" is only a schedule.  FORWARD on CUDA is ONE kernel (``_ring_fused_forward``): communication
+CTAs inside the flash-attention grid stage the peers' K/V chunks into a local gathered buffer block by block while the
+attention CTAs consume the blocks that have landed; the running (O, m, l) never leave the chip.  The chunk-loop below
+(each rank PULLS the K/V chunk of rank (r - t) mod P out of that rank's symmetric buffer, one flash kernel per chunk, LSE
+merge) remains for backward, for CPU tensors and for shapes the fused kernel does not take.  Causality is handled by the kernel's ``q_offset`` / ``k_offset`` arguments, so
 future chunks cost nothing and the diagonal chunk is masked in-kernel.  Backward re-runs the chunk schedule with the
 merged LSE; dK/dV partials are reduced to their owners with one reduce-scatter.
 """
@@ -35,11 +37,63 @@ def _chunk_attention(q, k, v, causal, scale, q_off, k_off):
     return F_._attention_reference(q, k, v, causal, scale, q_off, k_off)
 
 
+_RING_FUSED = __import__("os").environ.get("B200DIST_RING_FUSED", "1") not in ("", "0")
+_RING_CHANNEL = 10
+_ring_ws = {}
+
+
+def _fused_ok(q, k, comm) -> bool:
+    return (_RING_FUSED and comm.native and comm.world > 1 and q.is_cuda and q.dtype == torch.bfloat16
+            and q.shape[-1] in (64, 128) and q.shape[1] % 128 == 0 and k.shape[1] == q.shape[1]
+            and q.shape[2] % k.shape[2] == 0)
+
+
+def _ring_fused_forward(q, k, v, comm, causal, scale):
+    """Ring attention forward as ONE kernel (csrc/flash_attn_fwd.cu, RingParams): this rank's K/V chunk is placed in a
+    symmetric gathered buffer, communication CTAs inside the attention grid stage the peers' chunks into the local copy
+    block by block (ascending key order, ready flag per 128-key block) and the attention CTAs consume the blocks as they
+    land.  Returns (out, global log-sum-exp): no per-chunk partials, no merge."""
+    import ctypes as C
+
+    from ..ops import _lib as L
+
+    P, r = comm.world, comm.rank
+    B, s, H, hd = q.shape
+    Hkv = k.shape[2]
+    S_total = P * s
+    n_el = 2 * B * S_total * Hkv * hd
+    key = id(comm)
+    ws = _ring_ws.get(key)
+    if ws is None or ws["buf"].nbytes < n_el * 2 or ws["flags"].numel() < 2 * B * (S_total // 128):
+        ws = {"buf": comm.symmetric_buffer(n_el * 2),                         # collective, same order on every rank
+              "flags": torch.zeros(2 * B * (S_total // 128) + 8, dtype=torch.int32, device=q.device), "epoch": 0}
+        _ring_ws[key] = ws
+    kv = ws["buf"].tensor(torch.bfloat16, 0, n_el).view(2, B, S_total, Hkv, hd)
+    kv[0, :, r * s:(r + 1) * s].copy_(k)
+    kv[1, :, r * s:(r + 1) * s].copy_(v)
+    qc = q if (q.stride(-1) == 1 and not any(st % 8 for st in q.stride()[:-1]) and not (q.data_ptr() & 15)) else q.contiguous()
+    out = torch.empty((B, s, H, hd), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, H, s), dtype=torch.float32, device=q.device)
+    ws["epoch"] += 1
+    comm._seq[_RING_CHANNEL] += 1
+    I, LL, U, F = C.c_int, C.c_longlong, C.c_uint, C.c_float
+    L.call("flash_attn_fwd_ring", L.ptr(qc), ws["buf"].ptr_array, L.ptr(out), L.ptr(lse), I(B), I(H), I(Hkv), I(s), I(s), I(hd),
+           LL(qc.stride(0)), LL(qc.stride(1)), LL(qc.stride(2)), LL(out.stride(0)), LL(out.stride(1)), LL(out.stride(2)),
+           F(scale), I(int(causal)), L.ptr(ws["flags"]), U(ws["epoch"]), I(8), comm.flags.ptr_array, L.ptr(comm.counter),
+           I(_RING_CHANNEL), U(comm._seq[_RING_CHANNEL] & 0xFFFFFFFF), I(P), I(r), L.stream_ptr())
+    return out, lse
+
+
 class _RingAttn(Function):
     @staticmethod
     def forward(ctx, q, k, v, comm, causal, scale):
         P, r = comm.world, comm.rank
         B, s, H, hd = q.shape
+        if _fused_ok(q, k, comm):
+            out, lse = _ring_fused_forward(q, k, v, comm, causal, scale)
+            ctx.save_for_backward(q, k, v, out, lse)
+            ctx.meta = (comm, causal, scale)
+            return out
         kv = torch.stack([k, v]).contiguous()                                   # [2, B, s, Hkv, hd]
         chunks = _gather_schedule(kv, comm)                                      # chunks[t] = kv of rank (r - t) % P
         o = torch.zeros((B, s, H, hd), dtype=torch.float32, device=q.device)

@@ -20,6 +20,30 @@ struct AttnParams {
   float* LSE;                      // fp32 [B, H, Sq]
 };
 
+// Ring (context-parallel) attention as ONE forward kernel: K and V of the whole sequence are addressed in a LOCAL gathered
+// buffer [B, S_total, Hkv, hd] whose remote chunks are still arriving while the kernel runs.  A few extra CTAs of the grid
+// ("communication CTAs") pull the peers' chunks out of their symmetric buffers with plain (non-multicast) TMA bulk copies,
+// 128-key block by block in ascending key order, and publish one ready flag per (tensor, batch, block); the loader warp of
+// every attention CTA waits for the flag of the block it is about to load.  (O, m, l) never leave the chip: no per-chunk
+// partial outputs, no log-sum-exp merge.  ring.on == 0 disables all of it.
+struct RingParams {
+  int on;
+  int n_comm;                      // communication CTAs appended to grid.x (blockIdx.y == blockIdx.z == 0 only)
+  int world, rank;
+  int chunk_rows;                  // keys per rank (multiple of 128)
+  long long block_bytes;           // 128 * Hkv * hd * 2: one key block of one tensor of one batch entry
+  long long batch_bytes;           // S_total * Hkv * hd * 2
+  long long v_offset_bytes;        // offset of V behind K inside the gathered buffer (B * batch_bytes)
+  int batch;
+  uint32_t* flags;                 // local, [2 (K, V)][B][S_total / 128], ready when >= epoch
+  uint32_t epoch;
+  const void* src[8];              // rank p's gathered buffer as mapped here (same layout as the local one)
+  void* dst;                       // local gathered buffer
+  uint32_t* sig[8];                // peers' signal pads (arrive / depart rows of the Communicator)
+  uint32_t* counter;               // local counter for the depart handshake
+  int channel; uint32_t seq;
+};
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 

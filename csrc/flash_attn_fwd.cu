@@ -32,11 +32,90 @@ template <int HD>
 __global__ void __launch_bounds__(kFaThreads, 1)
 flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
                       const __grid_constant__ CUtensorMap tmap_k,
-                      const __grid_constant__ CUtensorMap tmap_v, const AttnParams p) {
+                      const __grid_constant__ CUtensorMap tmap_v, const AttnParams p,
+                      const __grid_constant__ RingParams ring) {
   using Cfg = FaCfg<HD>;
   constexpr int kTile = Cfg::kTileBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int n_qt = (int)gridDim.x - (ring.on ? ring.n_comm : 0);     // query-tile CTAs along x
+  if (ring.on && (int)blockIdx.x >= n_qt) {
+    // ===================== communication CTA (ring attention) =====================
+    if (blockIdx.y != 0 || blockIdx.z != 0) return;
+    if (threadIdx.x != 0) return;
+    const int my = (int)blockIdx.x - n_qt, n_ctas = ring.n_comm, W = ring.world;
+    // six 32 KB tiles of dynamic shared memory serve as the copy ring; one mbarrier per slot behind them
+    constexpr int kSlots = 6;
+    const uint32_t cbar = smem_base + kSlots * kTile;
+    for (int i = 0; i < kSlots; ++i) mbar_init(cbar + 8u * i, 1);
+    fence_mbar_init();
+    auto sig_row = [&](int owner, int which) { return ring.sig[owner] + ((size_t)ring.channel * 2 + which) * 32; };
+    auto spin = [&](const uint32_t* f, uint32_t want, bool sys) {
+      uint64_t t0 = 0; uint32_t spins = 0;
+      for (;;) {
+        uint32_t v;
+        if (sys) asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        else asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if ((int32_t)(v - want) >= 0) break;
+        peer_spin_check(t0, spins, "ring attention flag", want, f);
+      }
+    };
+    if (my == 0) {   // my chunk sits in my buffer (stream order put the copy before this kernel): tell every peer
+      __threadfence_system();
+      for (int t = 0; t < W; ++t) asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(sig_row(t, 0) + ring.rank), "r"(ring.seq) : "memory");
+    }
+    const int blocks_per_chunk = ring.chunk_rows / kFaBlock;
+    const int blocks_total = blocks_per_chunk * W;
+    uint32_t phases = 0;
+    // regions in ascending key order (that is the order the attention CTAs consume them): block g of (tensor x, batch bi)
+    const long long n_regions = (long long)blocks_total * 2 * ring.batch;
+    for (long long rg = my; rg < n_regions; rg += n_ctas) {
+      const int g = (int)(rg / (2 * ring.batch));              // global key block
+      const int xb = (int)(rg % (2 * ring.batch));
+      const int x = xb / ring.batch, bi = xb % ring.batch;      // 0 = K, 1 = V
+      const int owner = g / blocks_per_chunk;
+      uint32_t* flag = ring.flags + ((long long)x * ring.batch + bi) * blocks_total + g;
+      if (owner == ring.rank) continue;                        // local chunk: always present, never flagged
+      spin(sig_row(ring.rank, 0) + owner, ring.seq, true);     // the owner's chunk is final
+      const long long off = (long long)x * ring.v_offset_bytes + (long long)bi * ring.batch_bytes + (long long)g * ring.block_bytes;
+      const char* src = reinterpret_cast<const char*>(ring.src[owner]) + off;
+      char* dst = reinterpret_cast<char*>(ring.dst) + off;
+      for (long long b0 = 0; b0 < ring.block_bytes; b0 += (long long)kTile * kSlots) {
+        int nb = 0;
+        for (; nb < kSlots && b0 + (long long)nb * kTile < ring.block_bytes; ++nb) {
+          const long long bo = b0 + (long long)nb * kTile;
+          const uint32_t n = (uint32_t)((ring.block_bytes - bo) < kTile ? (ring.block_bytes - bo) : kTile);
+          mbar_expect_tx(cbar + 8u * nb, n);
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       :: "r"(smem_base + nb * kTile), "l"(src + bo), "r"(n), "r"(cbar + 8u * nb) : "memory");
+        }
+        for (int i = 0; i < nb; ++i) {
+          const long long bo = b0 + (long long)i * kTile;
+          const uint32_t n = (uint32_t)((ring.block_bytes - bo) < kTile ? (ring.block_bytes - bo) : kTile);
+          mbar_wait(cbar + 8u * i, (phases >> i) & 1u);
+          phases ^= (1u << i);
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                       :: "l"(dst + bo), "r"(smem_base + i * kTile), "r"(n) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(flag), "r"(ring.epoch) : "memory");
+    }
+    // depart: a peer may overwrite its chunk (next call) only after everybody stopped reading it
+    __threadfence();
+    const uint32_t done = atomicAdd(ring.counter + ring.channel, 1u) + 1u;
+    if (done == (uint32_t)n_ctas) {
+      ring.counter[ring.channel] = 0;
+      __threadfence_system();
+      for (int t = 0; t < W; ++t) asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(sig_row(t, 1) + ring.rank), "r"(ring.seq) : "memory");
+      for (int t = 0; t < W; ++t) spin(sig_row(ring.rank, 1) + t, ring.seq, true);
+    }
+    return;
+  }
   auto sQ = [&](int t) { return smem_base + kTile * t; };
   auto sK = [&](int s) { return smem_base + kTile * (2 + s); };
   auto sV = [&](int s) { return smem_base + kTile * (4 + s); };
@@ -52,7 +131,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t tmem_ptr_addr = bar + 8u * 15;
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
-  const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
+  const int q_blk = n_qt - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
   const int h = blockIdx.y, b = blockIdx.z;
   const int hk = h / (p.H / p.Hkv);
   const int q_base = q_blk * kFaBlock * kFaTiles;
@@ -109,6 +188,22 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
         const uint32_t par = ((j >> 1) & 1) ^ 1u;
         const int kv0 = j * kFaBlock;
         mbar_wait(k_empty(st), par);
+        if (ring.on && kv0 / ring.chunk_rows != ring.rank) {   // remote key block: wait until it has landed locally
+          const int g = kv0 / kFaBlock, bt = ring.chunk_rows / kFaBlock * ring.world;
+          const uint32_t* fk = ring.flags + (long long)b * bt + g;
+          const uint32_t* fv = ring.flags + ((long long)ring.batch + b) * bt + g;
+          uint64_t t0 = 0; uint32_t spins = 0;
+          for (int w_ = 0; w_ < 2; ++w_) {
+            const uint32_t* f = w_ ? fv : fk;
+            for (;;) {
+              uint32_t v_;
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v_) : "l"(f) : "memory");
+              if ((int32_t)(v_ - ring.epoch) >= 0) break;
+              peer_spin_check(t0, spins, "ring attention block", ring.epoch, f);
+            }
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         mbar_expect_tx(k_full(st), kTile);
 #pragma unroll
         for (int hh = 0; hh < Cfg::kHalves; ++hh)
@@ -328,7 +423,7 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
 template <int HD>
 static int launch_fa_fwd(const void* Q, const void* K, const void* V, const AttnParams& p,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, const RingParams& ring = RingParams{}) {
   using Cfg = FaCfg<HD>;
   CUtensorMap tq, tk, tv;
   if (int rc = make_attn_tmap(&tq, Q, p.B, p.Sq, p.H, HD, p.q_sb, p.q_ss, p.q_sh, kFaBlock)) return rc;
@@ -340,8 +435,8 @@ static int launch_fa_fwd(const void* Q, const void* K, const void* V, const Attn
     B200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
-  dim3 grid(ceil_div(p.Sq, kFaBlock * kFaTiles), p.H, p.B);
-  kern<<<grid, kFaThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, p);
+  dim3 grid(ceil_div(p.Sq, kFaBlock * kFaTiles) + (ring.on ? ring.n_comm : 0), p.H, p.B);
+  kern<<<grid, kFaThreads, Cfg::kSmemBytes, stream>>>(tq, tk, tv, p, ring);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -380,4 +475,57 @@ B200_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V, vo
   }
   if (hd == 128) return launch_fa_fwd<128>(Q, K, V, p, stream);
   return launch_fa_fwd<64>(Q, K, V, p, stream);
+}
+
+// Ring attention forward as one kernel (see RingParams in attn_common.cuh).  Q: this rank's queries [B, Sq, H, hd]
+// (global positions q_offset ..); kv_ptrs[r]: rank r's gathered K/V buffer as mapped here - layout
+// [2 (K, V)][B][S_total][Hkv][hd] bf16, S_total = world * chunk_rows - of which only chunk r is filled (by its owner, before
+// the call); flags: local uint32 [2][B][S_total / 128], zero-initialised once; epoch / seq grow by one per call on the
+// channel.  Communication CTAs stage the peers' chunks into kv_ptrs[rank] block by block while the attention CTAs run.
+// O: [B, Sq, H, hd] (strided), LSE: [B, H, Sq].  hd in {64, 128}, chunk_rows % 128 == 0.
+// No counterpart kernel in the reference (its guide describes the algorithm, docs/guide/08_sequence_parallel.md:82-143).
+B200_API int b200_flash_attn_fwd_ring(const void* Q, const void* const* kv_ptrs, void* O, float* LSE, int B, int H, int Hkv,
+                                      int Sq, int chunk_rows, int hd, long long q_sb, long long q_ss, long long q_sh,
+                                      long long o_sb, long long o_ss, long long o_sh, float scale, int causal, void* flags,
+                                      unsigned epoch, int n_comm, const void* const* sig_ptrs, void* counter, int channel,
+                                      unsigned seq, int world, int rank, cudaStream_t stream) {
+  if (B <= 0 || H <= 0 || Sq <= 0) return B200_OK;
+  if (world < 1 || world > 8 || (chunk_rows % kFaBlock) || !(hd == 64 || hd == 128) || Hkv <= 0 || H % Hkv) {
+    b200_set_error("flash_attn_fwd_ring: unsupported geometry (world=%d chunk_rows=%d hd=%d H=%d Hkv=%d)", world, chunk_rows, hd, H, Hkv);
+    return B200_ERR_SHAPE;
+  }
+  const int S_total = world * chunk_rows;
+  AttnParams p = {};
+  p.B = B; p.H = H; p.Hkv = Hkv; p.Sq = Sq; p.Sk = S_total; p.hd = hd;
+  p.q_sb = q_sb; p.q_ss = q_ss; p.q_sh = q_sh;
+  p.k_sb = (long long)S_total * Hkv * hd; p.k_ss = (long long)Hkv * hd; p.k_sh = hd;
+  p.v_sb = p.k_sb; p.v_ss = p.k_ss; p.v_sh = p.k_sh;
+  p.o_sb = o_sb; p.o_ss = o_ss; p.o_sh = o_sh;
+  p.scale = scale; p.causal = causal; p.q_offset = rank * chunk_rows; p.k_offset = 0;
+  p.O = O; p.LSE = LSE;
+  if (!al16(Q) || !al16(O) || ((q_sb | q_ss | q_sh | o_sb | o_ss | o_sh) & 7)) {
+    b200_set_error("flash_attn_fwd_ring: Q / O must be 16-byte aligned with strides that are multiples of 8");
+    return B200_ERR_SHAPE;
+  }
+  RingParams r = {};
+  r.on = world > 1 ? 1 : 0;
+  r.n_comm = n_comm > 0 ? n_comm : 8;
+  r.world = world; r.rank = rank; r.chunk_rows = chunk_rows; r.batch = B;
+  r.block_bytes = (long long)kFaBlock * Hkv * hd * 2;
+  r.batch_bytes = (long long)S_total * Hkv * hd * 2;
+  r.v_offset_bytes = (long long)B * r.batch_bytes;
+  r.flags = reinterpret_cast<uint32_t*>(flags);
+  r.epoch = epoch;
+  for (int i = 0; i < world; ++i) {
+    r.src[i] = kv_ptrs[i];
+    r.sig[i] = reinterpret_cast<uint32_t*>(const_cast<void*>(sig_ptrs[i]));
+  }
+  r.dst = const_cast<void*>(kv_ptrs[rank]);
+  r.counter = reinterpret_cast<uint32_t*>(counter);
+  r.channel = channel; r.seq = seq;
+  const char* kbase = reinterpret_cast<const char*>(kv_ptrs[rank]);
+  const void* Kp = kbase;
+  const void* Vp = kbase + r.v_offset_bytes;
+  if (hd == 128) return launch_fa_fwd<128>(Q, Kp, Vp, p, stream, r);
+  return launch_fa_fwd<64>(Q, Kp, Vp, p, stream, r);
 }

@@ -84,6 +84,14 @@ B200DIST_API int b200_flash_attn_fwd(const void* Q, const void* K, const void* V
                                  long long o_sb, long long o_ss, long long o_sh,
                                  float scale, int causal, int q_offset, int k_offset,
                                  cudaStream_t stream);
+/* ring (context-parallel) attention forward as ONE kernel: communication CTAs stage the peers' K/V chunks into the local
+ * gathered buffer with plain TMA bulk copies while the attention CTAs consume arrived 128-key blocks; (O, m, l) stay on chip
+ * (the reference only describes the algorithm: docs/guide/08_sequence_parallel.md:82-143) */
+B200DIST_API int b200_flash_attn_fwd_ring(const void* Q, const void* const* kv_ptrs, void* O, float* LSE, int B, int H, int Hkv,
+                                          int Sq, int chunk_rows, int hd, long long q_sb, long long q_ss, long long q_sh,
+                                          long long o_sb, long long o_ss, long long o_sh, float scale, int causal, void* flags,
+                                          unsigned epoch, int n_comm, const void* const* sig_ptrs, void* counter, int channel,
+                                          unsigned seq, int world, int rank, cudaStream_t stream);
 B200DIST_API int b200_flash_attn_bwd(const void* Q, const void* K, const void* V, const void* O,
                                  const void* dO, const float* LSE, float* delta, void* dQ, void* dK,
                                  void* dV, int B, int H, int Hkv, int Sq, int Sk, int hd,

@@ -276,6 +276,47 @@ def main():
         ok &= good
         if rank == 0:
             print(f"[{'PASS' if good else 'FAIL'}] {name} attention vs single GPU: max err out/dq/dk/dv = {['%.3g' % e for e in errs]}", flush=True)
+    # fused ring forward (one kernel: communication CTAs + attention CTAs) vs the chunk loop: non-causal, GQA, timing
+    from b200dist.parallel import ring_attention as ra_mod
+
+    qg = torch.randn(1, S, 8, 128, generator=g).to(dev).to(torch.bfloat16)
+    kg, vg = [torch.randn(1, S, 2, 128, generator=g).to(dev).to(torch.bfloat16) for _ in range(2)]
+    for causal in (False, True):
+        refg = ops.attention(qg, kg, vg, causal=causal)
+        outs = {}
+        for fused in (True, False):
+            ra_mod._RING_FUSED = fused
+            outs[fused] = ring_attention(qg[:, sl].contiguous(), kg[:, sl].contiguous(), vg[:, sl].contiguous(), comm, causal=causal)
+        ra_mod._RING_FUSED = True
+        e_f = float((outs[True].float() - refg[:, sl].float()).abs().max())
+        e_c = float((outs[False].float() - refg[:, sl].float()).abs().max())
+        good = e_f < 3e-2 and e_c < 3e-2
+        ok &= good
+        if rank == 0:
+            print(f"[{'PASS' if good else 'FAIL'}] ring attention forward GQA causal={causal}: fused kernel err {e_f:.3g}, chunk loop err {e_c:.3g}", flush=True)
+    Sl = 4096
+    ql_, kl_, vl_ = [torch.randn(1, Sl, 32, 128, generator=g).to(dev).to(torch.bfloat16) for _ in range(3)]
+
+    def _ev(fn, iters=5):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        s_, e_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s_.record()
+        for _ in range(iters):
+            fn()
+        e_.record(); torch.cuda.synchronize()
+        t_ = torch.tensor([s_.elapsed_time(e_) / iters], device=dev); dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        return float(t_)
+    with torch.no_grad():
+        ra_mod._RING_FUSED = True
+        t_fused = _ev(lambda: ring_attention(ql_, kl_, vl_, comm, causal=True))
+        ra_mod._RING_FUSED = False
+        t_loop = _ev(lambda: ring_attention(ql_, kl_, vl_, comm, causal=True))
+        ra_mod._RING_FUSED = True
+    if rank == 0:
+        print(f"[TIME] ring attention forward, {Sl} tokens per rank x{world}, H32 hd128 causal: fused kernel {t_fused * 1e3:.0f} us | "
+              f"chunk loop + merge {t_loop * 1e3:.0f} us", flush=True)
     x = torch.randn(2, 64, 16 * world, 40, generator=g).to(dev).to(torch.bfloat16)
     w = (torch.randn(64, 64, 3, 3, generator=g) * 0.05).to(dev).to(torch.bfloat16)
     full = cops.conv2d(x, w, None, 1, 1)
