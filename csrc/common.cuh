@@ -94,6 +94,28 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// 2^t for a PAIR of fp32 values on the FMA / integer pipes instead of the MUFU unit (t finite, any sign; results below
+// 2^-126 clamp there).  Round-to-nearest split t = j + f with the 1.5 * 2^23 trick, degree-3 minimax polynomial for 2^f on
+// [-0.5, 0.5] (max relative error 7.5e-5 - two orders below the bf16 rounding of the probabilities it feeds), exponent
+// inserted by integer add.  The softmax of the attention forward is bound by the exponential unit (one MUFU result per
+// element against 2 x 128 x 128 x hd MMA flops per tile), so a share of the elements takes this path.
+__device__ __forceinline__ void ex2_poly2(uint64_t t2, float& p0, float& p1) {
+  float a, b;
+  f2_unpack(t2, a, b);
+  t2 = f2_pack(fmaxf(a, -126.f), fmaxf(b, -126.f));
+  const uint64_t r2 = fadd2(t2, f2_pack(12582912.f, 12582912.f));        // low mantissa bits of r = round(t)
+  const uint64_t j2 = fadd2(r2, f2_pack(-12582912.f, -12582912.f));
+  const uint64_t f2 = ffma2(j2, f2_pack(-1.f, -1.f), t2);                // f = t - round(t)
+  uint64_t q2 = ffma2(f2, f2_pack(0.055171459913253784f, 0.055171459913253784f), f2_pack(0.2426108568906784f, 0.2426108568906784f));
+  q2 = ffma2(q2, f2, f2_pack(0.6932609677314758f, 0.6932609677314758f));
+  q2 = ffma2(q2, f2, f2_pack(0.9999281167984009f, 0.9999281167984009f));
+  float qa, qb, ra, rb;
+  f2_unpack(q2, qa, qb);
+  f2_unpack(r2, ra, rb);
+  p0 = __int_as_float(__float_as_int(qa) + (__float_as_int(ra) << 23));   // (0x4B400000 + j) << 23 == j << 23 (mod 2^32)
+  p1 = __int_as_float(__float_as_int(qb) + (__float_as_int(rb) << 23));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

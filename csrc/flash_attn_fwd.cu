@@ -20,6 +20,11 @@ namespace b200 {
 constexpr int kFaThreads = 320;
 constexpr int kFaBlock = 128;   // rows per tile == keys per KV block
 constexpr int kFaTiles = 2;     // query tiles per CTA
+#ifndef B200_FA_POLY_EVERY
+#define B200_FA_POLY_EVERY 2     // 1 pair in this many takes the polynomial exp2 (0 = MUFU only)
+#endif
+constexpr int kFaPolyEvery = B200_FA_POLY_EVERY;
+constexpr int kFaPolyMod = kFaPolyEvery > 0 ? kFaPolyEvery : 1;
 
 template <int HD>
 struct FaCfg {
@@ -367,10 +372,37 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
         }
         tmem_st_32x16(s_addr + c * 16, pk);
       };
-      do_chunk(r0, 0);
-      do_chunk(r1, 1);
-      do_chunk(r2, 2);
-      do_chunk(r3, 3);
+      // unmasked blocks (the vast majority): every kFaPolyEvery-th pair of scores takes the polynomial exp2 on the FMA pipes,
+      // the rest the MUFU unit.  Masked blocks keep MUFU throughout: exp2(-inf) must be exactly 0 for fully masked rows.
+      auto do_chunk_mixed = [&](uint32_t (&r)[32], int c) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const uint64_t t2 = ffma2(f2_pack_u(r[i], r[i + 1]), sl2_2, mneg_2);
+          float p0, p1;
+          if (kFaPolyEvery > 0 && ((i >> 1) % kFaPolyMod) == kFaPolyMod - 1) {
+            ex2_poly2(t2, p0, p1);
+          } else {
+            float t0, t1;
+            f2_unpack(t2, t0, t1);
+            p0 = ex2_approx(t0); p1 = ex2_approx(t1);
+          }
+          lsum2 = fadd2(lsum2, f2_pack(p0, p1));
+          pk[i >> 1] = pack_bf16(p0, p1);
+        }
+        tmem_st_32x16(s_addr + c * 16, pk);
+      };
+      if (need_mask || kFaPolyEvery <= 0) {
+        do_chunk(r0, 0);
+        do_chunk(r1, 1);
+        do_chunk(r2, 2);
+        do_chunk(r3, 3);
+      } else {
+        do_chunk_mixed(r0, 0);
+        do_chunk_mixed(r1, 1);
+        do_chunk_mixed(r2, 2);
+        do_chunk_mixed(r3, 3);
+      }
       float ls0, ls1;
       f2_unpack(lsum2, ls0, ls1);
       l_run += ls0 + ls1;
