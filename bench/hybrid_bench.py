@@ -125,7 +125,7 @@ def main():
                 "feed_forward.w2": RowwiseParallel(output_layouts=Shard(1)),
                 "feed_forward.w3": ColwiseParallel(),
             })
-        mp = MixedPrecisionPolicy(param_dtype=torch.bfloat16, reduce_dtype=torch.float32)
+        mp = MixedPrecisionPolicy(param_dtype=torch.bfloat16, reduce_dtype=torch.bfloat16)  # same reduce precision as the repo arm (and as the reference FSDP recipe, resnet_fsdp_training.py:200-203)
         for block in model.layers:
             fully_shard(block, mesh=dp_mesh, mp_policy=mp)
         fully_shard(model, mesh=dp_mesh, mp_policy=mp)

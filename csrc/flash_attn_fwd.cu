@@ -21,7 +21,7 @@ constexpr int kFaThreads = 320;
 constexpr int kFaBlock = 128;   // rows per tile == keys per KV block
 constexpr int kFaTiles = 2;     // query tiles per CTA
 #ifndef B200_FA_POLY_EVERY
-#define B200_FA_POLY_EVERY 2     // 1 pair in this many takes the polynomial exp2 (0 = MUFU only)
+#define B200_FA_POLY_EVERY 0     // 1 pair in this many takes the polynomial exp2 (0 = MUFU only; measured: 2 is SLOWER, 778 vs 836 TFLOP/s - the softmax warps are issue bound, not MUFU bound)
 #endif
 constexpr int kFaPolyEvery = B200_FA_POLY_EVERY;
 constexpr int kFaPolyMod = kFaPolyEvery > 0 ? kFaPolyEvery : 1;
