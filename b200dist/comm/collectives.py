@@ -56,7 +56,8 @@ class Communicator:
         self.oneshot_threshold = 256 << 10
         self._seq = [0] * N_CHANNELS
         self._order = _debug.CollectiveOrderChecker() if _debug.collectives_debug_enabled() else None
-        self.push_threshold = 256 << 10   # all-reduce messages up to this size take the push (latency) path
+        self.push_threshold = 256 << 10   # messages (per-rank payload) up to this size take the push (latency) paths
+        self._push_slot_bytes = 256 << 10   # size of one slot of the push buffers (fixed: they are allocated once)
         self._push_slots = [None] * N_CHANNELS
         self.broadcast2_min_world = 3     # two-stage broadcast pays off once the root would serve >= 2 readers
         # NVLS (switch-side reduction): tried lazily on the first large all-reduce; None = not tried, False = unavailable
@@ -136,7 +137,7 @@ class Communicator:
         assert t.is_contiguous() and out.is_contiguous()
         n = t.numel()
         item = t.element_size()
-        if (algo in (0, 3) and n % 8 == 0 and n * item <= self.push_threshold and t.data_ptr() % 16 == 0
+        if (algo in (0, 3) and n % 8 == 0 and self._push_ok(n * item) and t.data_ptr() % 16 == 0
                 and out.data_ptr() % 16 == 0 and t.dtype in (torch.bfloat16, torch.float32)
                 and out.dtype in (torch.bfloat16, torch.float32)):
             return self._all_reduce_push(t, out, scale, channel)
@@ -261,13 +262,28 @@ class Communicator:
                 return None
         return buf.tensor(dtype, 0, numel)
 
-    def _all_reduce_push(self, t, out, scale, channel):
-        """Latency path (<= push_threshold bytes): one kernel, no staging copy-in / copy-out, no depart handshake."""
+    def _push_slot_buffer(self, channel):
+        """Slot buffer [2][world][push_threshold bytes] of a channel + the parity of this call (sets alternate)."""
         slots = self._push_slots[channel]
         if slots is None:   # collective allocation, same order on every rank
-            slots = self._push_slots[channel] = PeerBuffer(2 * self.world * self.push_threshold, self.group, self.device)
+            slots = self._push_slots[channel] = PeerBuffer(2 * self.world * self._push_slot_bytes, self.group, self.device)
         self._push_count[channel] += 1
-        slot_elems = self.push_threshold // t.element_size()
+        return slots, self._push_count[channel] & 1
+
+    def _push_ok(self, nbytes: int) -> bool:
+        return nbytes <= min(self.push_threshold, self._push_slot_bytes)
+
+    def _gather_push(self, out, inp, nbytes, root, channel):
+        """Latency path of all-gather (root < 0) and broadcast: one kernel, stores straight into the peers' slots."""
+        slots, parity = self._push_slot_buffer(channel)
+        L.call("comm_gather_push", *self._ctx(slots, channel), L.ptr(inp), L.ptr(out), LL(nbytes), LL(self._push_slot_bytes),
+               I(root), I(parity), self._s())
+        return out
+
+    def _all_reduce_push(self, t, out, scale, channel):
+        """Latency path (<= push_threshold bytes): one kernel, no staging copy-in / copy-out, no depart handshake."""
+        slots, _ = self._push_slot_buffer(channel)
+        slot_elems = self._push_slot_bytes // t.element_size()
         L.call("comm_allreduce_push", *self._ctx(slots, channel), L.ptr(t), L.ptr(out), LL(t.numel()), F(scale),
                I(L.dtype_code(t.dtype)), I(L.dtype_code(out.dtype)), LL(slot_elems), I(self._push_count[channel] & 1),
                self._s())
@@ -284,6 +300,9 @@ class Communicator:
             return out
         nbytes = inp.numel() * inp.element_size()
         assert nbytes % 16 == 0, "all_gather shards must be multiples of 16 bytes"
+        aligned = inp.is_contiguous() and out.is_contiguous() and inp.data_ptr() % 16 == 0 and out.data_ptr() % 16 == 0
+        if self._push_ok(nbytes) and aligned and out.numel() * out.element_size() >= nbytes * self.world:
+            return self._gather_push(out, inp, nbytes, -1, channel)
         if self._use_nvls(nbytes * self.world) and inp.is_contiguous() and out.is_contiguous() and inp.data_ptr() % 16 == 0 \
                 and out.data_ptr() % 16 == 0:
             mc = self._nvls_region(channel, nbytes * self.world)
@@ -374,6 +393,14 @@ class Communicator:
             return out
         assert inp.numel() == n * self.world and n % 8 == 0
         total = inp.numel() * inp.element_size()
+        both = (torch.bfloat16, torch.float32)
+        if (self._push_ok(n * inp.element_size()) and inp.dtype in both and out.dtype in both and inp.is_contiguous()
+                and out.is_contiguous() and inp.data_ptr() % 16 == 0 and out.data_ptr() % 16 == 0):
+            slots, parity = self._push_slot_buffer(channel)
+            L.call("comm_reducescatter_push", *self._ctx(slots, channel), L.ptr(inp), L.ptr(out), LL(n), F(scale),
+                   I(L.dtype_code(inp.dtype)), I(L.dtype_code(out.dtype)), LL(self._push_slot_bytes // inp.element_size()),
+                   I(parity), self._s())
+            return out
         if (self._use_nvls(total) and inp.dtype in (torch.bfloat16, torch.float32)
                 and out.dtype in (torch.bfloat16, torch.float32) and out.is_contiguous() and out.data_ptr() % 16 == 0):
             mc = self._nvls_region(channel, total)
@@ -435,6 +462,8 @@ class Communicator:
             return t
         assert t.is_contiguous()
         nbytes = t.numel() * t.element_size()
+        if self._push_ok(nbytes) and nbytes % 16 == 0 and t.data_ptr() % 16 == 0:
+            return self._gather_push(t, t, nbytes, src, channel)
         if (self.nvls_broadcast and self.world >= self.nvls_min_world and nbytes >= self.nvls_threshold and nbytes % 16 == 0
                 and t.data_ptr() % 16 == 0 and self._nvls_ready()):
             mc = self._nvls_buf[channel]

@@ -123,6 +123,14 @@ __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
   return r;
 }
 
+// 128-bit load of data a peer stored DURING this kernel (ordered after the flag acquire, never served from a stale line).
+__device__ __forceinline__ uint4 ld_sys_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+
 template <typename T> struct Acc8 {
   float v[8];
   __device__ __forceinline__ void zero() {
@@ -422,6 +430,25 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx 
   comm_depart(c);
 }
 
+// End of the store phase of a push kernel: the last block of the grid raises this rank's flag at every peer (after all
+// the grid's stores), then every block waits until all peers' flags have arrived.
+__device__ __forceinline__ void push_publish_and_wait(const CommCtx& c, int* is_last_smem) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(c.counter + 128 + c.channel, 1u) + 1u;
+    *is_last_smem = (done == gridDim.x);
+    if (*is_last_smem) c.counter[128 + c.channel] = 0;
+  }
+  __syncthreads();
+  if (*is_last_smem && threadIdx.x < c.world) {
+    __threadfence_system();
+    st_release_sys(flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) spin_until(flag_row(c, c.rank, 0) + threadIdx.x, c.seq, "push");
+  __syncthreads();
+}
+
 // push one-shot (latency path for small messages): no staging copy, no depart handshake.
 //   1. every rank stores its input straight from the user tensor into slot [parity][rank] of EVERY peer's slot buffer;
 //   2. the last block to finish raises this rank's arrive flag at every peer (release: the stores are visible first);
@@ -429,7 +456,8 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_twoshot_kernel(CommCtx 
 //      bitwise identical on every rank.
 // Two slot sets alternate (parity): a rank can run at most one collective ahead of the slowest peer (it needs that
 // peer's flag to pass step 3), so the set it overwrites was fully consumed two collectives ago.
-template <typename TIn, typename TOut>
+// RS = 1 turns it into a reduce-scatter: `in` holds world slices of n elements and peer t receives only slice t.
+template <typename TIn, typename TOut, int RS = 0>
 __global__ void __launch_bounds__(512, 1) comm_allreduce_push_kernel(CommCtx c, const TIn* __restrict__ in,
                                                                     TOut* __restrict__ out, long long n, float scale,
                                                                     long long slot_elems, int parity) {
@@ -440,25 +468,22 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_push_kernel(CommCtx c, 
   const uint4* src = reinterpret_cast<const uint4*>(in);
   const long long my_slot16 = ((long long)(parity * c.world + c.rank) * slot_elems * sizeof(TIn)) >> 4;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < nv; i += stride) {
-    const uint4 v = src[i];
+    if constexpr (RS) {
+      uint4 v[kMaxRanks];
 #pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t)
-      if (t < c.world) reinterpret_cast<uint4*>(c.data[(c.rank + t) % c.world])[my_slot16 + i] = v;
+      for (int t = 0; t < kMaxRanks; ++t)
+        if (t < c.world) v[t] = src[(long long)((c.rank + t) % c.world) * nv + i];
+#pragma unroll
+      for (int t = 0; t < kMaxRanks; ++t)
+        if (t < c.world) reinterpret_cast<uint4*>(c.data[(c.rank + t) % c.world])[my_slot16 + i] = v[t];
+    } else {
+      const uint4 v = src[i];
+#pragma unroll
+      for (int t = 0; t < kMaxRanks; ++t)
+        if (t < c.world) reinterpret_cast<uint4*>(c.data[(c.rank + t) % c.world])[my_slot16 + i] = v;
+    }
   }
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t done = atomicAdd(c.counter + 128 + c.channel, 1u) + 1u;
-    is_last_p = (done == gridDim.x);
-    if (is_last_p) c.counter[128 + c.channel] = 0;
-  }
-  __syncthreads();
-  if (is_last_p && threadIdx.x < c.world) {
-    __threadfence_system();
-    st_release_sys(flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
-  }
-  if (threadIdx.x < c.world) spin_until(flag_row(c, c.rank, 0) + threadIdx.x, c.seq, "push");
-  __syncthreads();
+  push_publish_and_wait(c, &is_last_p);
   const uint4* slots = reinterpret_cast<const uint4*>(c.data[c.rank]);
   const long long set16 = ((long long)parity * c.world * slot_elems * sizeof(TIn)) >> 4;
   const long long slot16 = (slot_elems * sizeof(TIn)) >> 4;
@@ -484,6 +509,37 @@ __global__ void __launch_bounds__(512, 1) comm_allreduce_push_kernel(CommCtx c, 
     for (int j = 0; j < (int)(sizeof(acc) / sizeof(float)); ++j) acc[j] *= scale;
     if constexpr (sizeof(TIn) == 2) Vec8<TOut>::store(out + i * 8, reinterpret_cast<const float(&)[8]>(acc));
     else store4(out + i * 4, acc);
+  }
+}
+
+// The same protocol for pure data movement.  root < 0: all-gather (every rank stores its n16 pieces into slot [rank] of
+// every peer, then copies the world slots out in rank order).  root >= 0: broadcast (only the root stores, into slot
+// [root]; the others copy that slot out).  Every rank raises and awaits every flag in both modes: that is what bounds
+// the skew between ranks to one collective and makes the two alternating slot sets sufficient.
+__global__ void __launch_bounds__(512, 1) comm_gather_push_kernel(CommCtx c, const uint4* __restrict__ in,
+                                                                 uint4* __restrict__ out, long long n16,
+                                                                 long long slot16, int parity, int root) {
+  __shared__ int is_last_p;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long set16 = (long long)parity * c.world * slot16;
+  if (root < 0 || root == c.rank) {
+    const long long my_slot16 = set16 + (long long)c.rank * slot16;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride) {
+      const uint4 v = in[i];
+#pragma unroll
+      for (int t = 0; t < kMaxRanks; ++t)
+        if (t < c.world && (root < 0 || t > 0)) reinterpret_cast<uint4*>(c.data[(c.rank + t) % c.world])[my_slot16 + i] = v;
+    }
+  }
+  push_publish_and_wait(c, &is_last_p);
+  const uint4* slots = reinterpret_cast<const uint4*>(c.data[c.rank]) + set16;
+  if (root < 0) {
+    for (int t = 0; t < c.world; ++t)
+      for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
+        out[(long long)t * n16 + i] = ld_sys_v4(slots + (long long)t * slot16 + i);
+  } else if (root != c.rank) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
+      out[i] = ld_sys_v4(slots + (long long)root * slot16 + i);
   }
 }
 
@@ -860,6 +916,44 @@ B200_API int b200_comm_allreduce_push(COMM_ARGS, const void* in, void* out, long
   else if (in_dtype == 1 && out_dtype == 0) ARP(float, __nv_bfloat16);
   else { b200_set_error("allreduce_push: bad dtype"); return B200_ERR_UNSUPPORTED; }
 #undef ARP
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Small-message reduce-scatter, same protocol: `in` = world slices of n elements, out = scale * sum of slice [rank].
+B200_API int b200_comm_reducescatter_push(COMM_ARGS, const void* in, void* out, long long n, float scale, int in_dtype,
+                                          int out_dtype, long long slot_elems, int parity, cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if ((n & 7) || n > slot_elems || (slot_elems & 7) || ((uintptr_t)in & 15) || ((uintptr_t)out & 15)) {
+    b200_set_error("reducescatter_push: n=%lld slot=%lld must be multiples of 8 with n <= slot, 16-byte aligned tensors", n, slot_elems);
+    return B200_ERR_SHAPE;
+  }
+  const long long nv = (n >> 3) * (in_dtype == 0 ? 1 : 2);
+  const int grid = comm_grid(nv, 512, 16);
+#define RSP(TI, TO) comm_allreduce_push_kernel<TI, TO, 1><<<grid, 512, 0, stream>>>(COMM_CTX, (const TI*)in, (TO*)out, n, \
+                                                                                  scale, slot_elems, parity & 1)
+  if (in_dtype == 0 && out_dtype == 0) RSP(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == 0 && out_dtype == 1) RSP(__nv_bfloat16, float);
+  else if (in_dtype == 1 && out_dtype == 1) RSP(float, float);
+  else if (in_dtype == 1 && out_dtype == 0) RSP(float, __nv_bfloat16);
+  else { b200_set_error("reducescatter_push: bad dtype"); return B200_ERR_UNSUPPORTED; }
+#undef RSP
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// Small-message all-gather (root < 0: out = world x bytes, rank order) or broadcast (root >= 0: `out` receives the
+// root's `in`; on the root itself nothing is written).  data_ptrs = the symmetric slot buffer [2][world][slot_bytes].
+B200_API int b200_comm_gather_push(COMM_ARGS, const void* in, void* out, long long bytes, long long slot_bytes, int root,
+                                   int parity, cudaStream_t stream) {
+  COMM_CHECK_WORLD();
+  if (((bytes | slot_bytes) & 15) || bytes > slot_bytes || ((uintptr_t)in & 15) || ((uintptr_t)out & 15) || root >= world) {
+    b200_set_error("gather_push: bytes=%lld slot=%lld must be multiples of 16 with bytes <= slot, 16-byte aligned tensors, root < world",
+                   bytes, slot_bytes);
+    return B200_ERR_SHAPE;
+  }
+  comm_gather_push_kernel<<<comm_grid(bytes >> 4, 512, 16), 512, 0, stream>>>(
+      COMM_CTX, (const uint4*)in, (uint4*)out, bytes >> 4, slot_bytes >> 4, parity & 1, root);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

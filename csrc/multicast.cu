@@ -194,19 +194,66 @@ __device__ __forceinline__ void mc_depart(const McCtx& c, int* is_last_smem) {
     __syncthreads();
   }
 }
-// 8 consecutive elements of the sum over all ranks' replicas, as fp32 (bf16 inputs are accumulated in fp32 by the switch
-// and arrive rounded to bf16 once; fp32 inputs take two 16-byte requests).
+// Where vector i (8 elements) of an fp32 array lives: a warp's 32 vectors cover 256 consecutive floats and lane l takes
+// floats [4l, 4l + 4) and [128 + 4l, 128 + 4l + 4), so each of its two 16-byte requests belongs to a fully used 512-byte
+// warp request.  (A lane reading 32 contiguous bytes as two requests would send every 32-byte sector over NVLink twice.)
+// The ragged tail (fewer than 32 vectors left) falls back to the contiguous layout.  16-bit arrays: o0 = 8 i.
+template <typename T>
+__device__ __forceinline__ void mm_offsets(long long i, long long n8, long long& o0, long long& o1) {
+  if constexpr (sizeof(T) == 2) { o0 = i * 8; o1 = o0 + 4; }
+  else {
+    const long long w = i & ~31LL;
+    if (w + 32 <= n8) { o0 = w * 8 + (i & 31) * 4; o1 = o0 + 128; }
+    else { o0 = i * 8; o1 = o0 + 4; }
+  }
+}
+// vector i of the sum over all ranks' replicas, as fp32 (bf16 inputs are accumulated in fp32 by the switch and arrive
+// rounded to bf16 once; fp32 inputs take two 16-byte requests at the offsets above).
 template <typename TIn>
-__device__ __forceinline__ void mm_ldred8(const TIn* p, float (&v)[8]) {
+__device__ __forceinline__ void mm_ldred8(const TIn* base, long long i, long long n8, float (&v)[8]) {
   if constexpr (sizeof(TIn) == 2) {
-    const uint4 r = mm_ldred_bf16(p);
+    const uint4 r = mm_ldred_bf16(base + i * 8);
     v[0] = bf16lo(r.x); v[1] = bf16hi(r.x); v[2] = bf16lo(r.y); v[3] = bf16hi(r.y);
     v[4] = bf16lo(r.z); v[5] = bf16hi(r.z); v[6] = bf16lo(r.w); v[7] = bf16hi(r.w);
   } else {
+    long long o0, o1;
+    mm_offsets<TIn>(i, n8, o0, o1);
     float a[4], b[4];
-    mm_ldred_f32(p, a);
-    mm_ldred_f32(p + 4, b);
+    mm_ldred_f32(base + o0, a);
+    mm_ldred_f32(base + o1, b);
     v[0] = a[0]; v[1] = a[1]; v[2] = a[2]; v[3] = a[3]; v[4] = b[0]; v[5] = b[1]; v[6] = b[2]; v[7] = b[3];
+  }
+}
+__device__ __forceinline__ void mm_ld4(const float* p, float* v) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void mm_st4(float* p, const float* v) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void mm_st4(__nv_bfloat16* p, const float* v) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&a); u.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+// the 8 values of vector i of an ordinary array that is processed alongside inputs of type TIn (same element positions)
+template <typename TIn, typename T>
+__device__ __forceinline__ void mm_store8(T* out, long long i, long long n8, const float (&v)[8]) {
+  if constexpr (sizeof(TIn) == 2) Vec8<T>::store(out + i * 8, v);
+  else {
+    long long o0, o1;
+    mm_offsets<TIn>(i, n8, o0, o1);
+    mm_st4(out + o0, v); mm_st4(out + o1, v + 4);
+  }
+}
+template <typename TIn>
+__device__ __forceinline__ void mm_load8(const float* src, long long i, long long n8, float (&v)[8]) {
+  if constexpr (sizeof(TIn) == 2) Vec8<float>::load(src + i * 8, v);
+  else {
+    long long o0, o1;
+    mm_offsets<TIn>(i, n8, o0, o1);
+    mm_ld4(src + o0, v); mm_ld4(src + o1, v + 4);
   }
 }
 
@@ -226,13 +273,13 @@ __global__ void __launch_bounds__(512, 1) nvls_reducescatter_kernel(McCtx c, con
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += stride * kU) {
     float v[kU][8];
 #pragma unroll
-    for (int u = 0; u < kU; ++u) if (i + u * stride < n8) mm_ldred8<TIn>(base + (i + u * stride) * 8, v[u]);
+    for (int u = 0; u < kU; ++u) if (i + u * stride < n8) mm_ldred8<TIn>(base, i + u * stride, n8, v[u]);
 #pragma unroll
     for (int u = 0; u < kU; ++u)
       if (i + u * stride < n8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[u][j] *= scale;
-        Vec8<TOut>::store(out + (i + u * stride) * 8, v[u]);
+        mm_store8<TIn>(out, i + u * stride, n8, v[u]);
       }
   }
   mc_depart(c, &is_last);   // the region may be refilled only after every rank has read its slice
@@ -256,15 +303,15 @@ __global__ void __launch_bounds__(512, 1) nvls_rs_adamw_kernel(McCtx c, const TI
   for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n8; i0 += stride * kU) {
     float g[kU][8];
 #pragma unroll
-    for (int u = 0; u < kU; ++u) if (i0 + u * stride < n8) mm_ldred8<TIn>(base + (i0 + u * stride) * 8, g[u]);
+    for (int u = 0; u < kU; ++u) if (i0 + u * stride < n8) mm_ldred8<TIn>(base, i0 + u * stride, n8, g[u]);
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       const long long i = i0 + u * stride;
       if (i >= n8) continue;
       float pv[8], mv[8], vv[8];
-      Vec8<float>::load(master + i * 8, pv);
-      Vec8<float>::load(m + i * 8, mv);
-      Vec8<float>::load(v + i * 8, vv);
+      mm_load8<TIn>(master, i, n8, pv);
+      mm_load8<TIn>(m, i, n8, mv);
+      mm_load8<TIn>(v, i, n8, vv);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float gj = g[u][j] * grad_scale;
@@ -272,10 +319,10 @@ __global__ void __launch_bounds__(512, 1) nvls_rs_adamw_kernel(McCtx c, const TI
         vv[j] = beta2 * vv[j] + (1.f - beta2) * gj * gj;
         pv[j] = pv[j] * decay - step_size * (mv[j] / (sqrtf(vv[j]) / bc2_sqrt + eps));
       }
-      Vec8<float>::store(master + i * 8, pv);
-      Vec8<float>::store(m + i * 8, mv);
-      Vec8<float>::store(v + i * 8, vv);
-      if (lowp) Vec8<__nv_bfloat16>::store(lowp + i * 8, pv);
+      mm_store8<TIn>(master, i, n8, pv);
+      mm_store8<TIn>(m, i, n8, mv);
+      mm_store8<TIn>(v, i, n8, vv);
+      if (lowp) mm_store8<TIn>(lowp, i, n8, pv);
     }
   }
   mc_depart(c, &is_last);

@@ -260,6 +260,14 @@ B200DIST_API int b200_comm_rs_adamw_local(const void* const* slab_ptrs, int worl
 B200DIST_API int b200_comm_allreduce_push(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, const void* in, void* out, long long n, float scale, int in_dtype,
                                       int out_dtype, long long slot_elems, int parity, cudaStream_t stream);
+/* the same latency path for reduce-scatter (in = world slices of n elements) ... */
+B200DIST_API int b200_comm_reducescatter_push(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, const void* in, void* out, long long n, float scale, int in_dtype,
+                                      int out_dtype, long long slot_elems, int parity, cudaStream_t stream);
+/* ... and for all-gather (root < 0) / broadcast (root >= 0) of `bytes` <= slot_bytes */
+B200DIST_API int b200_comm_gather_push(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
+                  int world, int channel, unsigned seq, const void* in, void* out, long long bytes, long long slot_bytes,
+                                      int root, int parity, cudaStream_t stream);
 /* large-message broadcast: scatter from the root, then all-gather among the ranks */
 B200DIST_API int b200_comm_broadcast2(const void* const* data_ptrs, const void* const* flag_ptrs, void* counter, int rank,
                   int world, int channel, unsigned seq, void* out, long long in_off_bytes, long long bytes, int root,

@@ -75,12 +75,31 @@ def main():
             yo = torch.empty(n, device=dev, dtype=torch.float32 if dt == torch.bfloat16 else torch.bfloat16)
             comm.all_reduce(x, scale=0.25, out=yo)
             check(f"all_reduce push cast {dt} n={n}", yo, (ref.float() * 0.25).to(yo.dtype))
-        for n in (8 * 33, 8 * 32 * 5 + 8 * 7, 1 << 18):      # reduce-scatter tails around the 32-vector fp32 layout
-            xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
-            o = torch.empty(n, device=dev, dtype=dt); r = torch.empty(n, device=dev, dtype=dt)
-            dist.reduce_scatter_tensor(r, xin)
-            comm.reduce_scatter(o, xin)
-            check(f"reduce_scatter {dt} n={n}", o, r)
+        keep_push = comm.push_threshold
+        for push in (0, keep_push):                            # pull kernels, then the push (latency) kernels
+            comm.push_threshold = push
+            tag = "push" if push else "pull"
+            for n in (8 * 33, 8 * 32 * 5 + 8 * 7, 1 << 18):      # reduce-scatter tails around the 32-vector fp32 layout
+                xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+                o = torch.empty(n, device=dev, dtype=dt); r = torch.empty(n, device=dev, dtype=dt)
+                dist.reduce_scatter_tensor(r, xin)
+                comm.reduce_scatter(o, xin)
+                check(f"reduce_scatter {tag} {dt} n={n}", o, r)
+            for it in range(4):                                  # back-to-back small collectives alternate the slot sets
+                n = 8 * (it + 1) * 41
+                xin = torch.randint(-8, 8, (n * world,), device=dev).to(dt)
+                r = torch.empty(n, device=dev, dtype=dt); dist.reduce_scatter_tensor(r, xin)
+                o32 = torch.empty(n, device=dev, dtype=torch.float32); comm.reduce_scatter(o32, xin, scale=0.5)
+                check(f"reduce_scatter {tag} scale+cast {dt} n={n} call {it}", o32, r.float() * 0.5)
+                x = torch.randint(-8, 8, (n,), device=dev).to(dt)
+                ref = torch.empty(n * world, device=dev, dtype=dt); dist.all_gather_into_tensor(ref, x)
+                out = torch.empty(n * world, device=dev, dtype=dt); comm.all_gather(out, x)
+                check(f"all_gather {tag} {dt} n={n} call {it}", out, ref)
+                root = it % world
+                b = torch.randint(-8, 8, (n,), device=dev).to(dt); rb = b.clone()
+                dist.broadcast(rb, src=root); comm.broadcast(b, src=root)
+                check(f"broadcast {tag} {dt} n={n} root {root}", b, rb)
+        comm.push_threshold = keep_push
         bb = torch.randint(-8, 8, ((4 << 20) // (2 if dt == torch.bfloat16 else 4) * world // world,), device=dev).to(dt)
         bb = bb[: bb.numel() // (8 * world) * (8 * world)].contiguous(); rbb = bb.clone()
         dist.broadcast(rbb, src=0)
@@ -128,6 +147,7 @@ def main():
     # ---- reduce-scatter / all-gather through the switch (multimem.ld_reduce / multimem.st), forced on at any world size ----
     prev_nv = (comm.nvls_min_world, comm.nvls_threshold)
     comm.nvls_min_world, comm.nvls_threshold = 2, 0
+    keep_push, comm.push_threshold = comm.push_threshold, 0      # small sizes must reach the switch kernels here
     if comm._nvls_ready():
         for dt in (torch.float32, torch.bfloat16):
             for n in (8 * 33, 1 << 18, (1 << 20) + 8 * 5):
@@ -176,6 +196,7 @@ def main():
     elif rank == 0:
         print("[INFO] NVLS unavailable: reduce-scatter / all-gather through the switch not checked", flush=True)
     comm.nvls_min_world, comm.nvls_threshold = prev_nv
+    comm.push_threshold = keep_push
     # fused reduce-scatter + AdamW vs (NCCL reduce-scatter, torch AdamW)
     n = 1 << 16
     g = torch.randn(n * world, device=dev).bfloat16()
