@@ -251,7 +251,8 @@ class Communicator:
     def nvls_tensor(self, numel: int, dtype: torch.dtype, channel: int = 0) -> Optional[torch.Tensor]:
         """Collective: a tensor of ``numel`` elements inside the channel's NVSwitch multicast buffer ("registered"
         memory).  ``all_reduce`` on it (in place, numel % (world * 16 / itemsize) == 0) runs zero-copy through the
-        switch.  None when NVLS is unavailable.  The tensor is valid until a larger request reallocates the buffer."""
+        switch; so do ``reduce_scatter`` with it as the input (channel 2), ``all_gather`` with it as the output (channel 1)
+        and ``broadcast`` of it (channel 3) - pass the channel of the collective that will use it.  None when NVLS is unavailable.  The tensor is valid until a larger request reallocates the buffer."""
         if self.world == 1 or not self.native or not self._nvls_ready():
             return None
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
@@ -303,8 +304,12 @@ class Communicator:
         aligned = inp.is_contiguous() and out.is_contiguous() and inp.data_ptr() % 16 == 0 and out.data_ptr() % 16 == 0
         if self._push_ok(nbytes) and aligned and out.numel() * out.element_size() >= nbytes * self.world:
             return self._gather_push(out, inp, nbytes, -1, channel)
-        if self._use_nvls(nbytes * self.world) and inp.is_contiguous() and out.is_contiguous() and inp.data_ptr() % 16 == 0 \
-                and out.data_ptr() % 16 == 0:
+        if self._use_nvls(nbytes * self.world) and aligned:
+            off = self._registered_offset(out, channel)
+            if off is not None and out.numel() * out.element_size() >= nbytes * self.world:
+                # the output lives in the multicast buffer: the switch writes every shard straight into it on every rank
+                self.all_gather_nvls_into(self._nvls_buf[channel], off, inp, channel)
+                return out
             mc = self._nvls_region(channel, nbytes * self.world)
             if mc is not None:
                 # every rank streams its shard through the switch once (multimem.st); no staging copy of the input
@@ -318,6 +323,17 @@ class Communicator:
     # ------------------------------------------------------------------ NVLS helpers
     def _use_nvls(self, total_bytes: int) -> bool:
         return (self.world >= self.nvls_min_world and total_bytes >= self.nvls_threshold and self._nvls_ready())
+
+    def _registered_offset(self, t: torch.Tensor, channel: int):
+        """Byte offset of ``t`` inside the channel's multicast buffer if it lives there (``nvls_tensor``), else None.  Such
+        "registered" tensors take part in switch collectives where they are: no staging copy in, no copy out."""
+        buf = self._nvls_buf[channel]
+        if buf is None or not t.is_contiguous():
+            return None
+        p, nb = t.data_ptr(), t.numel() * t.element_size()
+        if buf.local_ptr <= p and p + nb <= buf.local_ptr + buf.nbytes and (p - buf.local_ptr) % 16 == 0:
+            return p - buf.local_ptr
+        return None
 
     def _nvls_region(self, channel: int, nbytes: int):
         mc = self._nvls_buf[channel]
@@ -403,6 +419,9 @@ class Communicator:
             return out
         if (self._use_nvls(total) and inp.dtype in (torch.bfloat16, torch.float32)
                 and out.dtype in (torch.bfloat16, torch.float32) and out.is_contiguous() and out.data_ptr() % 16 == 0):
+            off = self._registered_offset(inp, channel)
+            if off is not None:     # the input already sits in the multicast buffer on every rank: reduce it where it is
+                return self.reduce_scatter_nvls_from(out, self._nvls_buf[channel], off, inp.dtype, scale, channel)
             mc = self._nvls_region(channel, total)
             if mc is not None:
                 mc.tensor(inp.dtype, 0, inp.numel()).copy_(inp.reshape(-1))
@@ -466,17 +485,21 @@ class Communicator:
             return self._gather_push(t, t, nbytes, src, channel)
         if (self.nvls_broadcast and self.world >= self.nvls_min_world and nbytes >= self.nvls_threshold and nbytes % 16 == 0
                 and t.data_ptr() % 16 == 0 and self._nvls_ready()):
+            off = self._registered_offset(t, channel)
             mc = self._nvls_buf[channel]
-            if mc is None or mc.nbytes < nbytes:
+            if off is None and (mc is None or mc.nbytes < nbytes):
                 mc = self._nvls_alloc(channel, nbytes)
             if mc is not None:
-                # the root streams its tensor through the switch (multimem.st); the others copy their replica out
+                # the root streams its tensor through the switch (multimem.st); the others copy their replica out -
+                # unless the tensor itself lives in the multicast buffer, in which case the payload lands in place
                 self._seq[channel] += 1
                 if self._order is not None:
                     self._order.record(channel, "broadcast_nvls", nbytes)
+                o = off or 0
                 L.call("comm_broadcast_nvls", self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world),
-                       I(channel), U(self._seq[channel] & 0xFFFFFFFF), L.ptr(t), C.c_void_p(mc.mc_ptr),
-                       C.c_void_p(mc.local_ptr), L.ptr(t), LL(nbytes), I(src), I(self.max_ctas), self._s())
+                       I(channel), U(self._seq[channel] & 0xFFFFFFFF), L.ptr(t), C.c_void_p(mc.mc_ptr + o),
+                       C.c_void_p(mc.local_ptr + o), C.c_void_p(0) if off is not None else L.ptr(t), LL(nbytes), I(src),
+                       I(self.max_ctas), self._s())
                 return t
         pad = (nbytes + 15) // 16 * 16
         buf = self._stage(channel, pad)

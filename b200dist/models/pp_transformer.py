@@ -15,7 +15,8 @@ from .layers import GELU, LayerNorm, Linear
 
 class MHA(nn.Module):
     """Self-attention with fused in-projection (parameter names as nn.MultiheadAttention: in_proj_weight,
-    in_proj_bias, out_proj.*), non-causal like the reference block; dropout on the attention output."""
+    in_proj_bias, out_proj.*), non-causal like the reference block; dropout on the attention PROBABILITIES, as
+    nn.MultiheadAttention(dropout=p) applies it (Philox mask regenerated in backward, ``ops.attention_dropout``)."""
 
     def __init__(self, dim, heads, dropout=0.1):
         super().__init__()
@@ -23,14 +24,14 @@ class MHA(nn.Module):
         self.in_proj_weight = nn.Parameter(torch.empty(3 * dim, dim))
         self.in_proj_bias = nn.Parameter(torch.zeros(3 * dim))
         self.out_proj = Linear(dim, dim)
-        self.drop = nn.Dropout(dropout)
+        self.dropout = dropout
         nn.init.xavier_uniform_(self.in_proj_weight)
 
     def forward(self, x):
         B, S, D = x.shape
         qkv = ops.linear(x, self.in_proj_weight, self.in_proj_bias).view(B, S, 3, self.heads, self.hd)
-        o = ops.attention(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal=False)
-        return self.out_proj(self.drop(o.reshape(B, S, D)))
+        o = ops.attention_dropout(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], self.dropout, causal=False, training=self.training)
+        return self.out_proj(o.reshape(B, S, D))
 
 
 class Block(nn.Module):

@@ -1,7 +1,7 @@
 """Hot ops: hand-written sm_100a kernels behind differentiable PyTorch functions."""
-from .functional import (attention, cross_entropy, embedding, gelu, layer_norm, linear, precompute_freqs_cis,
+from .functional import (attention, attention_dropout, cross_entropy, embedding, gelu, layer_norm, linear, precompute_freqs_cis,
                          relu, rms_norm, rope, silu, swiglu)
 from .optim import FusedAdamW, FusedSGD
 
-__all__ = ["attention", "cross_entropy", "embedding", "gelu", "layer_norm", "linear", "precompute_freqs_cis",
+__all__ = ["attention", "attention_dropout", "cross_entropy", "embedding", "gelu", "layer_norm", "linear", "precompute_freqs_cis",
            "relu", "rms_norm", "rope", "silu", "swiglu", "FusedAdamW", "FusedSGD"]

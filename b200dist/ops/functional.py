@@ -293,6 +293,84 @@ def _attention_reference(q, k, v, causal, scale, q_offset=0, k_offset=0):
     return (p @ vf).transpose(1, 2).to(q.dtype), lse
 
 
+def philox_keep_mask(numel: int, p_drop: float, seed: int, offset: int = 0) -> torch.Tensor:
+    """Host restatement of the dropout mask of ``csrc/softmax_dropout.cu`` (Philox4x32-10, key = seed, counter =
+    (element index / 4, offset), element kept when its 32-bit draw >= p * 2^32): bool [numel] on the CPU.  The oracle of
+    the kernel tests; not used on any training path."""
+    import numpy as np
+
+    n4 = (numel + 3) // 4
+    g = np.arange(n4, dtype=np.uint64)
+    c = [g & 0xFFFFFFFF, g >> np.uint64(32), np.full(n4, offset & 0xFFFFFFFF, np.uint64), np.full(n4, (offset >> 32) & 0xFFFFFFFF, np.uint64)]
+    k0, k1 = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+    M0, M1, W0, W1, mask = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), 0x9E3779B9, 0xBB67AE85, np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c[0], M1 * c[2]
+        c = [(p1 >> np.uint64(32)) ^ c[1] ^ np.uint64(k0), p1 & mask, (p0 >> np.uint64(32)) ^ c[3] ^ np.uint64(k1), p0 & mask]
+        k0, k1 = (k0 + W0) & 0xFFFFFFFF, (k1 + W1) & 0xFFFFFFFF
+    draws = np.stack(c, axis=1).reshape(-1)[:numel]
+    thresh = min(int(p_drop * 4294967296.0), 0xFFFFFFFF)
+    return torch.from_numpy(draws >= np.uint64(thresh))
+
+
+class _AttnDropoutFn(Function):
+    """Explicit attention with dropout on the probabilities: S = Q K^T (batched GEMM), softmax + Philox dropout (one
+    kernel, mask regenerated in backward), O = Pd V.  For small-head recipe models; the flash kernels have no dropout."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, causal, scale, p_drop, seed, offset):
+        # [B, S, H, hd] -> [B, H, S, hd]
+        qh, kh, vh = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+        s = torch.matmul(qh, kh.transpose(-1, -2)).contiguous()
+        probs, dropped = N.softmax_dropout_fwd(s, q.shape[1], scale, causal, p_drop, seed, offset)
+        o = torch.matmul(dropped, vh)
+        ctx.save_for_backward(qh, kh, vh, probs, dropped)
+        ctx.args = (scale, p_drop, seed, offset)
+        return o.transpose(1, 2)
+
+    @staticmethod
+    def backward(ctx, do):
+        qh, kh, vh, probs, dropped = ctx.saved_tensors
+        scale, p_drop, seed, offset = ctx.args
+        doh = do.transpose(1, 2).to(torch.bfloat16)
+        dv = torch.matmul(dropped.transpose(-1, -2), doh)
+        d_dropped = torch.matmul(doh, vh.transpose(-1, -2)).contiguous()
+        ds = N.softmax_dropout_bwd(probs, d_dropped, scale, p_drop, seed, offset)   # regenerates the mask from the seed
+        dq = torch.matmul(ds, kh)
+        dk = torch.matmul(ds.transpose(-1, -2), qh)
+        return dq.transpose(1, 2), dk.transpose(1, 2), dv.transpose(1, 2), None, None, None, None, None
+
+
+_dropout_calls = 0
+
+
+def attention_dropout(q, k, v, p_drop: float, causal: bool = False, scale: Optional[float] = None, training: bool = True,
+                      seed: Optional[int] = None):
+    """Attention with dropout on the softmax probabilities (``nn.MultiheadAttention(dropout=p)`` semantics) on
+    [B, S, H, hd] tensors, H == Hkv.  Without dropout (eval, p == 0) this is :func:`attention`.  The seed comes from
+    torch's generator (so ``torch.manual_seed`` makes runs repeatable); every call advances a Philox offset."""
+    global _dropout_calls
+    if not training or p_drop <= 0.0:
+        return attention(q, k, v, causal=causal, scale=scale)
+    hd = q.shape[-1]
+    scale = float(scale if scale is not None else hd ** -0.5)
+    if not q.is_cuda or k.shape[1] % 4 or k.shape[2] != q.shape[2]:
+        qf, kf, vf = q.transpose(1, 2).float(), k.transpose(1, 2).float(), v.transpose(1, 2).float()
+        s_ = (qf @ kf.transpose(-1, -2)) * scale
+        if causal:
+            Sq, Sk = q.shape[1], k.shape[1]
+            keep = torch.arange(Sk, device=q.device).view(1, -1) <= torch.arange(Sq, device=q.device).view(-1, 1) + (Sk - Sq)
+            s_ = s_.masked_fill(~keep, float("-inf"))
+        pr = F.dropout(torch.softmax(s_, dim=-1), p_drop, training=True)
+        return (pr @ vf).transpose(1, 2).to(q.dtype)
+    if seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())      # host generator: no device sync
+    _dropout_calls += 1
+    in_dtype = q.dtype
+    o = _AttnDropoutFn.apply(_bf16(q), _bf16(k), _bf16(v), causal, scale, float(p_drop), seed, _dropout_calls)
+    return o.to(in_dtype)
+
+
 def attention(q, k, v, causal: bool = True, scale: Optional[float] = None, q_offset: int = 0,
               k_offset: int = 0, return_lse: bool = False):
     """softmax(q k^T * scale [+ causal mask]) v on [B, S, H, hd] tensors (GQA when k/v have fewer heads).

@@ -121,6 +121,28 @@ def rope(x, freqs, pos_offset=0, backward=False, out=None):
     return y
 
 
+def softmax_dropout_fwd(scores, sq: int, scale: float, causal: bool, p_drop: float, seed: int, offset: int):
+    """probs, probs_dropped (bf16, same shape) of ``scores`` [..., sq, sk] (bf16 / fp32, contiguous, sk % 4 == 0)."""
+    assert scores.is_contiguous() and scores.dtype in (torch.bfloat16, torch.float32)
+    cols = scores.shape[-1]
+    rows = scores.numel() // cols
+    probs = torch.empty(scores.shape, device=scores.device, dtype=torch.bfloat16)
+    dropped = torch.empty_like(probs)
+    L.call("softmax_dropout_fwd", L.ptr(scores), L.ptr(probs), L.ptr(dropped), LL(rows), I(cols), I(sq), F(scale),
+           I(1 if causal else 0), F(p_drop), C.c_ulonglong(seed), C.c_ulonglong(offset), I(L.dtype_code(scores.dtype)), _s())
+    return probs, dropped
+
+
+def softmax_dropout_bwd(probs, d_dropped, scale: float, p_drop: float, seed: int, offset: int):
+    assert probs.is_contiguous() and probs.dtype == torch.bfloat16
+    d_dropped = d_dropped.to(torch.bfloat16).contiguous()
+    cols = probs.shape[-1]
+    ds = torch.empty_like(probs)
+    L.call("softmax_dropout_bwd", L.ptr(probs), L.ptr(d_dropped), L.ptr(ds), LL(probs.numel() // cols), I(cols), F(scale),
+           F(p_drop), C.c_ulonglong(seed), C.c_ulonglong(offset), _s())
+    return ds
+
+
 def rope_strided(x2d, freqs, S: int, n_heads: int, hd: int, pos_offset=0, backward=False, out=None):
     """Rotate the first ``n_heads`` heads of every row of ``x2d`` [tokens, ld] (fused QKV buffer), in place by default."""
     assert x2d.dim() == 2 and x2d.stride(1) == 1

@@ -34,7 +34,18 @@ DEFAULT_SIZES = [256 * 4 ** i for i in range(11)]  # 1 KB ... 1 GB of fp32
 
 
 def timed(fn, n, device, world):
+    import gc
+
     out = []
+    gc.collect()
+    gc.disable()        # a collector pause between the two events of one iteration would be charged to the collective
+    try:
+        return _timed(fn, n, device, world, out)
+    finally:
+        gc.enable()
+
+
+def _timed(fn, n, device, world, out):
     for _ in range(n):
         if device.type == "cuda":
             torch.cuda.synchronize()
@@ -73,7 +84,7 @@ def main():
     ap.add_argument("--output_file", default="results/benchmark_results.log")
     ap.add_argument("--impl", default="both", choices=["b200dist", "nccl", "both"])
     ap.add_argument("--no-registered", dest="registered", action="store_false",
-                    help="b200dist all-reduce on an ordinary tensor (staging copies) instead of one inside the multicast buffer")
+                    help="skip the b200dist-registered rows (tensors placed inside the NVSwitch multicast buffer)")
     ap.add_argument("--ops", nargs="+", default=["broadcast", "all_reduce", "all_gather", "reduce_scatter", "send_recv"])
     ap.add_argument("--max_bytes", type=int, default=1 << 30)
     a = ap.parse_args()
@@ -84,6 +95,10 @@ def main():
     from b200dist.comm import Communicator
 
     impls = ["b200dist", "nccl"] if a.impl == "both" else [a.impl]
+    if "b200dist" in impls and a.registered and device.type == "cuda":
+        # second arm of ours: the tensor a collective works on lives in "registered" memory (the NVSwitch multicast buffer;
+        # what ncclMemAlloc + user-buffer registration is to NCCL), so no staging copy in / copy out is needed
+        impls.insert(1, "b200dist-reg")
     comm = Communicator(None, staging_bytes=min(a.max_bytes, 1 << 30) + (1 << 20)) if "b200dist" in impls else None
     if rank == 0:
         os.makedirs(os.path.dirname(os.path.abspath(a.output_file)), exist_ok=True)
@@ -101,35 +116,48 @@ def main():
         gathered = torch.empty(n_pad * world, device=device) if nbytes * world <= (4 << 30) else None
         shard = torch.empty(n_pad // world, device=device)
         for impl in impls:
-            tag = f"{a.backend}" if impl == "nccl" else "b200dist-peer"
+            tag = {"nccl": a.backend, "b200dist": "b200dist-peer", "b200dist-reg": "b200dist-registered"}[impl]
+            reg = impl == "b200dist-reg"
+            if reg and not (world >= comm.nvls_min_world and nbytes >= comm.nvls_threshold and n_pad % (4 * world) == 0):
+                continue            # the switch paths start at nvls_threshold; below it both arms of ours are the same code
+
+            def registered(numel, channel, fill=None):
+                t = comm.nvls_tensor(numel, torch.float32, channel=channel)
+                if t is not None and fill is not None:
+                    t.fill_(fill)
+                return t
             for op in a.ops:
                 if op == "broadcast":
-                    fn = (lambda: comm.broadcast(x, 0)) if impl == "b200dist" else (lambda: dist.broadcast(x, 0))
+                    xb = registered(n_pad, 3, 1.0) if reg else x
+                    if xb is None:
+                        continue
+                    fn = (lambda xb=xb: comm.broadcast(xb, 0)) if impl != "nccl" else (lambda: dist.broadcast(x, 0))
                     size = nbytes
                 elif op == "all_reduce":
-                    if impl == "b200dist":
-                        # large messages: place the tensor in the NVSwitch multicast buffer ("registered" user buffer, what
-                        # ncclMemAlloc + buffer registration is to NCCL) so the all-reduce runs in place through the switch
-                        xr = comm.nvls_tensor(n_pad, torch.float32) if (a.registered and device.type == "cuda" and world >= comm.nvls_min_world
-                                                                        and nbytes >= comm.nvls_threshold and n_pad % (4 * world) == 0) else None
-                        if xr is not None:
-                            xr.fill_(1.0)
-                            fn = (lambda xr=xr: comm.all_reduce(xr, algo=4))
-                        else:
-                            fn = (lambda: comm.all_reduce(x))
+                    xr = registered(n_pad, 0, 1.0) if reg else x
+                    if xr is None:
+                        continue
+                    if reg:
+                        fn = (lambda xr=xr: comm.all_reduce(xr, algo=4))
                     else:
-                        fn = (lambda: dist.all_reduce(x))
+                        fn = (lambda: comm.all_reduce(x)) if impl == "b200dist" else (lambda: dist.all_reduce(x))
                     size = nbytes
                 elif op == "all_gather":
                     if gathered is None:
                         continue
-                    fn = (lambda: comm.all_gather(gathered, x)) if impl == "b200dist" else (lambda: dist.all_gather_into_tensor(gathered, x))
+                    go = registered(n_pad * world, 1) if reg else gathered
+                    if go is None:
+                        continue
+                    fn = (lambda go=go: comm.all_gather(go, x)) if impl != "nccl" else (lambda: dist.all_gather_into_tensor(gathered, x))
                     size = nbytes * world
                 elif op == "reduce_scatter":
-                    fn = (lambda: comm.reduce_scatter(shard, x)) if impl == "b200dist" else (lambda: dist.reduce_scatter_tensor(shard, x))
+                    xi = registered(n_pad, 2, 1.0) if reg else x
+                    if xi is None:
+                        continue
+                    fn = (lambda xi=xi: comm.reduce_scatter(shard, xi)) if impl != "nccl" else (lambda: dist.reduce_scatter_tensor(shard, x))
                     size = nbytes
                 elif op == "send_recv":
-                    if world < 2 or impl == "b200dist":
+                    if world < 2 or impl != "nccl":
                         continue  # p2p stays on NCCL by design (pipeline stages)
 
                     def fn():

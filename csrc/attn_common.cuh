@@ -44,6 +44,29 @@ struct RingParams {
   int channel; uint32_t seq;
 };
 
+// Work per CTA of a causal kernel falls along grid.x, so the ORDER in which CTAs are handed out decides the tail: the
+// hardware dispatches x-fastest, which on a (tile, head, batch) grid runs each head's heavy tiles right before its light
+// ones and leaves a heavy tile of the last head for the very end (measured: SMs active 77 % of the forward kernel at
+// 512 CTAs over 148 SMs).  Read the linear dispatch index tile-major inside GROUPS of `group` heads instead: the
+// heaviest tiles of all heads of a group first, their lightest last (longest-processing-time-first), one group after
+// the other.  A group is large enough that its light tiles keep the SMs busy while the next group's heavy ones start
+// (group * work per head >= heaviest tile * SMs), and small enough that the K / V (and Q / dO) of the heads in flight
+// stay in L2 - fully tile-major order (one group) made the backward kernels slower, its working set exceeds L2.
+// `rank` = position in heavy -> light order (the caller maps it to its tile index), nx = tiles along x (without any
+// extra CTAs appended to grid.x).
+__device__ __forceinline__ void lpt_decode(int nx, int group, int& rank, int& h, int& b) {
+  const int ny = (int)gridDim.y, per = ny * (int)gridDim.z;
+  const int lin = (int)blockIdx.x + nx * ((int)blockIdx.y + ny * (int)blockIdx.z);
+  const int full = nx * group;
+  const int g = lin / full, base = g * group;
+  const int gsz = min(group, per - base);
+  const int within = lin - g * full;
+  rank = within / gsz;
+  const int hb = base + (within - rank * gsz);
+  b = hb / ny;
+  h = hb - b * ny;
+}
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 

@@ -111,7 +111,8 @@ flash_attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
   const AttnParams& a = p.a;
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
-  const int kv_blk = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+  int kv_blk, hk, b;                                         // early key blocks see the most queries: already heavy first
+  lpt_decode((int)gridDim.x, 8, kv_blk, hk, b);
   const int kv0 = kv_blk * kFbBlock;
   const int G = a.H / a.Hkv;
   const int nq = (a.Sq + kFbSub - 1) / kFbSub;              // 64-query steps
@@ -344,8 +345,9 @@ flash_attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
   const AttnParams& a = p.a;
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
-  const int q_blk = (int)gridDim.x - 1 - (int)blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
+  int lpt_rank, h, b;
+  lpt_decode((int)gridDim.x, 8, lpt_rank, h, b);
+  const int q_blk = (int)gridDim.x - 1 - lpt_rank;
   const int hk = h / (a.H / a.Hkv);
   const int q0 = q_blk * kFbBlock;
   int kv_limit = a.Sk;

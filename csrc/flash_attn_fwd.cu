@@ -136,8 +136,9 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t tmem_ptr_addr = bar + 8u * 15;
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // warp index: provably uniform
-  const int q_blk = n_qt - 1 - (int)blockIdx.x;  // heavy (late) causal blocks first
-  const int h = blockIdx.y, b = blockIdx.z;
+  int lpt_rank, h, b;
+  lpt_decode(n_qt, 16, lpt_rank, h, b);
+  const int q_blk = n_qt - 1 - lpt_rank;         // heavy (late) causal blocks first, over all heads
   const int hk = h / (p.H / p.Hkv);
   const int q_base = q_blk * kFaBlock * kFaTiles;
 

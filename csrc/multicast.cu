@@ -261,9 +261,11 @@ __device__ __forceinline__ void mm_load8(const float* src, long long i, long lon
 // rank r reads slice r with multimem.ld_reduce - ONE read per element answered by the NVSwitch with the sum over all
 // replicas - scales and writes it to its ordinary output tensor.  The SMs never see the peers' partial values and each GPU
 // receives n elements instead of (world - 1) * n.
+// (Measured at 4 GPUs, 1 GiB fp32: 4 or 8 vectors in flight per thread and one or two CTAs per SM all give 1.57 ms - the
+// rate is set by the switch / links, not by the request depth.)
 template <typename TIn, typename TOut>
 __global__ void __launch_bounds__(512, 1) nvls_reducescatter_kernel(McCtx c, const TIn* __restrict__ mc, TOut* __restrict__ out,
-                                                                   long long n, float scale) {
+                                                                      long long n, float scale) {
   __shared__ int is_last;
   mc_arrive_and_wait(c);
   const long long n8 = n >> 3;

@@ -142,6 +142,14 @@ B200DIST_API int b200_swiglu_fwd(const void* a, const void* b, void* y, long lon
 B200DIST_API int b200_swiglu_bwd(const void* dy, const void* a, const void* b, void* da, void* db,
                              long long rows, int F, long long ldy, long long lda, long long ldb,
                              long long ldda, long long lddb, int dtype, cudaStream_t stream);
+/* softmax over attention scores with Philox dropout on the probabilities (mask regenerated from seed / offset, never stored):
+   probs = softmax(scale * scores [+ causal]), probs_dropped = probs * mask / (1 - p); rows = B * H * sq, cols % 4 == 0 */
+B200DIST_API int b200_softmax_dropout_fwd(const void* scores, void* probs, void* probs_dropped, long long rows, int cols, int sq,
+                                      float scale, int causal, float p_drop, unsigned long long seed,
+                                      unsigned long long offset, int dtype, cudaStream_t stream);
+B200DIST_API int b200_softmax_dropout_bwd(const void* probs, const void* d_probs_dropped, void* d_scores, long long rows, int cols,
+                                      float scale, float p_drop, unsigned long long seed, unsigned long long offset,
+                                      cudaStream_t stream);
 B200DIST_API int b200_elementwise(const void* x, const void* y2, void* out, long long n, int op,
                               float alpha, int dtype, cudaStream_t stream);
 B200DIST_API int b200_cast_scale(const void* src, int src_dtype, void* dst, int dst_dtype, long long n,

@@ -5,7 +5,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-GROUPS = ["gemm_k1", "gemm_k2", "gemm_k3", "simt", "norms", "elementwise", "attn_fwd", "attn_bwd", "conv", "models", "optim_overlap", "fused_block"]
+GROUPS = ["gemm_k1", "gemm_k2", "gemm_k3", "simt", "norms", "elementwise", "attn_fwd", "attn_bwd", "conv", "models", "optim_overlap", "fused_block", "attn_dropout"]
 
 
 @pytest.mark.parametrize("group", GROUPS)

@@ -162,6 +162,28 @@ def main():
                     ref = torch.empty(n * world, device=dev, dtype=dt); dist.all_gather_into_tensor(ref, x)
                     out = torch.empty(n * world, device=dev, dtype=dt); comm.all_gather(out, x)
                     check(f"all_gather NVLS {dt} n={n} call {rep}", out, ref)
+        # "registered" tensors (Communicator.nvls_tensor): the collective runs where the tensor is, no staging copies
+        n = 1 << 16
+        xi = comm.nvls_tensor(n * world, torch.float32, channel=2)
+        go = comm.nvls_tensor(n * world, torch.float32, channel=1)
+        xb = comm.nvls_tensor(n, torch.float32, channel=3)
+        if xi is not None and go is not None and xb is not None:
+            for rep in range(2):
+                srcv = torch.randint(-8, 8, (n * world,), device=dev).float(); xi.copy_(srcv)
+                r = torch.empty(n, device=dev); dist.reduce_scatter_tensor(r, srcv)
+                o = torch.empty(n, device=dev); comm.reduce_scatter(o, xi)
+                check(f"reduce_scatter registered input call {rep}", o, r)
+                x = torch.randint(-8, 8, (n,), device=dev).float()
+                ref = torch.empty(n * world, device=dev); dist.all_gather_into_tensor(ref, x)
+                comm.all_gather(go, x)
+                check(f"all_gather registered output call {rep}", go, ref)
+            keep_b, comm.nvls_broadcast = comm.nvls_broadcast, True
+            for root in (0, world - 1):
+                val = torch.randint(-8, 8, (n,), device=dev).float(); xb.copy_(val)
+                rb = val.clone(); dist.broadcast(rb, src=root)
+                comm.broadcast(xb, src=root)
+                check(f"broadcast registered root {root}", xb, rb)
+            comm.nvls_broadcast = keep_b
         # zero-copy forms on a dedicated multicast buffer (what FSDP uses for its gradient staging)
         n = 1 << 16
         mcb = comm.nvls_buffer(n * world * 4)

@@ -195,7 +195,7 @@ def group_attn_fwd(results):
     ro2, rl2 = _attn_ref(q[:, 128:], k[:, :128], v[:, :128], True, 128, 0)
     _check("attn fwd chunk offsets", o2, ro2, 2e-2, 2e-2, results)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    for (B, S, H, hd) in ((2, 4096, 32, 128), (1, 8192, 32, 128)):
+    for (B, S, H, hd) in ((2, 4096, 32, 128), (1, 4096, 32, 128), (1, 8192, 32, 128)):
         q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q)
         ms = _time(lambda: N.flash_attn_fwd(q, k, v, causal=True), flush=flush)
         fl = 4.0 * B * H * S * S * hd / 2
@@ -228,12 +228,12 @@ def group_attn_bwd(results):
         _check(f"attn bwd dK {tag}", dk, kr.grad, 5e-2, 3e-2, results)
         _check(f"attn bwd dV {tag}", dv, vr.grad, 5e-2, 3e-2, results)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    B, S, H, hd = 2, 4096, 32, 128
-    q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q); do = torch.randn_like(q)
-    o, lse = N.flash_attn_fwd(q, k, v, causal=True)
-    ms = _time(lambda: N.flash_attn_bwd(q, k, v, o, do, lse, causal=True), flush=flush)
-    fl = 2.5 * 4.0 * B * H * S * S * hd / 2
-    print(f"[TIME] attn bwd causal B{B} S{S} H{H} hd{hd}: {ms:.3f} ms {fl/ms/1e9:.0f} TFLOP/s (5-GEMM flops)", flush=True)
+    for (B, S, H, hd) in ((2, 4096, 32, 128), (1, 4096, 32, 128)):     # the second one is what a Llama-7B step runs
+        q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q); do = torch.randn_like(q)
+        o, lse = N.flash_attn_fwd(q, k, v, causal=True)
+        ms = _time(lambda: N.flash_attn_bwd(q, k, v, o, do, lse, causal=True), flush=flush)
+        fl = 2.5 * 4.0 * B * H * S * S * hd / 2
+        print(f"[TIME] attn bwd causal B{B} S{S} H{H} hd{hd}: {ms:.3f} ms {fl/ms/1e9:.0f} TFLOP/s (5-GEMM flops)", flush=True)
 
 
 GROUPS = {"norms": group_norms, "elementwise": group_elementwise, "attn_fwd": group_attn_fwd,
@@ -463,5 +463,59 @@ def group_fused_block(results):
         print(f"[TIME] llama-7b block fwd+bwd S4096 {'fused node' if fused else 'module-by-module'}: {ms:.3f} ms", flush=True)
 
 
+def group_attn_dropout(results):
+    """Attention with Philox dropout on the probabilities vs an fp32 PyTorch expression that uses the SAME mask (rebuilt on
+    the host from the seed), forward and backward; the pipeline transformer block in train / eval mode."""
+    import torch
+    from b200dist import ops
+    from b200dist.ops import native as N
+    from b200dist.ops.functional import philox_keep_mask
+    _check, _time = _h()
+    dev = "cuda"
+    torch.manual_seed(11)
+    # 1. the mask itself: uniform scores make every kept probability 1 / cols / (1 - p), every dropped one 0
+    for (rows, cols, p, seed, off) in ((64, 128, 0.1, 1234, 1), (37, 516, 0.5, 2 ** 40 + 17, 99)):
+        s = torch.zeros(rows, cols, device=dev)
+        probs, dropped = N.softmax_dropout_fwd(s, rows, 1.0, False, p, seed, off)
+        ref = philox_keep_mask(rows * cols, p, seed, off).view(rows, cols).to(dev)
+        _check(f"philox mask {rows}x{cols} p={p}", (dropped > 0).float(), ref.float(), 0.0, 0.0, results)
+        _check(f"softmax probs {rows}x{cols}", probs, torch.full_like(s, 1.0 / cols), 1e-3, 1e-2, results)
+    # 2. full attention, forward + backward, same mask on both sides
+    for (B, S, H, hd, causal, p) in ((2, 64, 8, 32, False, 0.1), (1, 132, 4, 64, True, 0.25), (2, 256, 2, 128, False, 0.0001)):
+        q = torch.randn(B, S, H, hd, device=dev).bfloat16(); k = torch.randn_like(q); v = torch.randn_like(q)
+        do = torch.randn_like(q)
+        seed = 4242 + S
+        ql, kl, vl = [t.clone().requires_grad_(True) for t in (q, k, v)]
+        import b200dist.ops.functional as Fn
+        Fn._dropout_calls = 6                       # the call below uses offset 7
+        o = ops.attention_dropout(ql, kl, vl, p, causal=causal, seed=seed)
+        o.backward(do)
+        keep = philox_keep_mask(B * H * S * S, p, seed, 7).view(B, H, S, S).to(dev)
+        qr, kr, vr = [t.float().requires_grad_(True) for t in (q, k, v)]
+        sc = (qr.transpose(1, 2) @ kr.transpose(1, 2).transpose(-1, -2)) * hd ** -0.5
+        if causal:
+            sc = sc.masked_fill(torch.ones(S, S, device=dev, dtype=torch.bool).triu(1), float("-inf"))
+        pr = torch.softmax(sc, -1) * keep / (1 - p)
+        orf = (pr @ vr.transpose(1, 2)).transpose(1, 2)
+        orf.backward(do.float())
+        tag = f"B{B} S{S} H{H} hd{hd} causal={causal} p={p}"
+        _check(f"attn dropout O {tag}", o, orf, 3e-2, 3e-2, results)
+        _check(f"attn dropout dQ {tag}", ql.grad, qr.grad, 6e-2, 4e-2, results)
+        _check(f"attn dropout dK {tag}", kl.grad, kr.grad, 6e-2, 4e-2, results)
+        _check(f"attn dropout dV {tag}", vl.grad, vr.grad, 6e-2, 4e-2, results)
+    # 3. the recipe model: train mode runs (different masks per call), eval mode is deterministic and equals no-dropout
+    from b200dist.models.pp_transformer import Block
+    blk = Block(256, 8).to(dev).bfloat16()
+    x = torch.randn(2, 128, 256, device=dev).bfloat16()
+    blk.train()
+    y1, y2 = blk(x), blk(x)
+    differ = bool((y1 != y2).any().item())
+    results.append({"name": "pp block: two training calls draw different masks", "ok": differ, "max_err": 0.0, "bad": int(not differ),
+                    "ref_absmax": 0.0})
+    print(f"[{'PASS' if differ else 'FAIL'}] pp block: two training calls draw different masks", flush=True)
+    blk.eval()
+    _check("pp block eval deterministic", blk(x), blk(x), 0.0, 0.0, results)
+
+
 GROUPS.update({"conv": group_conv, "models": group_models, "optim_overlap": group_optim_overlap,
-               "fused_block": group_fused_block})
+               "fused_block": group_fused_block, "attn_dropout": group_attn_dropout})
