@@ -86,3 +86,38 @@ def test_fsdp_unit_layout_pulls_adjacent_groups_together():
     j = names.index("feed_forward.w1.weight")
     assert names[j + 1] == "feed_forward.w3.weight"
     assert sorted(names) == sorted(n for n, _ in m.layers[0].named_parameters())
+
+
+def test_attention_probability_dropout_and_host_philox_mask():
+    """nn.MultiheadAttention(dropout=p) semantics of the pipeline transformer block (reference
+    scripts/04_pipeline_parallel_pp/03_pipeline_training.py:57-58): dropout acts on the attention probabilities in
+    training mode only; the host Philox restatement (oracle of the CUDA kernel) is deterministic in (seed, offset)."""
+    from b200dist import ops
+    from b200dist.models.pp_transformer import Block
+    from b200dist.ops.functional import philox_keep_mask
+
+    m1 = philox_keep_mask(40000, 0.25, seed=77, offset=3)
+    assert torch.equal(m1, philox_keep_mask(40000, 0.25, seed=77, offset=3))
+    assert not torch.equal(m1, philox_keep_mask(40000, 0.25, seed=77, offset=4))
+    assert not torch.equal(m1, philox_keep_mask(40000, 0.25, seed=78, offset=3))
+    assert abs(m1.float().mean().item() - 0.75) < 0.02
+    assert torch.equal(m1[:1000], philox_keep_mask(1000, 0.25, seed=77, offset=3))      # counter-based: a prefix is a prefix
+    assert philox_keep_mask(1000, 0.0, 1).all()
+
+    torch.manual_seed(0)
+    q, k, v = (torch.randn(2, 12, 4, 16) for _ in range(3))
+    plain = ops.attention(q, k, v, causal=False)
+    assert torch.allclose(ops.attention_dropout(q, k, v, 0.3, training=False), plain)
+    assert torch.allclose(ops.attention_dropout(q, k, v, 0.0, training=True), plain)
+    dropped = ops.attention_dropout(q, k, v, 0.3, training=True)
+    assert dropped.shape == plain.shape and not torch.allclose(dropped, plain)
+
+    blk = Block(32, 4, dropout=0.2)
+    x = torch.randn(2, 12, 32, requires_grad=True)
+    blk.train()
+    y1, y2 = blk(x), blk(x)
+    assert not torch.equal(y1, y2)
+    y1.sum().backward()
+    assert x.grad is not None and torch.isfinite(x.grad).all()
+    blk.eval()
+    assert torch.equal(blk(x), blk(x))

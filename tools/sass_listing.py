@@ -5,8 +5,9 @@ kernel under profiles/sass/, gzip-compressed, plus an index with instruction cou
     python tools/sass_listing.py 'flash_attn'    # any kernels whose demangled name matches the regex
 
 What to look for (B200_PROFILING.md): UTCHMMA(.2CTA) = tcgen05.mma, LDTM / STTM = tcgen05.ld / st, UTMALDG = TMA tensor
-load, UBLKCP = TMA bulk copy (the peer pulls of the all-gather GEMM), UTCBAR = tcgen05.commit, LDGMC / STGMC... (multimem)
-= NVSwitch in-fabric reduce / multicast store, ST.E.*.SYS / LD.E.*.SYS = peer-memory accesses with system scope.
+load, UTMASTG = TMA tensor store, UBLKCP = TMA bulk copy (the peer pulls of the all-gather GEMM), UTCBAR = tcgen05.commit,
+LDGMC = multimem.ld_reduce (NVSwitch in-fabric reduction); multimem.st is an ordinary STG.E.128.STRONG.SYS on the multicast
+address; ST / LD ... .STRONG.SYS = peer-memory accesses with system scope.
 """
 from __future__ import annotations
 
@@ -20,17 +21,18 @@ ROOT = Path(__file__).resolve().parent.parent
 SO = ROOT / "b200dist" / "_native" / "libb200dist.so"
 OUT = ROOT / "profiles" / "sass"
 
-DEFAULT = (r"gemm_tcgen05_kernel<2, 256, false, false, __nv_bfloat16, true>|"       # all-gather -> GEMM / GEMM -> reduce-scatter
-           r"gemm_tcgen05_kernel<2, 256, false, true, __nv_bfloat16, true>|"
-           r"gemm_tcgen05_kernel<2, 256, false, false, __nv_bfloat16, false>|"      # plain forward GEMM (reference point)
-           r"gemm_tcgen05_kernel<1, 128, false, false, __nv_bfloat16, true>|"       # implicit-GEMM convolution fprop / dgrad
-           r"gemm_tcgen05_kernel<1, 128, true, true, float, true>|"                 # implicit-GEMM weight gradient
+DEFAULT = (r"gemm_tcgen05_kernel<2, 256, false, false, __nv_bfloat16, true, [01]>|"  # all-gather -> GEMM / GEMM -> reduce-scatter (1 = TMA-store epilogue)
+           r"gemm_tcgen05_kernel<2, 256, false, true, __nv_bfloat16, true, [01]>|"
+           r"gemm_tcgen05_kernel<2, 256, false, false, __nv_bfloat16, false, 0>|"   # plain forward GEMM (reference point)
+           r"gemm_tcgen05_kernel<1, (64|128), false, false, __nv_bfloat16, true, 0>|"  # implicit-GEMM convolution fprop / dgrad / stem
+           r"gemm_tcgen05_kernel<1, 128, true, true, float, true, 0>|"              # implicit-GEMM weight gradient
            r"comm_rs_adamw_kernel<__nv_bfloat16|nvls_rs_adamw_kernel<__nv_bfloat16|nvls_allreduce_kernel<__nv_bfloat16|"
-           r"nvls_reducescatter_kernel<__nv_bfloat16, float|nvls_allgather_kernel|nvls_broadcast_kernel|"
-           r"comm_slab_reduce_kernel|comm_allreduce_push_kernel<__nv_bfloat16, __nv_bfloat16|"
+           r"nvls_reducescatter_kernel<__nv_bfloat16, float|nvls_reducescatter_kernel<float, float|nvls_allgather_kernel|"
+           r"nvls_broadcast_kernel|comm_slab_reduce_kernel|comm_allreduce_push_kernel<__nv_bfloat16, __nv_bfloat16, [01]>|"
+           r"comm_gather_push_kernel|comm_neighbor_kernel|"
            r"flash_attn_fwd_kernel<128>|flash_attn_bwd_dkv_kernel<128>|flash_attn_bwd_dq_kernel<128>")
 KEY = re.compile(r"\b(UTC[A-Z]*MMA[.\w]*|LDTM[.\w]*|STTM[.\w]*|UTMALDG[.\w]*|UTMASTG[.\w]*|UBLKCP[.\w]*|UTCBAR[.\w]*|LDGMC[.\w]*|"
-                 r"STGMC[.\w]*|REDG[.\w]*|RED\.E[.\w]*|HMMA[.\w]*|MUFU\.EX2|FFMA2|SYNCS[.\w]*)")
+                 r"STG\.E\.128\.STRONG\.SYS|LDG\.E\.128\.STRONG\.SYS|LD\.E\.128\.STRONG\.SYS|ST\.E\.128\.STRONG\.SYS|REDG[.\w]*|RED\.E[.\w]*|HMMA[.\w]*|MUFU\.EX2|FFMA2|SYNCS[.\w]*)")
 
 
 def main():
