@@ -213,13 +213,13 @@ class Communicator:
         self._nvls_buf[channel] = buf
         return buf
 
-    def _launch_nvls(self, buf, offset_bytes: int, n: int, dtype, scale: float, channel: int) -> None:
+    def _launch_nvls(self, buf, offset_bytes: int, n: int, dtype, scale: float, channel: int, split: bool = False) -> None:
         self._seq[channel] += 1
         if self._order is not None:
             self._order.record(channel, "all_reduce_nvls", n)
         L.call("comm_allreduce_nvls", self.flags.ptr_array, L.ptr(self.counter), I(self.rank), I(self.world), I(channel),
                U(self._seq[channel] & 0xFFFFFFFF), C.c_void_p(buf.mc_ptr + offset_bytes), LL(n), F(scale),
-               I(L.dtype_code(dtype)), I(self.max_ctas), self._s())
+               I(L.dtype_code(dtype)), I(self.max_ctas), I(1 if split else 0), self._s())
 
     def nvls_buffer(self, nbytes: int):
         """Collective: a dedicated NVSwitch multicast buffer (e.g. all DDP buckets of a model); None if unavailable."""
@@ -241,12 +241,16 @@ class Communicator:
         return buf
 
     def all_reduce_nvls_inplace(self, buf, offset_bytes: int, numel: int, dtype: torch.dtype, scale: float = 1.0,
-                                channel: int = 0) -> None:
+                                channel: int = 0, split: bool = False) -> None:
         """Reduce ``numel`` elements at ``offset_bytes`` of multicast buffer ``buf`` in place on every rank
-        (numel % (world * 16 / itemsize) == 0, offset 16-byte aligned)."""
+        (numel % (world * 16 / itemsize) == 0, offset 16-byte aligned).
+
+        ``split=True`` (for collectives issued on a side stream beside compute that may itself wait for other GPUs): the
+        waits for the peers run as one-warp kernels before and after the bulk kernel, which then never waits and cannot
+        take part in a cross-stream, cross-rank deadlock for SMs."""
         item = torch.empty((), dtype=dtype).element_size()
         assert offset_bytes % 16 == 0 and numel % (self.world * (16 // item)) == 0
-        self._launch_nvls(buf, offset_bytes, numel, dtype, scale, channel)
+        self._launch_nvls(buf, offset_bytes, numel, dtype, scale, channel, split)
 
     def nvls_tensor(self, numel: int, dtype: torch.dtype, channel: int = 0) -> Optional[torch.Tensor]:
         """Collective: a tensor of ``numel`` elements inside the channel's NVSwitch multicast buffer ("registered"
@@ -358,21 +362,22 @@ class Communicator:
                         LL(nbytes), I(self.max_ctas), self._s())
 
     def reduce_scatter_nvls_from(self, out: torch.Tensor, mc, offset_bytes: int, in_dtype: torch.dtype, scale: float = 1.0,
-                                 channel: int = 2) -> torch.Tensor:
+                                 channel: int = 2, split: bool = False) -> torch.Tensor:
         """out = scale * sum over ranks of slice ``rank`` of the [world * out.numel()] region at ``offset_bytes`` of
         multicast buffer ``mc`` (every rank wrote its own input into its replica): reduced inside the NVSwitch."""
         self._nvls_call("comm_reducescatter_nvls", channel, "reduce_scatter_nvls", out.numel(),
                         C.c_void_p(mc.mc_ptr + offset_bytes), L.ptr(out), LL(out.numel()), F(scale),
-                        I(L.dtype_code(in_dtype)), I(L.dtype_code(out.dtype)), I(self.max_ctas), self._s())
+                        I(L.dtype_code(in_dtype)), I(L.dtype_code(out.dtype)), I(self.max_ctas), I(1 if split else 0), self._s())
         return out
 
     def rs_adamw_nvls_from(self, mc, offset_bytes: int, in_dtype: torch.dtype, n: int, grad_scale: float, master, lowp, m, v,
-                           *, lr, beta1, beta2, eps, wd, step, channel: int = 2) -> None:
-        """FSDP gradient step in ONE kernel: reduce-scatter inside the switch + scale + AdamW on the local shard."""
+                           *, lr, beta1, beta2, eps, wd, step, channel: int = 2, split: bool = False) -> None:
+        """FSDP gradient step in ONE kernel: reduce-scatter inside the switch + scale + AdamW on the local shard
+        (``split``: see :meth:`all_reduce_nvls_inplace`)."""
         bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
         self._nvls_call("comm_rs_adamw_nvls", channel, "rs_adamw_nvls", n, C.c_void_p(mc.mc_ptr + offset_bytes), LL(n),
                         F(grad_scale), I(L.dtype_code(in_dtype)), L.ptr(master), L.ptr(lowp), L.ptr(m), L.ptr(v), F(lr),
-                        F(beta1), F(beta2), F(eps), F(wd), F(bc1), F(bc2), I(self.max_ctas), self._s())
+                        F(beta1), F(beta2), F(eps), F(wd), F(bc1), F(bc2), I(self.max_ctas), I(1 if split else 0), self._s())
 
     def all_gather_from(self, out: torch.Tensor, src: PeerBuffer, offset_bytes: int, nbytes: int,
                         channel: int = 1, copy_engine: bool = False) -> torch.Tensor:

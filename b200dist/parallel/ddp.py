@@ -145,7 +145,9 @@ class DistributedDataParallel(nn.Module):
 
     def _reduce(self, bucket: _Bucket, scale: float) -> None:
         if bucket.mc_offset is not None:
-            self.comm.all_reduce_nvls_inplace(self._mc, bucket.mc_offset, bucket.numel, bucket.dtype, scale, self._channel)
+            # split: the reducer stream runs beside backward kernels that may wait for other GPUs themselves (halo exchange)
+            self.comm.all_reduce_nvls_inplace(self._mc, bucket.mc_offset, bucket.numel, bucket.dtype, scale, self._channel,
+                                              split=True)
         else:
             self.comm.all_reduce(bucket.flat, scale=scale, channel=self._channel)
 

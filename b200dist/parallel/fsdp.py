@@ -403,19 +403,21 @@ class FSDP(nn.Module):
             ev.record(cur)
             with torch.cuda.stream(self.rs_stream):
                 self.rs_stream.wait_event(ev)
-                # the fused kernel writes a bf16 compute copy next to the fp32 master: bf16 models only
+                # the fused kernel writes a bf16 compute copy next to the fp32 master: bf16 models only.  split=True: this
+                # stream runs beside compute that may itself wait for other GPUs (fused TP GEMMs, ring attention), so
+                # the waits for the peers are one-warp kernels and the bulk kernel never holds SMs while waiting
                 if (self.nvls_grads and self.fused_optimizer and hp is not None and hp["kind"] == "adamw"):
                     self._ensure_state(u)
                     self.comm.rs_adamw_nvls_from(stage, 0, self.dtype, u.shard_numel, 1.0 / self.world, u.master, u.shard,
                                                  u.m, u.v, lr=hp["lr"], beta1=hp["betas"][0], beta2=hp["betas"][1],
-                                                 eps=hp["eps"], wd=hp["weight_decay"], step=t, channel=2)
+                                                 eps=hp["eps"], wd=hp["weight_decay"], step=t, channel=2, split=True)
                 elif self.nvls_grads:
                     if u.grad_shard is None:
                         u.grad_shard = torch.zeros(u.shard_numel, dtype=torch.float32, device=self.device)
-                        self.comm.reduce_scatter_nvls_from(u.grad_shard, stage, 0, self.dtype, 1.0 / self.world, channel=2)
+                        self.comm.reduce_scatter_nvls_from(u.grad_shard, stage, 0, self.dtype, 1.0 / self.world, channel=2, split=True)
                     else:
                         tmp = torch.empty_like(u.grad_shard)
-                        self.comm.reduce_scatter_nvls_from(tmp, stage, 0, self.dtype, 1.0 / self.world, channel=2)
+                        self.comm.reduce_scatter_nvls_from(tmp, stage, 0, self.dtype, 1.0 / self.world, channel=2, split=True)
                         u.grad_shard.add_(tmp)
                 elif self.fused_optimizer and hp is not None and hp["kind"] == "adamw" and self.dtype == torch.bfloat16:
                     self._ensure_state(u)

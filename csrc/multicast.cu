@@ -90,6 +90,7 @@ struct McCtx {
   uint32_t* counter;
   int rank, world, channel;
   uint32_t seq;
+  int split;   // 1: the waits for other GPUs happen in nvls_sync_kernel launches around this kernel (see there)
 };
 __device__ __forceinline__ uint32_t* mc_flag_row(const McCtx& c, int owner, int which) {
   return c.flags[owner] + ((size_t)c.channel * 2 + which) * 32;
@@ -100,6 +101,52 @@ __device__ __forceinline__ void mc_spin(const uint32_t* p, uint32_t seq) {
   while ((int32_t)(mc_ld_acquire(p) - seq) < 0) peer_spin_check(t0, spins, "nvls flag", seq, p);
 }
 
+// ---- shared prologue / epilogue of the NVLS kernels ----
+// A kernel that holds SMs while it waits for another GPU can deadlock against a second such kernel on another stream: on
+// rank A kernel X owns the SMs and waits for B's X, on rank B kernel Y owns them and waits for A's Y (seen at TP 4 x
+// FSDP 2: the fused all-gather GEMM of the main stream against reduce-scatter + AdamW of FSDP's side stream).  Callers
+// that run beside compute therefore ask for the SPLIT form: the waits move into one-warp nvls_sync_kernel launches (which
+// always find room on an SM) before and after, and the bulk kernel only signals - it never waits, so it always finishes.
+__device__ __forceinline__ void mc_arrive_and_wait(const McCtx& c) {
+  if (c.split) return;
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+  }
+  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
+  __syncthreads();
+}
+// Last CTA of the grid tells every peer "I am done" and (unless split) waits until every peer said so.
+__device__ __forceinline__ void mc_depart(const McCtx& c, int* is_last_smem) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
+    *is_last_smem = (done == gridDim.x);
+    if (*is_last_smem) c.counter[192 + c.channel] = 0;
+  }
+  __syncthreads();
+  if (*is_last_smem) {
+    if (threadIdx.x < c.world) {
+      __threadfence_system();
+      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + c.rank, c.seq);
+      if (!c.split) mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
+    }
+    __syncthreads();
+  }
+}
+// phase 0: raise my arrive flag at every peer and wait for theirs; phase 1: wait for every peer's depart flag.
+__global__ void __launch_bounds__(32, 1) nvls_sync_kernel(McCtx c, int phase) {
+  if ((int)threadIdx.x >= c.world) return;
+  if (phase == 0) {
+    __threadfence_system();
+    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
+    mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
+  } else {
+    mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
+  }
+}
+
 // In-place all-reduce of the multicast buffer: rank r reduces and re-broadcasts elements [r * slice, (r+1) * slice).
 //   arrive : every rank's input is final (flag row 0)
 //   body   : ld_reduce own slice through the switch, scale, multimem.st it back to every copy
@@ -107,12 +154,7 @@ __device__ __forceinline__ void mc_spin(const uint32_t* p, uint32_t seq) {
 template <typename T>
 __global__ void __launch_bounds__(512, 1) nvls_allreduce_kernel(McCtx c, T* __restrict__ mc, long long n, float scale) {
   __shared__ int is_last;
-  if (blockIdx.x == 0 && threadIdx.x < c.world) {
-    __threadfence_system();
-    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
-  }
-  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
-  __syncthreads();
+  mc_arrive_and_wait(c);
   constexpr int kPer = 16 / sizeof(T);               // elements per 16-byte access
   const long long slice = n / c.world;               // n % (world * kPer) == 0 (host-checked)
   const long long nv = slice / kPer;
@@ -148,52 +190,9 @@ __global__ void __launch_bounds__(512, 1) nvls_allreduce_kernel(McCtx c, T* __re
         }
     }
   }
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
-    is_last = (done == gridDim.x);
-    if (is_last) c.counter[192 + c.channel] = 0;
-  }
-  __syncthreads();
-  if (is_last) {
-    if (threadIdx.x < c.world) {
-      __threadfence_system();
-      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + c.rank, c.seq);
-      mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
-    }
-    __syncthreads();
-  }
+  mc_depart(c, &is_last);
 }
 
-// ---- shared prologue / epilogue of the NVLS kernels ----
-__device__ __forceinline__ void mc_arrive_and_wait(const McCtx& c) {
-  if (blockIdx.x == 0 && threadIdx.x < c.world) {
-    __threadfence_system();
-    mc_st_release(mc_flag_row(c, threadIdx.x, 0) + c.rank, c.seq);
-  }
-  if (threadIdx.x < c.world) mc_spin(mc_flag_row(c, c.rank, 0) + threadIdx.x, c.seq);
-  __syncthreads();
-}
-// Last CTA of the grid tells every peer "I am done" and waits until every peer said so.
-__device__ __forceinline__ void mc_depart(const McCtx& c, int* is_last_smem) {
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t done = atomicAdd(c.counter + 192 + c.channel, 1u) + 1u;
-    *is_last_smem = (done == gridDim.x);
-    if (*is_last_smem) c.counter[192 + c.channel] = 0;
-  }
-  __syncthreads();
-  if (*is_last_smem) {
-    if (threadIdx.x < c.world) {
-      __threadfence_system();
-      mc_st_release(mc_flag_row(c, threadIdx.x, 1) + c.rank, c.seq);
-      mc_spin(mc_flag_row(c, c.rank, 1) + threadIdx.x, c.seq);
-    }
-    __syncthreads();
-  }
-}
 // Where vector i (8 elements) of an fp32 array lives: a warp's 32 vectors cover 256 consecutive floats and lane l takes
 // floats [4l, 4l + 4) and [128 + 4l, 128 + 4l + 4), so each of its two 16-byte requests belongs to a fully used 512-byte
 // warp request.  (A lane reading 32 contiguous bytes as two requests would send every 32-byte sector over NVLink twice.)
@@ -537,7 +536,7 @@ B200_API int b200_mc_release(void* state) {
 // Communicator's signal pads; n must be a multiple of world * (16 / element size).
 B200_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                       unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas,
-                                      cudaStream_t stream) {
+                                      int split, cudaStream_t stream) {
   if (world < 2 || world > 8) { b200_set_error("allreduce_nvls: world %d out of range", world); return B200_ERR_LIMIT; }
   const int per = dtype == 0 ? 8 : 4;
   if (n % ((long long)world * per)) { b200_set_error("allreduce_nvls: n must be a multiple of world * %d", per); return B200_ERR_SHAPE; }
@@ -545,15 +544,17 @@ B200_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counte
   memset(&c, 0, sizeof(c));
   for (int r = 0; r < world; ++r) c.flags[r] = reinterpret_cast<uint32_t*>(const_cast<void*>(flag_ptrs[r]));
   c.counter = reinterpret_cast<uint32_t*>(counter);
-  c.rank = rank; c.world = world; c.channel = channel; c.seq = seq;
+  c.rank = rank; c.world = world; c.channel = channel; c.seq = seq; c.split = split ? 1 : 0;
+  if (dtype != 0 && dtype != 1) { b200_set_error("allreduce_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
   const long long nv = n / world / per;
   long long g = (nv + 512 * 8 - 1) / (512 * 8);
   int cap = max_ctas > 0 ? max_ctas : b200_sm_count();
   if (g > cap) g = cap;
   if (g < 1) g = 1;
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
   if (dtype == 0) nvls_allreduce_kernel<__nv_bfloat16><<<(int)g, 512, 0, stream>>>(c, (__nv_bfloat16*)mc_ptr, n, scale);
-  else if (dtype == 1) nvls_allreduce_kernel<float><<<(int)g, 512, 0, stream>>>(c, (float*)mc_ptr, n, scale);
-  else { b200_set_error("allreduce_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  else nvls_allreduce_kernel<float><<<(int)g, 512, 0, stream>>>(c, (float*)mc_ptr, n, scale);
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 1);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -603,20 +604,23 @@ static int mc_grid(long long items, int per_thread, int max_ctas) {
 // Replaces dist.reduce_scatter_tensor (the collective FSDP issues for gradients).
 B200_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                           unsigned seq, const void* mc_ptr, void* out, long long n, float scale,
-                                          int in_dtype, int out_dtype, int max_ctas, cudaStream_t stream) {
+                                          int in_dtype, int out_dtype, int max_ctas, int split, cudaStream_t stream) {
   McCtx c;
   if (int rc = mc_fill_ctx(c, flag_ptrs, counter, rank, world, channel, seq, "reducescatter_nvls")) return rc;
+  c.split = split ? 1 : 0;
   if ((n & 7) || ((uintptr_t)mc_ptr & 15) || ((uintptr_t)out & 15)) {
     b200_set_error("reducescatter_nvls: n %% 8 == 0 and 16-byte aligned pointers required"); return B200_ERR_SHAPE;
   }
   const int g = mc_grid(n >> 3, in_dtype == 0 ? 8 : 4, max_ctas);
 #define RSN(TI, TO) nvls_reducescatter_kernel<TI, TO><<<g, 512, 0, stream>>>(c, (const TI*)mc_ptr, (TO*)out, n, scale)
+  if ((in_dtype | out_dtype) & ~1) { b200_set_error("reducescatter_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
   if (in_dtype == 0 && out_dtype == 0) RSN(__nv_bfloat16, __nv_bfloat16);
   else if (in_dtype == 0 && out_dtype == 1) RSN(__nv_bfloat16, float);
   else if (in_dtype == 1 && out_dtype == 1) RSN(float, float);
-  else if (in_dtype == 1 && out_dtype == 0) RSN(float, __nv_bfloat16);
-  else { b200_set_error("reducescatter_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  else RSN(float, __nv_bfloat16);
 #undef RSN
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 1);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -625,19 +629,23 @@ B200_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* co
 B200_API int b200_comm_rs_adamw_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                      unsigned seq, const void* mc_ptr, long long n, float grad_scale, int in_dtype,
                                      float* master, void* lowp, float* m, float* v, float lr, float beta1, float beta2,
-                                     float eps, float wd, float bc1, float bc2, int max_ctas, cudaStream_t stream) {
+                                     float eps, float wd, float bc1, float bc2, int max_ctas, int split,
+                                     cudaStream_t stream) {
   McCtx c;
   if (int rc = mc_fill_ctx(c, flag_ptrs, counter, rank, world, channel, seq, "rs_adamw_nvls")) return rc;
   if ((n & 7) || ((uintptr_t)mc_ptr & 15)) { b200_set_error("rs_adamw_nvls: n %% 8 == 0 and a 16-byte aligned buffer required"); return B200_ERR_SHAPE; }
+  if (in_dtype != 0 && in_dtype != 1) { b200_set_error("rs_adamw_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  c.split = split ? 1 : 0;
   const int g = mc_grid(n >> 3, 4, max_ctas);
   const float bc2s = sqrtf(bc2);
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
   if (in_dtype == 0)
     nvls_rs_adamw_kernel<__nv_bfloat16><<<g, 512, 0, stream>>>(c, (const __nv_bfloat16*)mc_ptr, n, grad_scale, master,
                                                                 (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
-  else if (in_dtype == 1)
+  else
     nvls_rs_adamw_kernel<float><<<g, 512, 0, stream>>>(c, (const float*)mc_ptr, n, grad_scale, master, (__nv_bfloat16*)lowp,
                                                         m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
-  else { b200_set_error("rs_adamw_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
+  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 1);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -308,7 +308,7 @@ B200DIST_API int b200_mc_add_device(unsigned long long handle);
 B200DIST_API int b200_mc_bind_map(unsigned long long handle, size_t bytes, void** local_ptr, void** mc_ptr, void** state);
 B200DIST_API int b200_mc_release(void* state);
 B200DIST_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
-                                      unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas,
+                                      unsigned seq, void* mc_ptr, long long n, float scale, int dtype, int max_ctas, int split,
                                       cudaStream_t stream);
 B200DIST_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                       unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
@@ -318,11 +318,11 @@ B200DIST_API int b200_comm_broadcast_nvls(const void* const* flag_ptrs, void* co
  * dist.reduce_scatter_tensor / dist.all_gather_into_tensor and FSDP's gradient + optimizer step */
 B200DIST_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                               unsigned seq, const void* mc_ptr, void* out, long long n, float scale,
-                                              int in_dtype, int out_dtype, int max_ctas, cudaStream_t stream);
+                                              int in_dtype, int out_dtype, int max_ctas, int split, cudaStream_t stream);
 B200DIST_API int b200_comm_rs_adamw_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                          unsigned seq, const void* mc_ptr, long long n, float grad_scale, int in_dtype,
                                          float* master, void* lowp, float* m, float* v, float lr, float beta1, float beta2,
-                                         float eps, float wd, float bc1, float bc2, int max_ctas, cudaStream_t stream);
+                                         float eps, float wd, float bc1, float bc2, int max_ctas, int split, cudaStream_t stream);
 B200DIST_API int b200_comm_allgather_nvls(const void* const* flag_ptrs, void* counter, int rank, int world, int channel,
                                           unsigned seq, const void* src, void* mc_ptr, const void* replica_ptr, void* out,
                                           long long bytes, int max_ctas, cudaStream_t stream);

@@ -194,6 +194,19 @@ def main():
             o = torch.empty(n, device=dev, dtype=torch.float32)
             comm.reduce_scatter_nvls_from(o, mcb, 0, torch.bfloat16, 1.0)
             check("reduce_scatter NVLS zero-copy bf16 -> fp32", o, r)
+            # split handshakes (what FSDP / DDP use on their side streams): waits in one-warp kernels around the bulk kernel
+            for rep in range(3):
+                gi2 = torch.randint(-8, 8, (n * world,), device=dev).to(torch.bfloat16)
+                r2 = torch.empty(n, device=dev, dtype=torch.float32); dist.reduce_scatter_tensor(r2, gi2.float())
+                mcb.tensor(torch.bfloat16, 0, n * world).copy_(gi2)
+                o2 = torch.empty(n, device=dev, dtype=torch.float32)
+                comm.reduce_scatter_nvls_from(o2, mcb, 0, torch.bfloat16, 1.0, split=True)
+                check(f"reduce_scatter NVLS split handshake call {rep}", o2, r2)
+                ar = torch.randint(-8, 8, (n * world,), device=dev).to(torch.bfloat16)
+                rar = ar.clone(); dist.all_reduce(rar)
+                mcb.tensor(torch.bfloat16, 0, n * world).copy_(ar)
+                comm.all_reduce_nvls_inplace(mcb, 0, n * world, torch.bfloat16, 1.0, channel=2, split=True)
+                check(f"all_reduce NVLS in place, split handshake call {rep}", mcb.tensor(torch.bfloat16, 0, n * world), rar)
             sh = torch.randint(-8, 8, (n,), device=dev).to(torch.bfloat16)
             ref = torch.empty(n * world, device=dev, dtype=torch.bfloat16); dist.all_gather_into_tensor(ref, sh)
             comm.all_gather_nvls_into(mcb, 0, sh)
