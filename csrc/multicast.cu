@@ -135,6 +135,11 @@ __device__ __forceinline__ void mc_depart(const McCtx& c, int* is_last_smem) {
     __syncthreads();
   }
 }
+// Not waiting is not enough: a bulk kernel whose CTA needs a whole SM's registers (512 threads x 126) cannot START while a
+// peer-waiting GEMM of the main stream holds one CTA on every SM, and the sync kernels queued behind it - which the other
+// ranks wait for - are stuck with it.  Split-mode bulk kernels therefore run 256-thread CTAs (32 K registers, twice as many
+// CTAs): they fit beside a 192-thread GEMM CTA (23 K registers, 226 KB of shared memory) on the same SM.
+constexpr int kSplitThreads = 256;
 // phase 0: raise my arrive flag at every peer and wait for theirs; phase 1: wait for every peer's depart flag.
 __global__ void __launch_bounds__(32, 1) nvls_sync_kernel(McCtx c, int phase) {
   if ((int)threadIdx.x >= c.world) return;
@@ -551,9 +556,10 @@ B200_API int b200_comm_allreduce_nvls(const void* const* flag_ptrs, void* counte
   int cap = max_ctas > 0 ? max_ctas : b200_sm_count();
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
-  if (dtype == 0) nvls_allreduce_kernel<__nv_bfloat16><<<(int)g, 512, 0, stream>>>(c, (__nv_bfloat16*)mc_ptr, n, scale);
-  else nvls_allreduce_kernel<float><<<(int)g, 512, 0, stream>>>(c, (float*)mc_ptr, n, scale);
+  const int threads = split ? kSplitThreads : 512;
+  if (split) { g = g * (512 / kSplitThreads); nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0); }
+  if (dtype == 0) nvls_allreduce_kernel<__nv_bfloat16><<<(int)g, threads, 0, stream>>>(c, (__nv_bfloat16*)mc_ptr, n, scale);
+  else nvls_allreduce_kernel<float><<<(int)g, threads, 0, stream>>>(c, (float*)mc_ptr, n, scale);
   if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 1);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -612,7 +618,8 @@ B200_API int b200_comm_reducescatter_nvls(const void* const* flag_ptrs, void* co
     b200_set_error("reducescatter_nvls: n %% 8 == 0 and 16-byte aligned pointers required"); return B200_ERR_SHAPE;
   }
   const int g = mc_grid(n >> 3, in_dtype == 0 ? 8 : 4, max_ctas);
-#define RSN(TI, TO) nvls_reducescatter_kernel<TI, TO><<<g, 512, 0, stream>>>(c, (const TI*)mc_ptr, (TO*)out, n, scale)
+  const int threads = split ? kSplitThreads : 512, gs = split ? g * (512 / kSplitThreads) : g;
+#define RSN(TI, TO) nvls_reducescatter_kernel<TI, TO><<<gs, threads, 0, stream>>>(c, (const TI*)mc_ptr, (TO*)out, n, scale)
   if ((in_dtype | out_dtype) & ~1) { b200_set_error("reducescatter_nvls: bad dtype"); return B200_ERR_UNSUPPORTED; }
   if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
   if (in_dtype == 0 && out_dtype == 0) RSN(__nv_bfloat16, __nv_bfloat16);
@@ -638,12 +645,13 @@ B200_API int b200_comm_rs_adamw_nvls(const void* const* flag_ptrs, void* counter
   c.split = split ? 1 : 0;
   const int g = mc_grid(n >> 3, 4, max_ctas);
   const float bc2s = sqrtf(bc2);
+  const int threads = split ? kSplitThreads : 512, gs = split ? g * (512 / kSplitThreads) : g;
   if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 0);
   if (in_dtype == 0)
-    nvls_rs_adamw_kernel<__nv_bfloat16><<<g, 512, 0, stream>>>(c, (const __nv_bfloat16*)mc_ptr, n, grad_scale, master,
+    nvls_rs_adamw_kernel<__nv_bfloat16><<<gs, threads, 0, stream>>>(c, (const __nv_bfloat16*)mc_ptr, n, grad_scale, master,
                                                                 (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
   else
-    nvls_rs_adamw_kernel<float><<<g, 512, 0, stream>>>(c, (const float*)mc_ptr, n, grad_scale, master, (__nv_bfloat16*)lowp,
+    nvls_rs_adamw_kernel<float><<<gs, threads, 0, stream>>>(c, (const float*)mc_ptr, n, grad_scale, master, (__nv_bfloat16*)lowp,
                                                         m, v, lr, beta1, beta2, eps, wd, bc1, bc2s);
   if (split) nvls_sync_kernel<<<1, 32, 0, stream>>>(c, 1);
   B200_LAUNCH_CHECK();
