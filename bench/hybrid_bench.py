@@ -1,13 +1,13 @@
 #!/usr/bin/env python
 """BASELINE config 4: Llama-2 13B, TP 4 (+ sequence parallel) x FSDP 2, seq 8192, bf16, AdamW -> tokens/s.
 
-    torchrun --nproc-per-node 8 --master-addr 127.0.0.1 bench/hybrid_bench.py --tp 4 [--impl reference] [--fused]
+    torchrun --nproc-per-node 8 --master-addr 127.0.0.1 bench/hybrid_bench.py --tp 4 [--impl reference] [--no-fused]
 
-b200dist arm : llama_tp_plan (the plan of 01_fsdp_tp_hybrid.py:110-152 on local shards, peer-memory collectives; --fused
-               swaps in the all-gather->GEMM / GEMM->reduce-scatter kernels), then FSDP over the dp mesh dimension.
+b200dist arm : llama_tp_plan (the plan of 01_fsdp_tp_hybrid.py:110-152 on local shards, peer-memory collectives; by default
+               with the fused all-gather->GEMM / GEMM->reduce-scatter kernels, --no-fused keeps them apart), then FSDP over the dp mesh dimension.
 reference arm: the reference's own Llama model with the SAME plan expressed in torch DTensor styles exactly as the recipe
                does (parallelize_module + ColwiseParallel/RowwiseParallel/SequenceParallel/PrepareModuleInput), then
-               fully_shard over dp (per block + root, bf16 params / fp32 reduce) and torch AdamW(foreach) — BASELINE.md §4
+               fully_shard over dp (per block + root, bf16 params / bf16 reduce) and torch AdamW(foreach) — BASELINE.md §4
                row 4.  Both arms: cross-entropy loss, identical tokens on the TP peers of a dp replica."""
 from __future__ import annotations
 
@@ -32,7 +32,8 @@ def main():
     ap.add_argument("--batch-per-replica", type=int, default=1)
     ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--fused", action="store_true")
+    ap.add_argument("--fused", action="store_true", default=True, help="fused TP kernels (default)")
+    ap.add_argument("--no-fused", dest="fused", action="store_false", help="separate collective kernels + GEMMs")
     ap.add_argument("--no-sp", action="store_true")
     ap.add_argument("--activation-checkpointing", action="store_true", help="recompute each block in backward (b200dist arm)")
     ap.add_argument("--vocab-parallel-loss", action="store_true", help="keep the logits vocabulary-sharded (no [M, V] all-gather)")

@@ -22,6 +22,8 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--lr", type=float, default=3e-3)
     ap.add_argument("--no-sp", action="store_true")
+    ap.add_argument("--no-fused", action="store_true",
+                    help="keep collectives and GEMMs separate (default on CUDA with SP: fused all-gather->GEMM / GEMM->reduce-scatter blocks)")
     ap.add_argument("--activation-checkpointing", action="store_true")
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float32"])
     a = ap.parse_args()
@@ -45,6 +47,11 @@ def main():
     torch.manual_seed(0)
     model = Transformer.from_name(a.model, device=device, dtype=dtype, max_seq_len=max(a.seq_len, 256))
     llama_tp_plan(model, mesh["tp"], sequence_parallel=not a.no_sp)
+    if device.type == "cuda" and not a.no_sp and not a.no_fused:
+        # one kernel per (collective, GEMM) pair of the plan; inputs that do not qualify (batch > 1, local sequence not a
+        # multiple of 256) take the unfused path block by block.  13B, TP 4 x FSDP 2, seq 8192: 220.9 vs 251.7 ms per step
+        from b200dist.parallel.tp import enable_fused_tp
+        enable_fused_tp(model, mesh["tp"])
     if a.activation_checkpointing:
         model.enable_activation_checkpointing()
     model = FSDP(model, process_group=mesh.get_group("dp"))

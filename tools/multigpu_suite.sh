@@ -24,7 +24,7 @@ for w in $WHAT; do
       run comm_bench 260 $TR bench/comm_bench.py --impl both --benchmark_runs 10 --warmup_runs 3 --output_file gpurun_out/comm_bench_${N}gpu.csv ;;
     hybrid)
       run hybrid_fused 200 $TR bench/hybrid_bench.py --tp 4 --fused --steps 6 --warmup 3
-      run hybrid 200 $TR bench/hybrid_bench.py --tp 4 --steps 6 --warmup 3
+      run hybrid 200 $TR bench/hybrid_bench.py --tp 4 --no-fused --steps 6 --warmup 3
       run hybrid_ref 260 $TR bench/hybrid_bench.py --tp 4 --impl reference --steps 6 --warmup 3 ;;
     pp)
       run pp 200 $TR bench/pp_bench.py --pp 4 --dp 2
