@@ -70,12 +70,17 @@ __global__ void rope_strided_kernel(const T* __restrict__ x, T* __restrict__ y, 
 template <typename T>
 __global__ void swiglu_fwd_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y,
                                   long long rows, int F, long long lda, long long ldb, long long ldy) {
+  // (row, chunk) advance incrementally: one 64-bit division per thread instead of one per 8 elements (the division and
+  // its address arithmetic were a third of the instructions of these kernels, which sit close to the issue limit)
   const int cpr = F >> 3;
-  const long long n = rows * cpr;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / cpr;
-    const int c = (int)(i - r * cpr) * 8;
+  const long long stride = (long long)gridDim.x * blockDim.x, i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long dr = stride / cpr;
+  const int dc = (int)(stride - dr * cpr);
+  long long r = i0 / cpr;
+  int cc = (int)(i0 - r * cpr);
+  for (; r < rows; r += dr, cc += dc) {
+    if (cc >= cpr) { cc -= cpr; ++r; if (r >= rows) break; }
+    const int c = cc * 8;
     float av[8], bv[8], o[8];
     Vec8<T>::load(a + r * lda + c, av);
     Vec8<T>::load(b + r * ldb + c, bv);
@@ -91,11 +96,14 @@ __global__ void swiglu_bwd_kernel(const T* __restrict__ dy, const T* __restrict_
                                   long long rows, int F, long long ldy, long long lda, long long ldb,
                                   long long ldda, long long lddb) {
   const int cpr = F >> 3;
-  const long long n = rows * cpr;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long r = i / cpr;
-    const int c = (int)(i - r * cpr) * 8;
+  const long long stride = (long long)gridDim.x * blockDim.x, i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long dr = stride / cpr;
+  const int dc = (int)(stride - dr * cpr);
+  long long r = i0 / cpr;
+  int cc = (int)(i0 - r * cpr);
+  for (; r < rows; r += dr, cc += dc) {
+    if (cc >= cpr) { cc -= cpr; ++r; if (r >= rows) break; }
+    const int c = cc * 8;
     float g[8], av[8], bv[8], oa[8], ob[8];
     Vec8<T>::load(dy + r * ldy + c, g);
     Vec8<T>::load(a + r * lda + c, av);

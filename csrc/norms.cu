@@ -14,24 +14,36 @@ namespace b200 {
 constexpr int kMaxChunks = 4;  // 8-element chunks cached per thread
 
 // ------------------------------- RMSNorm -----------------------------------
+// Persistent CTAs (all resident: grid <= 6 per SM), one row at a time, the next row's loads in flight (unconverted, 16
+// registers) while the current row is reduced, scaled and stored.
 template <typename T>
-__global__ void rmsnorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w, T* __restrict__ y,
-                                   float* __restrict__ rstd_out, int rows, int D, float eps) {
+__global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w, T* __restrict__ y,
+                                                          float* __restrict__ rstd_out, int rows, int D, float eps) {
   __shared__ float red[33];
   const int nchunks = D >> 3;
-  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
-    const T* xr = x + (long long)row * D;
+  Raw8<T> nx[kMaxChunks];
+  auto fetch = [&](int row) {
+#pragma unroll
+    for (int i = 0; i < kMaxChunks; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) nx[i].load(x + (long long)row * D + c * 8);
+    }
+  };
+  int row = blockIdx.x;
+  if (row < rows) fetch(row);
+  for (; row < rows; row += gridDim.x) {
     float v[kMaxChunks][8];
     float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < kMaxChunks; ++i) {
       const int c = threadIdx.x + i * blockDim.x;
       if (c < nchunks) {
-        Vec8<T>::load(xr + c * 8, v[i]);
+        nx[i].unpack(v[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
       }
     }
+    if (row + (int)gridDim.x < rows) fetch(row + (int)gridDim.x);
     ss = block_sum(ss, red);
     const float rstd = rsqrtf(ss / (float)D + eps);
     if (threadIdx.x == 0 && rstd_out) rstd_out[row] = rstd;
@@ -50,38 +62,61 @@ __global__ void rmsnorm_fwd_kernel(const T* __restrict__ x, const T* __restrict_
   }
 }
 
-template <typename T>
-__global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+// Persistent CTAs, one row at a time, software pipelined: the NEXT row's x / dy (/ residual gradient) are requested - and
+// parked unconverted in registers - before the current row's block reduction, so the HBM round trip of row r + 1 overlaps the
+// reduction, the arithmetic and the stores of row r (the unpipelined version was latency bound: 2.5 TB/s).  The weight is
+// re-read per row (8-16 KB, L1 resident) instead of being held in registers.  CH = 8-element chunks per thread: rows of up to
+// 2048 elements use 2, up to 4096 use 1 (512 threads for D = 4096: 32 warps per SM at two CTAs instead of 8 - with 4 chunks
+// per thread the kernel was bound by instruction latency at two warps per scheduler, not by memory: 80.7 -> 64.4 us at CH = 2).
+template <typename T, int CH>
+__global__ void __launch_bounds__(CH == 1 ? 512 : 256) rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                    const T* __restrict__ w, const float* __restrict__ rstd_in,
                                    T* __restrict__ dx, float* __restrict__ dw_partial, int rows, int D,
                                    const T* addsrc) {   // addsrc: optional [rows, D] added to dx (may alias dx)
   __shared__ float red[33];
   const int nchunks = D >> 3;
-  float dwacc[kMaxChunks][8];
-  float wv[kMaxChunks][8];
+  float dwacc[CH][8];
 #pragma unroll
-  for (int i = 0; i < kMaxChunks; ++i) {
-    const int c = threadIdx.x + i * blockDim.x;
+  for (int i = 0; i < CH; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
-    if (c < nchunks) Vec8<T>::load(w + c * 8, wv[i]);
-  }
-  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
-    const T* xr = x + (long long)row * D;
-    const T* gr = dy + (long long)row * D;
-    const float rstd = rstd_in[row];
-    float xv[kMaxChunks][8], gv[kMaxChunks][8];
-    float dot = 0.f;
+  Raw8<T> nx[CH], ng[CH], na[CH];
+  auto fetch = [&](int row) {
 #pragma unroll
-    for (int i = 0; i < kMaxChunks; ++i) {
+    for (int i = 0; i < CH; ++i) {
       const int c = threadIdx.x + i * blockDim.x;
       if (c < nchunks) {
-        Vec8<T>::load(xr + c * 8, xv[i]);
-        Vec8<T>::load(gr + c * 8, gv[i]);
+        const long long o = (long long)row * D + c * 8;
+        nx[i].load(x + o);
+        ng[i].load(dy + o);
+        if (addsrc != nullptr) na[i].load(addsrc + o);   // rows are disjoint: no hazard with the stores of earlier rows
+      }
+    }
+  };
+  int row = blockIdx.x;
+  if (row < rows) fetch(row);
+  for (; row < rows; row += gridDim.x) {
+    const float rstd = rstd_in[row];
+    float xv[CH][8], gv[CH][8];
+    Raw8<T> ca[CH];
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      nx[i].unpack(xv[i]);
+      ng[i].unpack(gv[i]);
+      ca[i] = na[i];
+    }
+    if (row + (int)gridDim.x < rows) fetch(row + (int)gridDim.x);
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) {
+      const int c = threadIdx.x + i * blockDim.x;
+      if (c < nchunks) {
+        float wv[8];
+        Vec8<T>::load(w + c * 8, wv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           dwacc[i][j] += gv[i][j] * xv[i][j] * rstd;
-          gv[i][j] *= wv[i][j];
+          gv[i][j] *= wv[j];
           dot += gv[i][j] * xv[i][j];
         }
       }
@@ -90,7 +125,7 @@ __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict
     const float coef = dot * rstd * rstd * rstd / (float)D;
     T* dxr = dx + (long long)row * D;
 #pragma unroll
-    for (int i = 0; i < kMaxChunks; ++i) {
+    for (int i = 0; i < CH; ++i) {
       const int c = threadIdx.x + i * blockDim.x;
       if (c < nchunks) {
         float o[8];
@@ -98,7 +133,7 @@ __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict
         for (int j = 0; j < 8; ++j) o[j] = gv[i][j] * rstd - xv[i][j] * coef;
         if (addsrc != nullptr) {
           float prev[8];
-          Vec8<T>::load(addsrc + (long long)row * D + c * 8, prev);
+          ca[i].unpack(prev);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += prev[j];
         }
@@ -108,7 +143,7 @@ __global__ void rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict
   }
   float* part = dw_partial + (long long)blockIdx.x * D;
 #pragma unroll
-  for (int i = 0; i < kMaxChunks; ++i) {
+  for (int i = 0; i < CH; ++i) {
     const int c = threadIdx.x + i * blockDim.x;
     if (c < nchunks) {
       *reinterpret_cast<float4*>(part + c * 8) = make_float4(dwacc[i][0], dwacc[i][1], dwacc[i][2], dwacc[i][3]);
@@ -290,12 +325,34 @@ B200_API int b200_norm_bwd_partials(int rows) {
   return rows < n ? (rows < 1 ? 1 : rows) : n;
 }
 
+// The pipelined RMSNorm backward keeps two rows per thread in registers (184): two CTAs per SM are resident, so a third
+// per SM would only form a half-empty second wave.  The scratch is sized by b200_norm_bwd_partials (>= this).
+static int rmsnorm_bwd_cfg(int D, int* threads, int* ch) {
+  if (int rc = norm_threads(D, threads)) return rc;
+  *ch = kMaxChunks;
+  const int nchunks = D >> 3;
+  if (nchunks > 256 && nchunks <= 512) {  // one chunk per thread on up to 512 threads (D = 4096: 32 warps per SM at two CTAs)
+    *threads = (nchunks + 31) / 32 * 32;
+    *ch = 1;
+  } else if (nchunks > 64 && nchunks <= 256) {   // two chunks per thread
+    int t = ((nchunks + 1) / 2 + 31) / 32 * 32;
+    *threads = t < 64 ? 64 : t;
+    *ch = 2;
+  }
+  return B200_OK;
+}
+static int rmsnorm_bwd_grid(int rows) {
+  const int n = b200_norm_bwd_partials(rows), cap = 2 * b200_sm_count();
+  return n < cap ? n : cap;
+}
+
 B200_API int b200_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int rows, int D,
                               float eps, int dtype, cudaStream_t stream) {
   if (rows <= 0) return B200_OK;
   int threads;
   if (int rc = norm_threads(D, &threads)) return rc;
-  const int grid = rows;   // one CTA per row: a capped persistent grid ran two unequal waves (7 CTAs/SM resident, 8/SM launched)
+  const int cap = 6 * b200_sm_count();   // all resident at once (<= 80 registers x <= 256 threads): one wave, no tail
+  const int grid = rows < cap ? rows : cap;
   B200_DISPATCH_DTYPE(dtype, T, (rmsnorm_fwd_kernel<T><<<grid, threads, 0, stream>>>(
       (const T*)x, (const T*)w, (T*)y, rstd, rows, D, eps)));
   B200_LAUNCH_CHECK();
@@ -307,11 +364,18 @@ B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, cons
                               void* dx, void* dw, float* scratch, int rows, int D, int add_to_dx,
                               int accumulate_dw, int dtype, cudaStream_t stream) {
   if (rows <= 0) return B200_OK;
-  int threads;
-  if (int rc = norm_threads(D, &threads)) return rc;
-  const int grid = b200_norm_bwd_partials(rows);
+  int threads, ch;
+  if (int rc = rmsnorm_bwd_cfg(D, &threads, &ch)) return rc;
+  const int grid = rmsnorm_bwd_grid(rows);
   B200_DISPATCH_DTYPE(dtype, T, {
-    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+    if (ch == 1)
+      rmsnorm_bwd_kernel<T, 1><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    else if (ch == 2)
+      rmsnorm_bwd_kernel<T, 2><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    else
+      rmsnorm_bwd_kernel<T, kMaxChunks><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
                                                         (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
     colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
                                                                     accumulate_dw);
@@ -326,11 +390,18 @@ B200_API int b200_rmsnorm_bwd_res(const void* dy, const void* x, const void* w, 
                                   void* dx, void* dw, float* scratch, int rows, int D, int accumulate_dw, int dtype,
                                   cudaStream_t stream) {
   if (rows <= 0) return B200_OK;
-  int threads;
-  if (int rc = norm_threads(D, &threads)) return rc;
-  const int grid = b200_norm_bwd_partials(rows);
+  int threads, ch;
+  if (int rc = rmsnorm_bwd_cfg(D, &threads, &ch)) return rc;
+  const int grid = rmsnorm_bwd_grid(rows);
   B200_DISPATCH_DTYPE(dtype, T, {
-    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+    if (ch == 1)
+      rmsnorm_bwd_kernel<T, 1><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, (const T*)dres);
+    else if (ch == 2)
+      rmsnorm_bwd_kernel<T, 2><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, (const T*)dres);
+    else
+      rmsnorm_bwd_kernel<T, kMaxChunks><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
                                                         (T*)dx, scratch, rows, D, (const T*)dres);
     colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D, accumulate_dw);
   });
@@ -418,8 +489,8 @@ B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void*
                    "(use b200_rmsnorm_bwd with caller-provided scratch)", D, kNoAllocMaxD);
     return B200_ERR_LIMIT;
   }
-  int threads;
-  if (int rc = norm_threads(D, &threads)) return rc;
+  int threads, ch;
+  if (int rc = rmsnorm_bwd_cfg(D, &threads, &ch)) return rc;
   int dev = -1;
   B200_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kNoAllocMaxDevices) {
@@ -435,7 +506,14 @@ B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void*
   }
   const int grid = rows < kNoAllocMaxPartials ? rows : kNoAllocMaxPartials;  // grid * D <= array size
   B200_DISPATCH_DTYPE(dtype, T, {
-    rmsnorm_bwd_kernel<T><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+    if (ch == 1)
+      rmsnorm_bwd_kernel<T, 1><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    else if (ch == 2)
+      rmsnorm_bwd_kernel<T, 2><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
+                                                             (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
+    else
+      rmsnorm_bwd_kernel<T, kMaxChunks><<<grid, threads, 0, stream>>>((const T*)dy, (const T*)x, (const T*)w, rstd,
                                                         (T*)dx, scratch, rows, D, add_to_dx ? (const T*)dx : (const T*)nullptr);
     colsum_partials_kernel<T><<<ceil_div(D, kColsumCols), 256, 0, stream>>>(scratch, (T*)dw, grid, D,
                                                                     accumulate_dw);

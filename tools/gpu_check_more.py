@@ -121,6 +121,15 @@ def group_elementwise(results):
     lg = torch.randn(8192, 32000, device=dev); tg = torch.randint(0, 32000, (8192,), device=dev)
     ms = _time(lambda: N.xent_fwd(lg, tg))
     print(f"[TIME] xent_fwd 8192x32000 fp32: {ms:.3f} ms {lg.numel()*4*2/ms/1e6:.0f} GB/s (2 reads)", flush=True)
+    del lg
+    # the Llama-7B feed-forward shapes of one 4096-token step (w1|w3 output stacked in one [M, 2F] tensor)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    M_, F_ = 4096, 11008
+    h13 = torch.randn(M_, 2 * F_, device=dev).bfloat16(); gy = torch.randn(M_, F_, device=dev).bfloat16()
+    ms = _time(lambda: N.swiglu_fwd(h13[:, :F_], h13[:, F_:]), flush=flush)
+    print(f"[TIME] swiglu_fwd {M_}x{F_} bf16: {ms*1e3:.1f} us  {3*M_*F_*2/ms/1e6:.0f} GB/s", flush=True)
+    ms = _time(lambda: N.swiglu_bwd(gy, h13[:, :F_], h13[:, F_:]), flush=flush)
+    print(f"[TIME] swiglu_bwd {M_}x{F_} bf16: {ms*1e3:.1f} us  {5*M_*F_*2/ms/1e6:.0f} GB/s", flush=True)
     # optimizers vs torch
     for pdt, gdt in ((torch.float32, torch.float32), (torch.float32, torch.bfloat16)):
         n = 10007
