@@ -325,8 +325,9 @@ B200_API int b200_norm_bwd_partials(int rows) {
   return rows < n ? (rows < 1 ? 1 : rows) : n;
 }
 
-// The pipelined RMSNorm backward keeps two rows per thread in registers (184): two CTAs per SM are resident, so a third
-// per SM would only form a half-empty second wave.  The scratch is sized by b200_norm_bwd_partials (>= this).
+// The pipelined RMSNorm backward keeps two rows per thread in registers: whichever chunk count is chosen below, two CTAs
+// per SM are resident (512 threads x 56 registers, 256 x 97, or 128-256 x 184), so a third per SM would only form a
+// half-empty second wave.  The scratch is sized by b200_norm_bwd_partials (>= this).
 static int rmsnorm_bwd_cfg(int D, int* threads, int* ch) {
   if (int rc = norm_threads(D, threads)) return rc;
   *ch = kMaxChunks;
