@@ -200,6 +200,15 @@ class ColwiseParallel(ParallelStyle):
         module._tp_info = {"style": "colwise", "dim": 0, "world": T, "rank": r}
 
         def forward(x, residual=None):
+            if seq_in and getattr(module, "_tp_fused_ag", False) and getattr(module, "bias", None) is None:
+                from . import tp_fused
+
+                if tp_fused.fusable(x, comm) and module.weight.shape[0] % 8 == 0:
+                    # all-gather(seq) -> GEMM as one kernel; backward = GEMM -> reduce-scatter(seq) + one wgrad GEMM
+                    y = tp_fused.ag_linear(comm, x, [module.weight])[0]
+                    if gather_out:
+                        y = all_gather_last(y, comm)
+                    return y + residual if residual is not None else y
             if seq_in:
                 x = all_gather_seq(x, comm)
             elif not getattr(module, "_tp_input_from_gather", False):
@@ -385,6 +394,10 @@ def enable_fused_tp(model, tp_mesh: DeviceMesh):
 
         blk._unfused_forward = blk.forward
         blk.forward = block_forward
+    # the LM head of the plan is a column-parallel Linear behind a sequence-sharded norm: the same all-gather -> GEMM kernel
+    head = getattr(model, "output", None)
+    if head is not None and getattr(head, "_tp_info", {}).get("style") == "colwise":
+        head._tp_fused_ag = True
     model._tp_fused = True
     return model
 
