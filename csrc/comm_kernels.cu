@@ -818,8 +818,10 @@ B200_API int b200_comm_rs_adamw_local(const void* const* slab_ptrs, int world, l
   CommCtx c = {};
   for (int r = 0; r < world; ++r) c.data[r] = const_cast<void*>(slab_ptrs[r]);
   c.rank = 0; c.world = world; c.channel = -1;
-  const int grid = comm_grid(n >> 3, 512, max_ctas);
-#define RSA(TI, KW) comm_rs_adamw_kernel<TI, KW><<<grid, 512, 0, stream>>>(c, 0, n, grad_scale, master, \
+  // 256-thread CTAs, twice as many: this kernel runs on FSDP's side stream, where a CTA must fit on an SM next to a CTA of a
+  // main-stream kernel that is waiting for other GPUs (see nvls_sync_kernel in multicast.cu)
+  const int grid = 2 * comm_grid(n >> 3, 512, max_ctas);
+#define RSA(TI, KW) comm_rs_adamw_kernel<TI, KW><<<grid, 256, 0, stream>>>(c, 0, n, grad_scale, master, \
         (__nv_bfloat16*)lowp, m, v, lr, beta1, beta2, eps, wd, bc1, sqrtf(bc2))
   if (in_dtype == 0) { if (world <= 2) RSA(__nv_bfloat16, 2); else if (world <= 4) RSA(__nv_bfloat16, 4); else RSA(__nv_bfloat16, 8); }
   else { if (world <= 2) RSA(float, 2); else if (world <= 4) RSA(float, 4); else RSA(float, 8); }
