@@ -46,7 +46,8 @@ class Trainer:
         removes the per-kernel launch cost of launch-bound models (several hundred launches per step for a ResNet).
         Needs an optimizer whose step-dependent scalars live on the device (``FusedAdamW(capturable=True)``; FusedSGD bakes
         its learning rate into the graph).  Wrappers that drive side streams from autograd hooks (DDP / FSDP) are not
-        captured: the flag is ignored for them.  EXPERIMENTAL: written against the capture rules, not yet run on a GPU."""
+        captured: the flag is ignored for them.  Checked by ``tools/cuda_graph_check.py`` on a B200: loss sequence identical to the
+        eager step, 4.71 -> 1.13 ms per step on a 4-layer, dim-512 Llama (``profiles/cuda_graph_check_r2.log``)."""
         self.model, self.optimizer, self.loss_fn = model, optimizer, loss_fn
         self._graph_wanted = bool(cuda_graph) and not callable(getattr(model, "finish_backward", None))
         self._graph_warmup = max(1, int(graph_warmup))
