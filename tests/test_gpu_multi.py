@@ -26,3 +26,13 @@ def test_collectives_match_nccl():
 def test_parallel_strategies_match_single_gpu():
     out = _torchrun("tools/parallel_check.py")
     assert "ALL OK" in out
+
+
+def test_zigzag_ring_and_fused_rowwise_linear():
+    out = _torchrun("tools/microbench/zigzag_linear_ar_check.py")
+    assert "failures 0" in out
+
+
+def test_fused_gemms_with_ragged_widths():
+    out = _torchrun("tools/microbench/ag_gemm_ragged_check.py")
+    assert "failures 0" in out
