@@ -378,3 +378,38 @@ def test_reference_arm_provisions_itself():
     for rel in ("fsdp_tp/llama2_model.py", "scripts/main.py", "tests/torch_comm_bench.py"):
         assert filecmp.cmp(REF / rel, ir.reference_path(*rel.split("/")), shallow=False), rel
     assert ir.ensure_reference() == root
+
+
+def test_attention_cta_order_covers_every_tile_once():
+    """Host restatement of ``lpt_decode`` (csrc/attn_common.cuh): the grouped heavy-first reading of the linear CTA index must
+    hit every (tile, head, batch) exactly once, also when heads x batch is not a multiple of the group size (40 heads in
+    groups of 16), and inside a group all heads' tiles of one weight class come before any lighter tile."""
+    def decode(bx, by, bz, nx, ny, nz, group):
+        per = ny * nz
+        lin = bx + nx * (by + ny * bz)
+        full = nx * group
+        g = lin // full
+        base = g * group
+        gsz = min(group, per - base)
+        within = lin - g * full
+        rank = within // gsz
+        hb = base + (within - rank * gsz)
+        return rank, hb % ny, hb // ny, lin
+
+    for nx, ny, nz, group in ((16, 32, 1, 16), (32, 40, 1, 8), (16, 40, 2, 16), (3, 10, 1, 16), (1, 4, 3, 8), (32, 32, 2, 8)):
+        seen, order = set(), []
+        for bz in range(nz):
+            for by in range(ny):
+                for bx in range(nx):
+                    rank, h, b, lin = decode(bx, by, bz, nx, ny, nz, group)
+                    assert 0 <= rank < nx and 0 <= h < ny and 0 <= b < nz
+                    seen.add((rank, h, b))
+                    order.append((lin, rank, b * ny + h))
+        assert len(seen) == nx * ny * nz
+        order.sort()
+        # dispatch order: groups ascend; inside a group the rank (heavy -> light) never decreases
+        last = {}
+        for _, rank, hb in order:
+            g = hb // group
+            assert rank >= last.get(g, 0)
+            last[g] = rank
