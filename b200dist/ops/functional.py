@@ -348,7 +348,8 @@ def attention_dropout(q, k, v, p_drop: float, causal: bool = False, scale: Optio
                       seed: Optional[int] = None):
     """Attention with dropout on the softmax probabilities (``nn.MultiheadAttention(dropout=p)`` semantics) on
     [B, S, H, hd] tensors, H == Hkv.  Without dropout (eval, p == 0) this is :func:`attention`.  The seed comes from
-    torch's generator (so ``torch.manual_seed`` makes runs repeatable); every call advances a Philox offset."""
+    torch's host generator (so ``torch.manual_seed`` makes runs repeatable and checkpointed recomputation sees the same
+    mask); with an explicit ``seed`` every call advances a Philox offset instead."""
     global _dropout_calls
     if not training or p_drop <= 0.0:
         return attention(q, k, v, causal=causal, scale=scale)
@@ -364,10 +365,14 @@ def attention_dropout(q, k, v, p_drop: float, causal: bool = False, scale: Optio
         pr = F.dropout(torch.softmax(s_, dim=-1), p_drop, training=True)
         return (pr @ vf).transpose(1, 2).to(q.dtype)
     if seed is None:
-        seed = int(torch.randint(0, 2 ** 62, (1,)).item())      # host generator: no device sync
-    _dropout_calls += 1
+        # a fresh seed per call from torch's HOST generator (no device sync).  Activation checkpointing restores that
+        # generator before it recomputes a block, so the recomputation draws the same seed and rebuilds the same mask.
+        seed, offset = int(torch.randint(0, 2 ** 62, (1,)).item()), 0
+    else:
+        _dropout_calls += 1          # explicit seed: successive calls (layers) get successive Philox offsets
+        offset = _dropout_calls
     in_dtype = q.dtype
-    o = _AttnDropoutFn.apply(_bf16(q), _bf16(k), _bf16(v), causal, scale, float(p_drop), seed, _dropout_calls)
+    o = _AttnDropoutFn.apply(_bf16(q), _bf16(k), _bf16(v), causal, scale, float(p_drop), seed, offset)
     return o.to(in_dtype)
 
 
