@@ -29,7 +29,8 @@ DEFAULT = (r"gemm_tcgen05_kernel<2, 256, false, false, __nv_bfloat16, true, [01]
            r"comm_rs_adamw_kernel<__nv_bfloat16|nvls_rs_adamw_kernel<__nv_bfloat16|nvls_allreduce_kernel<__nv_bfloat16|"
            r"nvls_reducescatter_kernel<__nv_bfloat16, float|nvls_reducescatter_kernel<float, float|nvls_allgather_kernel|"
            r"nvls_broadcast_kernel|comm_slab_reduce_kernel|comm_allreduce_push_kernel<__nv_bfloat16, __nv_bfloat16, [01]>|"
-           r"comm_gather_push_kernel|comm_neighbor_kernel|"
+           r"comm_gather_push_kernel|comm_neighbor_kernel|nvls_sync_kernel|"
+           r"rmsnorm_bwd_kernel<__nv_bfloat16, 1>|rmsnorm_fwd_kernel<__nv_bfloat16>|softmax_dropout_fwd_kernel<__nv_bfloat16>|"
            r"flash_attn_fwd_kernel<128>|flash_attn_bwd_dkv_kernel<128>|flash_attn_bwd_dq_kernel<128>")
 KEY = re.compile(r"\b(UTC[A-Z]*MMA[.\w]*|LDTM[.\w]*|STTM[.\w]*|UTMALDG[.\w]*|UTMASTG[.\w]*|UBLKCP[.\w]*|UTCBAR[.\w]*|LDGMC[.\w]*|"
                  r"STG\.E\.128\.STRONG\.SYS|LDG\.E\.128\.STRONG\.SYS|LD\.E\.128\.STRONG\.SYS|ST\.E\.128\.STRONG\.SYS|REDG[.\w]*|RED\.E[.\w]*|HMMA[.\w]*|MUFU\.EX2|FFMA2|SYNCS[.\w]*)")
