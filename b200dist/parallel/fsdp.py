@@ -485,6 +485,34 @@ class FSDP(nn.Module):
             self._free(self.root_unit)
         self._in_backward = False
 
+    def clip_grad_norm_(self, max_norm: float, norm_type: float = 2.0) -> torch.Tensor:
+        """Scale all gradients so that their GLOBAL norm (over every shard of every rank) is at most ``max_norm``; returns
+        the norm before clipping.  Call between ``backward()`` and ``optimizer.step()``.
+
+        Needs gradients that still exist at that point: with the fused reduce-scatter + AdamW path (bf16 parameters on
+        several GPUs, ``fused_optimizer=True``) every unit has already been updated when backward ends, so there is
+        nothing left to clip - construct ``FSDP(model, fused_optimizer=False)`` when you clip."""
+        self.finish_backward()
+        if self.native and self.world > 1 and self.fused_optimizer:
+            raise RuntimeError("clip_grad_norm_: the fused reduce-scatter + AdamW path applies each unit's update during "
+                               "backward; build the wrapper with FSDP(model, fused_optimizer=False) to clip gradients")
+        shards = [u.grad_shard for u in self.exec_units if u.grad_shard is not None]
+        if not shards:
+            return torch.zeros((), dtype=torch.float32, device=self.device)
+        if norm_type == float("inf"):
+            total = torch.stack([g.detach().abs().max().float() for g in shards]).max()
+            if self.world > 1:
+                dist.all_reduce(total, op=dist.ReduceOp.MAX, group=self.comm.group)
+        else:
+            total = torch.stack([g.detach().float().abs().pow(norm_type).sum() for g in shards]).sum()
+            if self.world > 1:          # shards are disjoint slices of the flat gradients (padding is zero)
+                dist.all_reduce(total, group=self.comm.group)
+            total = total.pow(1.0 / norm_type)
+        coef = (float(max_norm) / (total + 1e-6)).clamp(max=1.0)
+        for g in shards:
+            g.mul_(coef.to(g.dtype))
+        return total
+
     @contextlib.contextmanager
     def no_sync(self):
         """Gradient accumulation: backward passes inside the block keep their (unsharded) gradients in ``p.grad`` and skip

@@ -302,3 +302,39 @@ def _fsdp_consolidated_resume_worker(rank, world, tmpdir):
 
 def test_fsdp_consolidated_checkpoint_with_sharded_optimizer_resumes(tmp_path):
     run_distributed(_fsdp_consolidated_resume_worker, 2, args=(str(tmp_path),))
+
+
+def _fsdp_clip_worker(rank, world, ref_sd, ref_norms):
+    from b200dist import ops
+    from b200dist.parallel import FSDP
+
+    fsdp = FSDP(_toy_llama(), fused_optimizer=False)
+    opt = fsdp.build_optimizer("adamw", lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    for t, ref_norm in zip(_batches(3), ref_norms):
+        shard = t.chunk(world)[rank]
+        opt.zero_grad()
+        ops.cross_entropy(fsdp(shard[:, :-1]), shard[:, 1:]).backward()
+        norm = fsdp.clip_grad_norm_(0.5)
+        assert abs(float(norm) - ref_norm) < 1e-4 * max(1.0, ref_norm), (float(norm), ref_norm)
+        opt.step()
+    sd = fsdp.full_state_dict(rank0_only=False, offload_to_cpu=True)
+    for k, v in sd.items():
+        if not v.is_complex():
+            assert torch.allclose(v, ref_sd[k], atol=3e-5, rtol=1e-4), f"rank {rank} {k}: {(v - ref_sd[k]).abs().max()}"
+
+
+def test_fsdp_clip_grad_norm_matches_single_process():
+    """Global-norm clipping over sharded gradients == torch.nn.utils.clip_grad_norm_ on the unsharded model."""
+    from b200dist import ops
+
+    model = _toy_llama()
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-2, betas=(0.9, 0.95), weight_decay=0.1)
+    norms = []
+    for t in _batches(3):
+        opt.zero_grad()
+        ops.cross_entropy(model(t[:, :-1]), t[:, 1:]).backward()
+        norms.append(float(torch.nn.utils.clip_grad_norm_(model.parameters(), 0.5)))
+        opt.step()
+    assert max(norms) > 0.5          # the clip is active in this setting
+    ref = {k: v.clone() for k, v in model.state_dict().items()}
+    run_distributed(_fsdp_clip_worker, 2, args=(ref, norms))
